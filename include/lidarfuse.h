@@ -1,0 +1,183 @@
+/*
+ * lidarfuse.h -- C ABI of the B200-native LiDAR-camera fusion / evaluation path.
+ *
+ * The reference (KaranSankla/Lidar_Object_Detection) is 100 % Python and has no
+ * FFI of its own; its "operator interface" for this path is the set of
+ * module-level functions of Coding_testes/cvs_erosion.py, V1..V5 and
+ * seg_with_pointcloud.py.  Each entry point below names the reference lines it
+ * replaces (paths relative to the reference root).  The ctypes binding a
+ * maintainer would add to those scripts is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every pointer marked DEVICE is a device pointer owned by the caller
+ *     (e.g. torch.Tensor.data_ptr()); the library owns only the opaque lf_ctx;
+ *   - every call returns 0 on success or a negative LF_E_* code; nothing
+ *     throws, aborts or prints across this boundary;
+ *   - work is enqueued asynchronously on the caller's cudaStream_t (passed as
+ *     void*); no call synchronises or allocates, so every call is CUDA-graph
+ *     capturable;
+ *   - a ctx is bound to one device and is not thread-safe.
+ *
+ * Layouts
+ *   points        float [N][4]  (x, y, z, reflectance), 16-byte aligned
+ *   masks (raw)   uint8 [M][H][W], non-zero = set      (or float [M][H][W], >= 1.0 = set)
+ *   masks (packed) uint32 [M][H][wpr], wpr = ceil(W/32), bit (x & 31) of word x>>5, LSB = lowest x
+ *   boxes         lf_box (below), filled by lf_prepare_boxes or by the host binding
+ *   CSR offsets   pt_off int64 [F+1], mask_off / box_off int32 [F+1], cnt_off int64 [F+1]
+ *                 with cnt_off[f+1]-cnt_off[f] = M_f * B_f  (inside[] is row-major [M_f][B_f])
+ */
+#ifndef LIDARFUSE_H
+#define LIDARFUSE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LF_VERSION 100
+
+#define LF_OK            0
+#define LF_E_ARG        -1   /* bad argument (null pointer, negative size, unsupported shape) */
+#define LF_E_CUDA       -2   /* a CUDA call failed; lf_last_cuda_error() has the cudaError_t */
+#define LF_E_UNSUPPORTED -3  /* size beyond what the kernels are built for */
+#define LF_E_NOCAMERA   -4   /* lf_set_camera has not been called */
+
+#define LF_MAX_SE 15         /* structuring elements up to 15x15 */
+#define LF_MAX_CARS 64       /* masks per frame handled in one pass of lf_fuse_batch */
+
+#define LF_POLICY_NEAREST 0  /* z-buffer: smallest depth per pixel (north-star) */
+#define LF_POLICY_LAST    1  /* last point in index order wins (seg_with_pointcloud.py:162-168) */
+
+typedef struct lf_ctx lf_ctx;
+
+/* One oriented box in the form the containment test consumes
+ * (cvs_erosion.py:114-138): c0 = corner 0, e1 = c1-c0, e2 = c3-c0, e3 = c4-c0,
+ * ee[i] = dot(e_i, e_i); lo/hi = conservative float32 bounds of the region the
+ * three closed slabs intersect in, united with [amin, amax] (early-out only). */
+typedef struct lf_box {
+    double c0[3];
+    double e1[3];
+    double e2[3];
+    double e3[3];
+    double ee[3];
+    double amin[3];           /* min / max over the 8 corners: the axis-aligned */
+    double amax[3];           /* variant point_in_bbox (V1:118-139)             */
+    float lo[3];
+    float hi[3];
+} lf_box;                     /* 192 bytes */
+
+int lf_version(void);
+const char* lf_strerror(int code);
+
+int lf_create(lf_ctx** out, int device);
+int lf_destroy(lf_ctx* ctx);
+int lf_last_cuda_error(const lf_ctx* ctx);
+
+/* Calibration: TrVeloToRect (4x4 row-major, f64) and K (3x4 row-major, f64) as
+ * built by cvs_erosion.py:303-314 and CameraPerspective.{K,width,height}. */
+int lf_set_camera(lf_ctx* ctx, const double TrVeloToRect[16], const double K[12], int W, int H);
+
+/* A3 + A4  projection and validity gate.
+ * Replaces cvs_erosion.py:342-346, 359 (V1:340-344, V4:258-262, V5:467-471,
+ * seg_with_pointcloud.py:132-139).  u, v: int64 exactly as numpy's
+ * round(...).astype(int); depth f64; pix = v*W+u for points passing
+ * 0<=u<W, 0<=v<H, 0<depth<max_depth, else -1.  Any output pointer may be NULL. */
+int lf_project(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, double max_depth,
+               int64_t* u /*DEVICE*/, int64_t* v /*DEVICE*/, double* depth /*DEVICE*/,
+               int32_t* pix /*DEVICE*/, void* stream);
+
+/* A5  mask binarisation + erosion + bit-packing.
+ * Replaces cvs_erosion.py:96-106 (V3:81-97): cv2.erode with the k x k
+ * structuring element `se` (row-major uint8 [k][k], HOST pointer, anchor at the
+ * centre, border = +inf), `iterations` times; iterations == 0 packs only (the
+ * V2 no-erosion variant, V2:197-200).
+ * mode: 0 = uint8 masks, non-zero = set; 1 = float32 masks, >= 1.0 = set (the
+ * uint8 truncation of cvs_erosion.py:101 and V2:197); 2 = float32 masks,
+ * > 0.5 = set (seg_with_pointcloud.py:167). */
+int lf_erode_pack(lf_ctx* ctx, const void* masks /*DEVICE [m][H][W]*/, int mode, int64_t m,
+                  int H, int W, const uint8_t* se /*HOST [k][k]*/, int k, int iterations,
+                  uint32_t* packed /*DEVICE [m][H][wpr]*/, void* stream);
+
+/* packed -> uint8 0/1 images (the eroded masks the reference keeps as float32,
+ * cvs_erosion.py:103). */
+int lf_unpack_masks(lf_ctx* ctx, const uint32_t* packed /*DEVICE*/, int64_t m, int H, int W,
+                    uint8_t* out /*DEVICE [m][H][W]*/, void* stream);
+
+/* A7  box preparation on the host (plain C, no device work): corners_velo
+ * [n][8][3] f64 -> lf_box[n].  Replaces the per-call edge set-up of
+ * cvs_erosion.py:120-123, 129-131. */
+int lf_prepare_boxes(const double* corners_velo /*HOST [n][8][3]*/, int64_t n, lf_box* out /*HOST*/);
+
+/* A3 + A4 + A6 + A8 + A9 counters, fused, for a batch of F frames.
+ * Replaces the per-frame body cvs_erosion.py:342-372: projection, gate,
+ * extract_car_points_by_mask (:148-162), oriented_point_in_bbox (:114-145, or
+ * the AABB variant V1:118-139 when use_oriented == 0) and the counting half of
+ * calculate_car_point_statistics (:175-195).  Outputs must be zeroed by the
+ * caller (lf_zero_counters does it in one launch).
+ *   total[mask]        points of the car (gated, in mask)
+ *   inside[cnt_off[f] + c*B_f + b]   points of car c inside box b
+ *   n_in_box[box]      gated points inside box b (extension metrics)
+ *   n_valid[f]         points passing the gate
+ *   car_bits           optional DEVICE uint64 [total points]: bit c = point in mask c of its frame
+ *                      (0 for gated-out points); may be NULL                                       */
+int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
+                  const uint32_t* packed /*DEVICE*/, const int32_t* mask_off /*DEVICE [F+1]*/,
+                  const lf_box* boxes /*DEVICE*/, const int32_t* box_off /*DEVICE [F+1]*/,
+                  const int64_t* cnt_off /*DEVICE [F+1]*/, int F, int64_t max_points_per_frame,
+                  int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,
+                  int32_t* total /*DEVICE*/, int32_t* inside /*DEVICE*/, int32_t* n_in_box /*DEVICE*/,
+                  int32_t* n_valid /*DEVICE*/, uint64_t* car_bits /*DEVICE or NULL*/, void* stream);
+
+/* A6 stand-alone: bit c of bits[i] = packed mask c is set at (v[i], u[i])
+ * (extract_car_points_by_mask, cvs_erosion.py:148-162).  m <= LF_MAX_CARS. */
+int lf_mask_gather(lf_ctx* ctx, const uint32_t* packed /*DEVICE [m][H][wpr]*/, int m, int H, int W,
+                   const int64_t* u /*DEVICE*/, const int64_t* v /*DEVICE*/, int64_t n,
+                   uint64_t* bits /*DEVICE [n]*/, void* stream);
+
+/* A8 stand-alone: out[i] = point i inside the box (oriented_point_in_bbox,
+ * cvs_erosion.py:114-145; point_in_bbox, V1:118-139 when use_oriented == 0).
+ * xyz: DEVICE float32 or float64 rows of stride_elems elements (x, y, z first). */
+int lf_points_in_box(lf_ctx* ctx, const void* xyz /*DEVICE*/, int is_f64, int64_t n, int stride_elems,
+                     const lf_box* box /*DEVICE*/, int use_oriented, uint8_t* out /*DEVICE [n]*/, void* stream);
+
+/* A9 stand-alone counting: inside[set_id[i]*B + b] += point i in box b
+ * (the double loop of calculate_car_point_statistics, cvs_erosion.py:175-195). */
+int lf_count_in_boxes(lf_ctx* ctx, const void* xyz /*DEVICE*/, int is_f64, int64_t n, int stride_elems,
+                      const int32_t* set_id /*DEVICE [n]*/, const lf_box* boxes /*DEVICE [B]*/, int B,
+                      int use_oriented, int32_t* inside /*DEVICE, zeroed by the caller*/, void* stream);
+
+/* A9  per-car decision: first strict maximum over boxes starting from 0
+ * (cvs_erosion.py:181-195), matched iff best >= min_points (:198).
+ *   best_idx[mask] (-1 when no box holds a point), best_cnt[mask]
+ *   agg int64[8]: {frames with rows, rows, matched rows, sum total (matched),
+ *                  sum inside (matched), sum total (all rows), 0, 0} ADDED to what is there */
+int lf_car_stats(lf_ctx* ctx, const int32_t* total, const int32_t* inside, const int32_t* mask_off,
+                 const int32_t* box_off, const int64_t* cnt_off, int F, int min_points,
+                 int32_t* best_idx /*DEVICE*/, int32_t* best_cnt /*DEVICE*/, int64_t* agg /*DEVICE*/,
+                 void* stream);
+
+int lf_zero_counters(lf_ctx* ctx, void* buf /*DEVICE*/, int64_t bytes, void* stream);
+
+/* A10  depth maps.  Replaces seg_with_pointcloud.py:153-170.  One frame.
+ * scratch: DEVICE uint64 [H*W].  full: optional DEVICE f64 [H][W] full-frame
+ * map (0 where no point).  per_car: optional DEVICE f64 [m][H][W], pixel kept
+ * where packed mask c is set.  policy: LF_POLICY_*. */
+int lf_depth_maps(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, double max_depth,
+                  int policy, const uint32_t* packed /*DEVICE [m][H][wpr] or NULL*/, int m,
+                  uint64_t* scratch /*DEVICE*/, double* full /*DEVICE or NULL*/,
+                  double* per_car /*DEVICE or NULL*/, void* stream);
+
+/* Synthetic HDL-64-shaped workload (bench / tests only).
+ * cars: DEVICE f64 [F][ncars][8] = {cx, cy, cz, yaw, l, w, h, pad} in the velodyne frame. */
+int lf_synth_points(lf_ctx* ctx, const double* cars /*DEVICE*/, int ncars, int F, int rings, int azimuths,
+                    uint64_t seed, float* pts /*DEVICE [F][rings*azimuths][4]*/, void* stream);
+/* masks rendered by casting the pixel ray against each (inflated) car box;
+ * Tinv = inverse of TrVeloToRect (4x4 row-major f64, HOST). */
+int lf_synth_masks(lf_ctx* ctx, const double* cars /*DEVICE*/, int ncars, int F, const double Tinv[16],
+                   double inflate, uint8_t* masks /*DEVICE [F][ncars][H][W]*/, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIDARFUSE_H */

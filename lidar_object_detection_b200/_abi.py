@@ -1,0 +1,101 @@
+"""ctypes binding of include/lidarfuse.h.
+
+There is no CPU fallback: if the CUDA library cannot be loaded, or no CUDA
+device is present when a context is requested, this module raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, '_lib', 'liblidarfuse.so')
+
+LF_OK, LF_E_ARG, LF_E_CUDA, LF_E_UNSUPPORTED, LF_E_NOCAMERA = 0, -1, -2, -3, -4
+POLICY_NEAREST, POLICY_LAST = 0, 1
+MODE_U8, MODE_F32_GE1, MODE_F32_GT_HALF = 0, 1, 2
+MAX_CARS = 64
+
+# numpy mirror of struct lf_box (192 bytes)
+BOX_DTYPE = np.dtype([('c0', '<f8', 3), ('e1', '<f8', 3), ('e2', '<f8', 3), ('e3', '<f8', 3),
+                      ('ee', '<f8', 3), ('amin', '<f8', 3), ('amax', '<f8', 3),
+                      ('lo', '<f4', 3), ('hi', '<f4', 3)])
+assert BOX_DTYPE.itemsize == 192
+
+_vp, _i32, _i64, _f64, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_uint64
+
+SIGNATURES = {
+    'lf_version': (C.c_int, []),
+    'lf_strerror': (C.c_char_p, [_i32]),
+    'lf_create': (C.c_int, [C.POINTER(_vp), _i32]),
+    'lf_destroy': (C.c_int, [_vp]),
+    'lf_last_cuda_error': (C.c_int, [_vp]),
+    'lf_set_camera': (C.c_int, [_vp, _vp, _vp, _i32, _i32]),
+    'lf_project': (C.c_int, [_vp, _vp, _i64, _f64, _vp, _vp, _vp, _vp, _vp]),
+    'lf_erode_pack': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp]),
+    'lf_unpack_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
+    'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
+    'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
+                                _vp, _vp, _vp, _vp, _vp, _vp]),
+    'lf_mask_gather': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp]),
+    'lf_points_in_box': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _i32, _vp, _vp]),
+    'lf_count_in_boxes': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _vp, _i32, _i32, _vp, _vp]),
+    'lf_car_stats': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
+    'lf_zero_counters': (C.c_int, [_vp, _vp, _i64, _vp]),
+    'lf_depth_maps': (C.c_int, [_vp, _vp, _i64, _f64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    'lf_synth_points': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _u64, _vp, _vp]),
+    'lf_synth_masks': (C.c_int, [_vp, _vp, _i32, _i32, _vp, _f64, _vp, _vp]),
+}
+
+_lib = None
+
+
+class LidarFuseError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen the in-tree library and bind every symbol of the header."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise LidarFuseError('%s is missing: run `python -m lidar_object_detection_b200.build` '
+                             '(there is no CPU fallback)' % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(code, ctx=None):
+    if code == LF_OK:
+        return
+    lib = load()
+    msg = lib.lf_strerror(code).decode()
+    if code == LF_E_CUDA and ctx is not None:
+        msg += ' [cudaError_t %d]' % lib.lf_last_cuda_error(ctx)
+    if code in (LF_E_ARG, LF_E_UNSUPPORTED):
+        raise ValueError('lidarfuse: ' + msg)
+    raise LidarFuseError('lidarfuse: ' + msg)
+
+
+def ptr(t):
+    """Device / host pointer of a torch tensor or numpy array (None -> NULL)."""
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        return t.ctypes.data
+    return t.data_ptr()
+
+
+def prepare_boxes(corners_velo):
+    """corners [n,8,3] f64 (host) -> structured array of lf_box via lf_prepare_boxes."""
+    corners = np.ascontiguousarray(np.asarray(corners_velo, dtype=np.float64).reshape(-1, 8, 3))
+    out = np.zeros(len(corners), dtype=BOX_DTYPE)
+    if len(corners):
+        check(load().lf_prepare_boxes(corners.ctypes.data, len(corners), out.ctypes.data))
+    return out

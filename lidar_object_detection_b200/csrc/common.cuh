@@ -1,0 +1,89 @@
+// Shared declarations for the lidarfuse kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "lidarfuse.h"
+
+// Calibration as the kernels consume it: the three used rows of TrVeloToRect
+// and the 3x3 block of K (cvs_erosion.py:314, 344-345).  Passed by value as a
+// __grid_constant__ kernel parameter (constant bank, no global state).
+struct LfCam {
+    double T[12];   // rows 0..2 of the 4x4 velo->rect transform
+    double K[9];    // K[:3,:3]
+    int W, H, wpr;  // image size, packed words per row
+    int pad;
+};
+
+struct lf_ctx {
+    int device;
+    int has_camera;
+    int last_cuda;
+    int sm_count;
+    LfCam cam;
+};
+
+#define LF_CUDA(ctx, call)                                                  \
+    do {                                                                    \
+        cudaError_t e__ = (call);                                           \
+        if (e__ != cudaSuccess) {                                           \
+            (ctx)->last_cuda = (int)e__;                                    \
+            (void)cudaGetLastError();                                       \
+            return LF_E_CUDA;                                               \
+        }                                                                   \
+    } while (0)
+
+// Streaming 128-bit load: the point cloud is read exactly once.
+__device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+// Projection of one velodyne point, bit-compatible with the reference's numpy:
+//   pointsCam = matmul(TrVeloToRect[f64], [x y z 1]^T[f32->f64])   cvs_erosion.py:342-344
+//   proj = matmul(K[:3,:3], pointsCam); depth = proj.z; depth==0 -> -1e-6
+//   u = round(proj.x/|depth|), v = round(proj.y/|depth|)           (cam2image)
+// OpenBLAS dgemm accumulates k = 0..3 with fused multiply-adds, so
+// the chains below are spelled with __fma_rn / __dmul_rn (never re-associated).
+// uq, vq are the rounded quotients as doubles (may be NaN / huge).
+__device__ __forceinline__ void lf_project_point(const LfCam& c, float x, float y, float z,
+                                                 double& uq, double& vq, double& depth) {
+    const double X = (double)x, Y = (double)y, Z = (double)z;
+    double p[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double a = __dmul_rn(c.T[4 * i + 0], X);
+        a = __fma_rn(c.T[4 * i + 1], Y, a);
+        a = __fma_rn(c.T[4 * i + 2], Z, a);
+        a = __fma_rn(c.T[4 * i + 3], 1.0, a);
+        p[i] = a;
+    }
+    double q[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double a = __dmul_rn(c.K[3 * i + 0], p[0]);
+        a = __fma_rn(c.K[3 * i + 1], p[1], a);
+        a = __fma_rn(c.K[3 * i + 2], p[2], a);
+        q[i] = a;
+    }
+    depth = q[2];
+    if (depth == 0.0) depth = -1e-6;
+    const double ad = fabs(depth);
+    uq = rint(__ddiv_rn(q[0], ad));
+    vq = rint(__ddiv_rn(q[1], ad));
+}
+
+// numpy's float64 -> int64 cast (x86 cvttsd2si): NaN and out-of-range give INT64_MIN.
+__device__ __forceinline__ long long lf_np_f64_to_i64(double r) {
+    if (!(fabs(r) < 9.2233720368547758e18)) return (long long)0x8000000000000000ULL;
+    return __double2ll_rz(r);
+}
+
+// gate of cvs_erosion.py:359 on the rounded quotients
+__device__ __forceinline__ bool lf_gate(const LfCam& c, double uq, double vq, double depth, double max_depth) {
+    return (uq >= 0.0) && (uq < (double)c.W) && (vq >= 0.0) && (vq < (double)c.H) &&
+           (depth > 0.0) && (depth < max_depth);
+}
+
+static inline int lf_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

@@ -1,0 +1,326 @@
+// K3: mask binarisation + binary erosion + bit-packing  (cvs_erosion.py:96-106).
+//
+// One CTA = (mask, strip of rows).  The strip plus its halo (iterations * k/2
+// rows either side) is streamed from HBM exactly once, binarised and packed to
+// one bit per pixel in shared memory (176 B per 1408-px row), eroded there with
+// word-wide shifts and ANDs, and only the packed result goes back out:
+// 1 byte in, 1/8 byte out per pixel.  Algorithmic bytes per mask: H*W in.
+//
+// Fast path (uint8, W % 32 == 0, 16-B aligned): the strip is one contiguous byte
+// run, pulled in by cp.async.bulk (TMA engine, SASS UBLKCP) through a 4-stage
+// mbarrier ring, so ~24-32 KB per CTA are in flight with no register cost.
+// Generic path (any W, uint8 or float32): coalesced loads + __ballot_sync.
+#include "common.cuh"
+
+namespace {
+
+constexpr int ER_THREADS = 256;
+constexpr int ER_STAGES = 4;
+constexpr int ER_CHUNK = 8192;          // bytes per stage: 256 threads x 32 px
+constexpr int ER_MAX_ROWS = 96;         // strip height bound (smem: 2 x (96+2*halo) x wpr x 4)
+
+struct ErodeParams {
+    int H, W, wpr;
+    int rows_per_strip, strips;
+    int k, r, iterations, halo;
+    int buf_words;                       // words per packed smem buffer
+    unsigned short se_rows[LF_MAX_SE];   // bit j of se_rows[i] = SE[i][j]
+};
+
+// ---- mbarrier / bulk-copy PTX (sm_90+; SASS: SYNCS.*, UBLKCP) -----------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// 4 bytes -> 4 bits (bit j = byte j non-zero), returned in bits 28..31.
+__device__ __forceinline__ uint32_t nz_nibble_hi(uint32_t w) {
+    const uint32_t t = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;   // bit 7 of each byte = byte != 0
+    return (t * 0x00204081u) & 0xF0000000u;                                     // 7,15,23,31 -> 28,29,30,31
+}
+__device__ __forceinline__ uint32_t pack32(const uint4 a, const uint4 b) {
+    uint32_t acc = nz_nibble_hi(a.x);
+    acc = (acc >> 4) | nz_nibble_hi(a.y);
+    acc = (acc >> 4) | nz_nibble_hi(a.z);
+    acc = (acc >> 4) | nz_nibble_hi(a.w);
+    acc = (acc >> 4) | nz_nibble_hi(b.x);
+    acc = (acc >> 4) | nz_nibble_hi(b.y);
+    acc = (acc >> 4) | nz_nibble_hi(b.z);
+    acc = (acc >> 4) | nz_nibble_hi(b.w);
+    return acc;
+}
+
+// One erosion pass, smem -> smem, over the loaded rows [ga, gb) of the image.
+// Pixels outside the image are ones (cv2 border value +inf for erosion); rows
+// inside the image but outside the loaded window are treated as ones too --
+// the garbage this creates stays inside the halo.
+__device__ __forceinline__ void erode_pass(const ErodeParams& P, const uint32_t* __restrict__ src,
+                                           uint32_t* __restrict__ dst, int ga, int gb) {
+    const int nrows = gb - ga;
+    const int items = nrows * P.wpr;
+    const uint32_t padmask = (P.W & 31) ? ~((1u << (P.W & 31)) - 1u) : 0u;
+    for (int it = threadIdx.x; it < items; it += ER_THREADS) {
+        const int lr = it / P.wpr, wx = it - lr * P.wpr;
+        uint32_t acc = 0xFFFFFFFFu;
+        for (int i = 0; i < P.k; ++i) {
+            const unsigned bits = P.se_rows[i];
+            if (!bits) continue;
+            const int lr2 = lr + i - P.r;
+            if (lr2 < 0 || lr2 >= nrows) continue;
+            const uint32_t* row = src + lr2 * P.wpr;
+            const uint32_t c = row[wx];
+            const uint32_t l = wx > 0 ? row[wx - 1] : 0xFFFFFFFFu;
+            const uint32_t rr = wx + 1 < P.wpr ? row[wx + 1] : 0xFFFFFFFFu;
+            for (int j = 0; j < P.k; ++j) {
+                if (!((bits >> j) & 1u)) continue;
+                const int dx = j - P.r;
+                uint32_t s;
+                if (dx == 0) s = c;
+                else if (dx > 0) s = __funnelshift_r(c, rr, dx);
+                else s = __funnelshift_l(l, c, -dx);
+                acc &= s;
+            }
+        }
+        if (wx == P.wpr - 1) acc |= padmask;
+        dst[it] = acc;
+    }
+}
+
+__device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* bufA, uint32_t* bufB, int ga,
+                                                int gb, int r0, int r1, uint32_t* __restrict__ out_mask) {
+    uint32_t* cur = bufA;
+    uint32_t* nxt = bufB;
+    for (int itn = 0; itn < P.iterations; ++itn) {
+        __syncthreads();
+        erode_pass(P, cur, nxt, ga, gb);
+        uint32_t* t = cur; cur = nxt; nxt = t;
+    }
+    __syncthreads();
+    const uint32_t keep = (P.W & 31) ? ((1u << (P.W & 31)) - 1u) : 0xFFFFFFFFu;
+    const int items = (r1 - r0) * P.wpr;
+    const uint32_t* srcw = cur + (r0 - ga) * P.wpr;
+    uint32_t* dstw = out_mask + (int64_t)r0 * P.wpr;
+    for (int it = threadIdx.x; it < items; it += ER_THREADS) {
+        uint32_t w = srcw[it];
+        if ((it % P.wpr) == P.wpr - 1) w &= keep;
+        dstw[it] = w;
+    }
+}
+
+__device__ __forceinline__ void strip_rows(const ErodeParams& P, int strip, int& r0, int& r1, int& ga, int& gb) {
+    r0 = strip * P.rows_per_strip;
+    r1 = min(P.H, r0 + P.rows_per_strip);
+    ga = max(0, r0 - P.halo);
+    gb = min(P.H, r1 + P.halo);
+}
+
+// ---------------------------------------------------------------------------
+// fast path
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(ER_THREADS)
+lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __restrict__ masks,
+                     uint32_t* __restrict__ packed) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[ER_STAGES];
+    uint8_t* stage = smem;
+    uint32_t* bufA = (uint32_t*)(smem + ER_STAGES * ER_CHUNK);
+    uint32_t* bufB = bufA + P.buf_words;
+
+    const int64_t mask = blockIdx.x / P.strips;
+    const int strip = blockIdx.x - (int)(mask * P.strips);
+    int r0, r1, ga, gb;
+    strip_rows(P, strip, r0, r1, ga, gb);
+    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W;
+    const int L = (gb - ga) * P.W;                       // bytes in the run (multiple of 32)
+    const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < ER_STAGES; ++s) mbar_init(&full_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < ER_STAGES && i < nch; ++i) {
+            const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - i * ER_CHUNK);
+            mbar_expect_tx(&full_bar[i], bytes);
+            bulk_g2s(stage + i * ER_CHUNK, src + (int64_t)i * ER_CHUNK, bytes, &full_bar[i]);
+        }
+    }
+    for (int i = 0; i < nch; ++i) {
+        const int s = i % ER_STAGES;
+        mbar_wait(&full_bar[s], (uint32_t)((i / ER_STAGES) & 1));
+        const int off = i * ER_CHUNK + 32 * threadIdx.x;
+        if (off < L) {
+            const uint4* q = (const uint4*)(stage + s * ER_CHUNK + 32 * threadIdx.x);
+            bufA[off >> 5] = pack32(q[0], q[1]);
+        }
+        __syncthreads();                                  // stage s fully consumed
+        if (threadIdx.x == 0 && i + ER_STAGES < nch) {
+            const int j = i + ER_STAGES;
+            const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - j * ER_CHUNK);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(&full_bar[s], bytes);
+            bulk_g2s(stage + s * ER_CHUNK, src + (int64_t)j * ER_CHUNK, bytes, &full_bar[s]);
+        }
+    }
+    erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr);
+}
+
+// ---------------------------------------------------------------------------
+// generic path: MODE 0 = uint8 non-zero, 1 = float >= 1.0 (the uint8 truncation
+// of cvs_erosion.py:101 / V2:197), 2 = float > 0.5 (seg_with_pointcloud.py:167)
+// ---------------------------------------------------------------------------
+template <int MODE> struct MaskElem { typedef uint8_t type; };
+template <> struct MaskElem<1> { typedef float type; };
+template <> struct MaskElem<2> { typedef float type; };
+
+template <int MODE>
+__global__ void __launch_bounds__(ER_THREADS)
+lf_erode_generic_kernel(const __grid_constant__ ErodeParams P, const void* __restrict__ masks_v,
+                        uint32_t* __restrict__ packed) {
+    typedef typename MaskElem<MODE>::type T;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint32_t* bufA = (uint32_t*)smem;
+    uint32_t* bufB = bufA + P.buf_words;
+    const T* masks = (const T*)masks_v;
+
+    const int64_t mask = blockIdx.x / P.strips;
+    const int strip = blockIdx.x - (int)(mask * P.strips);
+    int r0, r1, ga, gb;
+    strip_rows(P, strip, r0, r1, ga, gb);
+    const T* src = masks + (mask * P.H + ga) * (int64_t)P.W;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int items = (gb - ga) * P.wpr;
+    for (int it = warp; it < items; it += ER_THREADS / 32) {
+        const int lr = it / P.wpr, wx = it - lr * P.wpr;
+        const int x = 32 * wx + lane;
+        bool bit = true;                                  // beyond W: ones (erosion border)
+        if (x < P.W) {
+            const T val = src[(int64_t)lr * P.W + x];
+            if (MODE == 0) bit = val != 0;
+            else if (MODE == 1) bit = (float)val >= 1.0f;
+            else bit = (float)val > 0.5f;
+        }
+        const uint32_t w = __ballot_sync(0xFFFFFFFFu, bit);
+        if (lane == 0) bufA[it] = w;
+    }
+    erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr);
+}
+
+__global__ void lf_unpack_kernel(const uint32_t* __restrict__ packed, int64_t total_px, int H, int W, int wpr,
+                                 uint8_t* __restrict__ out) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t plane = (int64_t)H * W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_px; i += stride) {
+        const int64_t m = i / plane;
+        const int rem = (int)(i - m * plane);
+        const int y = rem / W, x = rem - y * W;
+        const uint32_t w = __ldg(packed + (m * H + y) * wpr + (x >> 5));
+        out[i] = (uint8_t)((w >> (x & 31)) & 1u);
+    }
+}
+
+}  // namespace
+
+extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
+                             const uint8_t* se, int k, int iterations, uint32_t* packed, void* stream) {
+    if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 2) return LF_E_ARG;
+    if (m > 0 && (!masks || !packed)) return LF_E_ARG;
+    if (iterations > 0 && (!se || k < 1 || (k & 1) == 0)) return LF_E_ARG;
+    if (iterations > 0 && k > LF_MAX_SE) return LF_E_UNSUPPORTED;
+    if (m == 0) return LF_OK;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+
+    ErodeParams P;
+    memset(&P, 0, sizeof(P));
+    P.H = H; P.W = W; P.wpr = (W + 31) / 32;
+    P.iterations = iterations;
+    P.k = iterations > 0 ? k : 1;
+    P.r = P.k / 2;
+    bool any = false;
+    if (iterations > 0) {
+        for (int i = 0; i < k; ++i) {
+            unsigned short bits = 0;
+            for (int j = 0; j < k; ++j)
+                if (se[i * k + j]) bits |= (unsigned short)(1u << j);
+            P.se_rows[i] = bits;
+            any |= bits != 0;
+        }
+        if (!any) return LF_E_ARG;                        // an empty element has no cv2 meaning
+    }
+    P.halo = iterations * P.r;
+
+    // strip plan: enough CTAs to fill the machine several times over, strips <= ER_MAX_ROWS rows
+    int64_t want = ((int64_t)ctx->sm_count * 8 + m - 1) / m;
+    int min_strips = (H + ER_MAX_ROWS - 1) / ER_MAX_ROWS;
+    int max_strips = (H + 15) / 16;
+    int strips = (int)(want < min_strips ? min_strips : (want > max_strips ? max_strips : want));
+    P.rows_per_strip = (H + strips - 1) / strips;
+    P.strips = (H + P.rows_per_strip - 1) / P.rows_per_strip;
+    const int buf_rows = P.rows_per_strip + 2 * P.halo;
+    P.buf_words = buf_rows * P.wpr;
+    if (m * P.strips > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
+
+    const bool fast = mode == 0 && (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
+    size_t smem = (size_t)P.buf_words * 4 * (iterations > 0 ? 2 : 1) + (fast ? ER_STAGES * ER_CHUNK : 0);
+    if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
+    const unsigned grid = (unsigned)(m * P.strips);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (fast) {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)smem));
+        lf_erode_bulk_kernel<<<grid, ER_THREADS, smem, s>>>(P, (const uint8_t*)masks, packed);
+    } else if (mode == 0) {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<0>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lf_erode_generic_kernel<0><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+    } else if (mode == 1) {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<1>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lf_erode_generic_kernel<1><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+    } else {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<2>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lf_erode_generic_kernel<2><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+    }
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}
+
+extern "C" int lf_unpack_masks(lf_ctx* ctx, const uint32_t* packed, int64_t m, int H, int W, uint8_t* out,
+                               void* stream) {
+    if (!ctx || m < 0 || H <= 0 || W <= 0 || (m > 0 && (!packed || !out))) return LF_E_ARG;
+    if (m == 0) return LF_OK;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t total = m * H * W;
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)ctx->sm_count * 32;
+    if (blocks > cap) blocks = cap;
+    lf_unpack_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(packed, total, H, W, (W + 31) / 32, out);
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}

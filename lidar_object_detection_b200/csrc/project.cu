@@ -1,0 +1,141 @@
+// K1 projection + gate (per-point outputs) and K2 depth maps.
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------
+// K1: one thread per point, one coalesced 128-bit load, fp64 chain, up to 28 B out.
+// Algorithmic bytes: 16 in + (8+8+8+4) out per point.  HBM-bound.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+lf_project_kernel(const __grid_constant__ LfCam cam, const float4* __restrict__ pts, int64_t n,
+                  double max_depth, long long* __restrict__ u, long long* __restrict__ v,
+                  double* __restrict__ depth, int32_t* __restrict__ pix) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 p = ld_stream_f4(pts + i);
+        double uq, vq, d;
+        lf_project_point(cam, p.x, p.y, p.z, uq, vq, d);
+        if (u) u[i] = lf_np_f64_to_i64(uq);
+        if (v) v[i] = lf_np_f64_to_i64(vq);
+        if (depth) depth[i] = d;
+        if (pix) pix[i] = lf_gate(cam, uq, vq, d, max_depth) ? (int32_t)vq * cam.W + (int32_t)uq : -1;
+    }
+}
+
+extern "C" int lf_project(lf_ctx* ctx, const float* pts, int64_t n, double max_depth, int64_t* u,
+                          int64_t* v, double* depth, int32_t* pix, void* stream) {
+    if (!ctx || n < 0 || (n > 0 && !pts)) return LF_E_ARG;
+    if (!ctx->has_camera) return LF_E_NOCAMERA;
+    if (((uintptr_t)pts & 15) != 0) return LF_E_ARG;
+    if (n == 0) return LF_OK;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int threads = 256;
+    int64_t blocks = (n + threads - 1) / threads;
+    const int64_t cap = (int64_t)ctx->sm_count * 8 * 4;
+    if (blocks > cap) blocks = cap;
+    lf_project_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(
+        ctx->cam, (const float4*)pts, n, max_depth, (long long*)u, (long long*)v, depth, pix);
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}
+
+// ---------------------------------------------------------------------------
+// K2: depth maps.  Pass 1 scatters one 64-bit key per gated point into an
+// H*W image with a single atomic; pass 2 turns keys into f64 depths and fans
+// them out to the per-car maps through the packed masks.
+//   nearest: key = bits(depth f64)          atomicMin  (depth > 0 => IEEE bits are ordered)
+//   last:    key = (idx+1) << 0 .. see below atomicMax  (highest point index wins, which is
+//            what the index-ordered loop of seg_with_pointcloud.py:162-168 leaves behind)
+// For `last` the winning index is kept and the depth recomputed in pass 2 (the
+// projection is deterministic), so the stored value is the f64 depth, not a
+// float32 copy.  The scratch image is L2-resident (4.2 MB at 1408x376).
+// ---------------------------------------------------------------------------
+__global__ void lf_fill_u64_kernel(unsigned long long* p, int64_t n, unsigned long long val) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = val;
+}
+
+template <int POLICY>
+__global__ void __launch_bounds__(256)
+lf_zscatter_kernel(const __grid_constant__ LfCam cam, const float4* __restrict__ pts, int64_t n,
+                   double max_depth, unsigned long long* __restrict__ img) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 p = ld_stream_f4(pts + i);
+        double uq, vq, d;
+        lf_project_point(cam, p.x, p.y, p.z, uq, vq, d);
+        if (!lf_gate(cam, uq, vq, d, max_depth)) continue;
+        const int px = (int)vq * cam.W + (int)uq;
+        if (POLICY == LF_POLICY_NEAREST)
+            atomicMin(img + px, (unsigned long long)__double_as_longlong(d));
+        else
+            atomicMax(img + px, (unsigned long long)(i + 1));
+    }
+}
+
+template <int POLICY>
+__global__ void __launch_bounds__(256)
+lf_zresolve_kernel(const __grid_constant__ LfCam cam, const float4* __restrict__ pts,
+                   const unsigned long long* __restrict__ img, const uint32_t* __restrict__ packed, int m,
+                   double* __restrict__ full, double* __restrict__ per_car) {
+    const int npix = cam.W * cam.H;
+    const int px = blockIdx.x * blockDim.x + threadIdx.x;
+    if (px >= npix) return;
+    const unsigned long long key = img[px];
+    double d = 0.0;
+    if (POLICY == LF_POLICY_NEAREST) {
+        if (key != ~0ULL) d = __longlong_as_double((long long)key);
+    } else if (key != 0ULL) {
+        const float4 p = pts[key - 1];
+        double uq, vq;
+        lf_project_point(cam, p.x, p.y, p.z, uq, vq, d);
+    }
+    if (full) full[px] = d;
+    if (per_car) {
+        const int y = px / cam.W, x = px - y * cam.W;
+        const int64_t widx = (int64_t)y * cam.wpr + (x >> 5);
+        const int64_t plane = (int64_t)cam.H * cam.wpr;
+        for (int c = 0; c < m; ++c) {
+            const uint32_t w = __ldg(packed + c * plane + widx);
+            per_car[(int64_t)c * npix + px] = ((w >> (x & 31)) & 1u) ? d : 0.0;
+        }
+    }
+}
+
+extern "C" int lf_depth_maps(lf_ctx* ctx, const float* pts, int64_t n, double max_depth, int policy,
+                             const uint32_t* packed, int m, uint64_t* scratch, double* full,
+                             double* per_car, void* stream) {
+    if (!ctx || n < 0 || (n > 0 && !pts) || !scratch || m < 0) return LF_E_ARG;
+    if (policy != LF_POLICY_NEAREST && policy != LF_POLICY_LAST) return LF_E_ARG;
+    if (per_car && m > 0 && !packed) return LF_E_ARG;
+    if (!ctx->has_camera) return LF_E_NOCAMERA;
+    if (((uintptr_t)pts & 15) != 0) return LF_E_ARG;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int npix = ctx->cam.W * ctx->cam.H;
+    const int threads = 256;
+    lf_fill_u64_kernel<<<lf_div_up(npix, threads), threads, 0, s>>>(
+        (unsigned long long*)scratch, npix, policy == LF_POLICY_NEAREST ? ~0ULL : 0ULL);
+    LF_CUDA(ctx, cudaGetLastError());
+    if (n > 0) {
+        int64_t blocks = (n + threads - 1) / threads;
+        const int64_t cap = (int64_t)ctx->sm_count * 8 * 4;
+        if (blocks > cap) blocks = cap;
+        if (policy == LF_POLICY_NEAREST)
+            lf_zscatter_kernel<LF_POLICY_NEAREST><<<(unsigned)blocks, threads, 0, s>>>(
+                ctx->cam, (const float4*)pts, n, max_depth, (unsigned long long*)scratch);
+        else
+            lf_zscatter_kernel<LF_POLICY_LAST><<<(unsigned)blocks, threads, 0, s>>>(
+                ctx->cam, (const float4*)pts, n, max_depth, (unsigned long long*)scratch);
+        LF_CUDA(ctx, cudaGetLastError());
+    }
+    if (full || (per_car && m > 0)) {
+        if (policy == LF_POLICY_NEAREST)
+            lf_zresolve_kernel<LF_POLICY_NEAREST><<<lf_div_up(npix, threads), threads, 0, s>>>(
+                ctx->cam, (const float4*)pts, (const unsigned long long*)scratch, packed, m, full, per_car);
+        else
+            lf_zresolve_kernel<LF_POLICY_LAST><<<lf_div_up(npix, threads), threads, 0, s>>>(
+                ctx->cam, (const float4*)pts, (const unsigned long long*)scratch, packed, m, full, per_car);
+        LF_CUDA(ctx, cudaGetLastError());
+    }
+    return LF_OK;
+}
