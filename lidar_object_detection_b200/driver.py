@@ -1,0 +1,84 @@
+"""The frame loop of cvs_erosion.process_frames (cvs_erosion.py:298-379), batched.
+
+The reference walks the sweeps one by one; here every frame that survives the
+reference's skip rules is packed into one CSR batch and the whole
+sequence goes through the GPU in four launches.  YOLO inference is out of
+scope: ``detections(frame) -> (masks [M,H,W], boxes_xyxy [M,4], conf [M])`` is
+an input (any order; it is sorted by confidence here as cvs_erosion.py:86-94
+does).
+"""
+import os
+
+import numpy as np
+
+from . import kitti360 as K
+from . import lidarfuse as LF
+
+
+def sort_by_confidence(masks, boxes, conf):
+    """cvs_erosion.py:90-94: argsort(confidences)[::-1] applied to boxes, masks, confidences."""
+    order = np.argsort(conf)[::-1]
+    return masks[order], boxes[order], conf[order]
+
+
+class FrameSource:
+    """KITTI-360 layout reader (cvs_erosion.py:18-38, 320-335)."""
+
+    def __init__(self, root, seq=0, bbox_dir=None):
+        self.root = root
+        self.velo = K.Kitti360Viewer3DRaw(seq=seq, mode='velodyne', root=root)
+        self.bbox_dir = bbox_dir or os.path.join(root, 'bboxes_3D_cam0')
+
+    def frames(self):
+        return self.velo.frames()
+
+    def points(self, frame):
+        return self.velo.loadVelodyneData(frame)
+
+    def boxes(self, frame):
+        return K.load_bounding_boxes(os.path.join(self.bbox_dir, 'BBoxes_%d.json' % frame))
+
+
+def collect_frames(source, detections, camera, TrVeloToCam, log=None):
+    """Apply the reference's per-frame skip rules and gather what is left.
+    Returns a list of dicts {frame, points, masks, bboxes}."""
+    kept = []
+    for frame in source.frames():
+        try:
+            points = source.points(frame)
+        except Exception as e:                       # cvs_erosion.py:325-329
+            if log:
+                log('failed to load frame %d: %s' % (frame, e))
+            continue
+        raw = source.boxes(frame)
+        if not raw:                                  # :334-335 (missing / empty JSON)
+            continue
+        boxes = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(raw, camera), TrVeloToCam)
+        det = detections(frame)
+        if det is None or len(det[0]) == 0:          # no masks -> nothing to extract (:361-362)
+            continue
+        masks, b2d, conf = sort_by_confidence(np.asarray(det[0]), np.asarray(det[1]), np.asarray(det[2]))
+        kept.append({'frame': frame, 'points': points, 'masks': masks, 'bboxes': boxes})
+    return kept
+
+
+def process_frames(source, detections, camera, TrVeloToCam, TrVeloToRect, master_csv_path=None,
+                   erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True,
+                   timestamp=None, device=None, log=None):
+    """Whole-sequence equivalent of cvs_erosion.process_frames: returns
+    {frame: car_statistics} and appends the rows to ``master_csv_path``."""
+    kept = collect_frames(source, detections, camera, TrVeloToCam, log)
+    if not kept:
+        return {}
+    pts = np.concatenate([k['points'] for k in kept]).astype(np.float32, copy=False)
+    masks = np.concatenate([k['masks'] for k in kept])
+    stats = LF.process_frames_batched(pts, [len(k['points']) for k in kept], masks,
+                                      [len(k['masks']) for k in kept], [k['bboxes'] for k in kept], camera,
+                                      TrVeloToRect, erosion_kernel_size, erosion_iterations, max_depth,
+                                      min_points, use_oriented, device)
+    out = {}
+    for k, st in zip(kept, stats):
+        out[k['frame']] = st
+        if st and master_csv_path:                   # cvs_erosion.py:375-376
+            LF.append_to_master_csv(st, k['frame'], master_csv_path, timestamp)
+    return out

@@ -1,0 +1,390 @@
+"""CUDA path (through the C ABI) against the oracle and the golden vectors the
+reference's own code produced.  Everything here needs a B200: `-m gpu`."""
+import hashlib
+import os
+
+import cv2
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, SAMPLE, load_boxes, load_frame, standin
+from oracle import mask_provider as MP
+from oracle import pipeline as P
+
+pytestmark = pytest.mark.gpu
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope='module')
+def LF():
+    import torch
+    assert torch.cuda.is_available()
+    from lidar_object_detection_b200 import lidarfuse
+    return lidarfuse
+
+
+@pytest.fixture(scope='module')
+def calib():
+    from lidar_object_detection_b200 import kitti360 as K
+    return K.calibration_chain(SAMPLE)
+
+
+def _frames(golden):
+    return [f for f in golden['_meta']['frames'] if str(f) in golden and 'u_sha' in golden[str(f)]]
+
+
+# ------------------------------------------------------------------ A3 / A4
+
+def test_projection_bit_exact_on_all_sample_frames(LF, calib, golden, golden_arrays, oracle_calib):
+    """u, v, gate: bit-exact with the reference's numpy (sha of the int64 arrays the
+    reference produced); depth: bit-exact with the oracle here, <= 1e-6 relative
+    (north_star tolerance) against the committed reference samples."""
+    cam, TVC, TVR = calib
+    ocam, _, oTVR = oracle_calib
+    assert np.array_equal(TVR, golden_arrays['TrVeloToRect'])
+    stride = golden['_meta']['depth_stride']
+    margin = 1.0
+    for fr in golden['_meta']['frames']:
+        pts = load_frame(fr)
+        u, v, d, pix = LF.project_points(pts, TVR, cam, max_depth=50, return_pix=True)
+        assert u.dtype == np.int64 and v.dtype == np.int64 and d.dtype == np.float64
+        ou, ov, od = P.project_points(pts, oTVR, ocam)
+        assert np.array_equal(u, ou) and np.array_equal(v, ov)
+        assert np.array_equal(d, od), 'depth not bit-identical with numpy/OpenBLAS on this host'
+        valid = P.filter_valid(ou, ov, od, ocam, 50)
+        assert np.array_equal(pix >= 0, valid)
+        assert np.array_equal(pix[valid], (ov[valid] * cam.width + ou[valid]).astype(np.int32))
+        assert np.array_equal(LF.filter_valid(u, v, d, cam, 30), P.filter_valid(ou, ov, od, ocam, 30))
+        g = golden.get(str(fr))
+        if g and 'u_sha' in g:
+            assert sha(u) == g['u_sha'] and sha(v) == g['v_sha']
+            assert sha((pix >= 0).astype(np.uint8)) == g['valid50_sha']
+            np.testing.assert_allclose(d[::stride], golden_arrays['depth_sub_%d' % fr], rtol=1e-6, atol=0)
+            assert np.array_equal(d[::stride], golden_arrays['depth_sub_%d' % fr])
+        # distance of the pre-rounding quotients to a .5 tie
+        homo = pts.astype(np.float64).copy(); homo[:, 3] = 1
+        pc = (oTVR @ homo.T)
+        q = (ocam.K[:3, :3] @ pc[:3])
+        with np.errstate(all='ignore'):
+            fu = q[0] / np.abs(q[2])
+        fu = fu[valid]
+        margin = min(margin, float(np.min(np.abs(np.abs(fu - np.floor(fu)) - 0.5))))
+    assert margin > 1e-10, 'a projected point sits on a rounding tie: pixel parity is ULP-sensitive'
+
+
+def test_projection_special_values(LF, calib, oracle_calib):
+    """NaN / inf / zero-depth / huge inputs follow numpy's int64 cast (SURVEY A.2 notes)."""
+    cam, TVC, TVR = calib
+    ocam, _, oTVR = oracle_calib
+    pts = np.array([[np.nan, 0, 0, 0], [np.inf, 1, 1, 0], [1e30, -1e30, 5, 0], [0, 0, 0, 0],
+                    [1e-30, 1e-30, 1e-30, 1], [10, 0.5, -0.5, 0.2], [-10, 0.5, -0.5, 0.2],
+                    [3e38, 3e38, 3e38, 0]], np.float32)
+    u, v, d = LF.project_points(pts, TVR, cam)
+    with np.errstate(all='ignore'):
+        ou, ov, od = P.project_points(pts, oTVR, ocam)
+    assert np.array_equal(u, ou) and np.array_equal(v, ov)
+    assert np.array_equal(np.isnan(d), np.isnan(od))
+    assert np.array_equal(d[~np.isnan(d)], od[~np.isnan(od)])
+    e = LF.project_points(np.zeros((0, 4), np.float32), TVR, cam)
+    assert all(len(x) == 0 for x in e)
+
+
+# ------------------------------------------------------------------ A5
+
+@pytest.mark.parametrize('W,H', [(1408, 376), (1000, 123), (33, 17), (64, 8)])
+def test_erosion_matches_cv2(LF, W, H):
+    rng = np.random.default_rng(W * 1000 + H)
+    masks = MP.random_blob_masks(rng, 5, H, W, n_blobs=4, max_r=max(4, min(H, W) // 3))
+    masks[3] = 1                                   # all ones: borders must not erode
+    masks[4, :, :] = 0
+    masks[4, H // 4:, W // 5:] = 1                 # touches two borders
+    for shape, cvshape in [(LF.MORPH_ELLIPSE, cv2.MORPH_ELLIPSE), (LF.MORPH_RECT, cv2.MORPH_RECT),
+                           (LF.MORPH_CROSS, cv2.MORPH_CROSS)]:
+        for k in (1, 3, 5, 7, 9, 15):
+            se = cv2.getStructuringElement(cvshape, (k, k))
+            assert np.array_equal(LF.structuring_element(shape, k), se), (shape, k)
+            for it in (1, 2, 3):
+                if k * it > 21:
+                    continue
+                want = np.stack([cv2.erode(m * 255, se, iterations=it) == 255 for m in masks])
+                got = LF.erode_pack(masks, k, it, shape).unpack().cpu().numpy().astype(bool)
+                assert np.array_equal(got, want), (W, H, shape, k, it)
+    # pack only, float modes, the float round trip of cvs_erosion.py:101-103
+    f = masks.astype(np.float32) * rng.choice([1.0, 0.999, 0.6, 0.4], size=masks.shape).astype(np.float32)
+    assert np.array_equal(LF.erode_pack(f, 0, 0).unpack().cpu().numpy() != 0, f.astype(np.uint8) != 0)
+    assert np.array_equal(LF.erode_pack(f, 0, 0, float_threshold='gt_half').unpack().cpu().numpy() != 0, f > 0.5)
+    ref = P.erode_masks(f, 3, 1)
+    got = LF.erode_masks(f, 3, 1)
+    assert got.dtype == np.float32
+    assert np.array_equal(got != 0, ref.astype(np.uint8) != 0)     # what the gather sees (cvs_erosion.py:153-154)
+    assert len(LF.erode_pack(np.zeros((0, H, W), np.uint8))) == 0
+
+
+def test_eroded_sample_masks_match_reference_sha(LF, calib, golden):
+    cam, TVC, TVR = calib
+    for fr in [100, 947, 2098]:
+        g = golden[str(fr)]
+        masks, _, _ = standin(fr, cam)
+        got = LF.erode_masks(masks, 3, 1)
+        assert [sha(np.packbits(m > 0.5)) for m in got] == g['eroded_mask_sha']
+        assert [int((m > 0.5).sum()) for m in got] == g['eroded_mask_area']
+
+
+# ------------------------------------------------------------------ A6 / A8 / A9 function surface
+
+def _norm_stats(stats):
+    return [{k: (float(v) if 'percentage' in k else (list(v) if k == 'color' else int(v))) for k, v in s.items()}
+            for s in stats]
+
+
+@pytest.mark.parametrize('fr', [100, 947, 2098, 2449, 1866, 570])
+def test_function_surface_matches_oracle_and_reference(LF, calib, golden, golden_arrays, fr):
+    """extract_car_points_by_mask / oriented_point_in_bbox / calculate_car_point_statistics
+    called one by one, the way the V1-V3 scripts call them."""
+    cam, TVC, TVR = calib
+    g = golden.get(str(fr), {})
+    pts, raw = load_frame(fr), load_boxes(fr)
+    masks, _, _ = standin(fr, cam)
+    boxes = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(raw, cam), TVC)
+    if 'n_boxes_visible' in g:
+        assert len(boxes) == g['n_boxes_visible']
+        cv = np.array([b['corners_velo'] for b in boxes]).reshape(-1, 8, 3)
+        assert np.array_equal(cv, golden_arrays['corners_velo_%d' % fr])
+    u, v, d = LF.project_points(pts, TVR, cam)
+    valid = LF.filter_valid(u, v, d, cam, 50)
+    pv, uv, vv = pts[valid, :3], u[valid], v[valid]
+    want = P.process_frame(pts, raw, masks, cam, TVC, TVR)
+    em = LF.erode_masks(masks, 3, 1)
+    sets = LF.extract_car_points_by_mask(pv, uv, vv, em, cam)
+    assert len(sets) == len(want['car_point_sets'])
+    for a, b in zip(sets, want['car_point_sets']):
+        assert a.shape == b.shape and a.dtype == b.dtype and np.array_equal(a, b)
+    if 'eroded_car_points_sha' in g:
+        assert [sha(np.asarray(s, np.float32)) for s in sets] == g['eroded_car_points_sha']
+    # containment, box by box (first 12 boxes), oriented and axis-aligned
+    min_margin = np.inf
+    for b in boxes[:12]:
+        c = np.array(b['corners_velo'])
+        assert np.array_equal(LF.oriented_point_in_bbox(pv, c), P.oriented_point_in_bbox(pv, c))
+        assert np.array_equal(LF.point_in_bbox(pv, c), P.point_in_bbox(pv, c))
+        rel = pv - c[0]
+        for j in (1, 3, 4):
+            e = c[j] - c[0]
+            t = np.dot(rel, e) / np.dot(e, e)
+            min_margin = min(min_margin, float(np.min(np.minimum(np.abs(t), np.abs(t - 1)))))
+    assert min_margin > 1e-12, 'a point sits on a box face: counts would be ULP-sensitive (SURVEY 7.3 item 2)'
+    assert LF.oriented_point_in_bbox(np.zeros((0, 3)), np.zeros((8, 3))).shape == (0,)
+    colors = LF.generate_colors(len(masks))
+    for oriented in (True, False):
+        got = LF.calculate_car_point_statistics(sets, boxes, colors, 10, oriented)
+        ref = P.calculate_car_point_statistics(want['car_point_sets'], want['boxes'], colors, 10, oriented)
+        assert _norm_stats(got) == _norm_stats(ref)
+        assert all(type(a['points_inside_bbox']) is type(b['points_inside_bbox']) for a, b in zip(got, ref))
+    if 'stats_erosion3' in g:
+        assert _norm_stats(LF.calculate_car_point_statistics(sets, boxes, colors)) == g['stats_erosion3']
+        assert np.array_equal(LF.inside_count_matrix(sets, boxes), golden_arrays['inside_erosion3_%d' % fr])
+    if 'v1_matched_counts' in g:
+        raw_sets = LF.extract_car_points_by_mask(pv, uv, vv, masks, cam)
+        assert [len(s) for s in raw_sets] == g['raw_total_points']
+        pairs = LF.match_car_points_to_bboxes(raw_sets, boxes, colors)
+        assert [int(p[2]) for p in pairs] == g['v1_matched_counts']
+        assert np.array_equal(np.array([p[0] for p in pairs]).reshape(-1, 8, 3),
+                              golden_arrays['v1_matched_corners_%d' % fr])
+    assert LF.calculate_car_point_statistics(sets, [], colors) == []
+    assert LF.calculate_car_point_statistics([], boxes, colors) == []
+
+
+# ------------------------------------------------------------------ fused batch path
+
+def _batch_inputs(frames, cam, TVC, LF):
+    pts, masks, boxes, raws = [], [], [], []
+    for fr in frames:
+        raw = load_boxes(fr)
+        pts.append(load_frame(fr))
+        masks.append(standin(fr, cam)[0])
+        raws.append(raw)
+        boxes.append(LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(raw, cam), TVC))
+    return pts, masks, boxes, raws
+
+
+@pytest.mark.parametrize('variant', ['erosion3', 'noerosion', 'aabb', 'erosion5x2_30m'])
+def test_fused_batch_matches_oracle_on_all_sample_frames(LF, calib, golden, variant):
+    """All 20 sample frames (ragged N, M = 0..16, B = 0..300) in ONE batch:
+    every counter bit-exact with the oracle, statistics equal to the reference's."""
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames']
+    pts, masks, boxes, raws = _batch_inputs(frames, cam, TVC, LF)
+    kw = {'erosion3': dict(erosion_kernel_size=3, erosion_iterations=1, max_depth=50, use_oriented=True),
+          'noerosion': dict(erosion_kernel_size=0, erosion_iterations=1, max_depth=50, use_oriented=True),
+          'aabb': dict(erosion_kernel_size=0, erosion_iterations=1, max_depth=50, use_oriented=False),
+          'erosion5x2_30m': dict(erosion_kernel_size=5, erosion_iterations=2, max_depth=30, use_oriented=True)}[variant]
+    corners = np.concatenate([np.array([b['corners_velo'] for b in bs], dtype=np.float64).reshape(-1, 8, 3)
+                              for bs in boxes])
+    batch = LF.FrameBatch(np.concatenate(pts), [len(p) for p in pts], np.concatenate(masks),
+                          [len(m) for m in masks], corners, [len(b) for b in boxes], cam, TVR, want_car_bits=True)
+    batch.run(min_points=10, **kw)
+    res = batch.results()
+    bits = batch.car_bits.cpu().numpy()
+    agg = np.zeros(8, np.int64)
+    for i, fr in enumerate(frames):
+        want = P.process_frame(pts[i], raws[i], masks[i], cam, TVC, TVR, min_points=10, **kw)
+        m0, m1 = batch.h_mask_off[i], batch.h_mask_off[i + 1]
+        b0, b1 = batch.h_box_off[i], batch.h_box_off[i + 1]
+        assert res['n_valid'][i] == want['valid'].sum()
+        assert np.array_equal(res['total'][m0:m1], want['total'])
+        assert np.array_equal(res['n_in_box'][b0:b1], want['n_in_box'])
+        got_inside = res['inside'][batch.h_cnt_off[i]:batch.h_cnt_off[i + 1]].reshape(m1 - m0, b1 - b0)
+        assert np.array_equal(got_inside, want['inside'])
+        fb = bits[batch.h_pt_off[i]:batch.h_pt_off[i + 1]]
+        member = np.zeros((m1 - m0, len(pts[i])), bool)
+        if m1 > m0:
+            member[:, want['valid']] = want['member']
+        for c in range(m1 - m0):
+            assert np.array_equal(((fb >> c) & 1).astype(bool), member[c])
+        stats = batch.frame_stats(res, i) if res['n_valid'][i] else []
+        assert _norm_stats(stats) == _norm_stats(want['stats'])
+        g = golden.get(str(fr), {})
+        key = {'erosion3': 'stats_erosion3', 'noerosion': 'stats_noerosion', 'aabb': 'stats_noerosion_aabb'}.get(variant)
+        if key and key in g:
+            assert _norm_stats(stats) == g[key]
+        # K6 outputs and aggregates
+        for s in want['stats']:
+            c = s['car_id']
+            if s['matched_bbox_id'] >= 0:
+                assert res['best_idx'][m0 + c] == s['matched_bbox_id']
+                assert res['best_cnt'][m0 + c] == s['points_inside_bbox']
+        if want['stats']:
+            matched = [s for s in want['stats'] if s['matched_bbox_id'] >= 0]
+            agg += np.array([1, len(want['stats']), len(matched), sum(s['total_points'] for s in matched),
+                             sum(s['points_inside_bbox'] for s in matched),
+                             sum(s['total_points'] for s in want['stats']), 0, 0])
+    assert np.array_equal(res['agg'], agg)
+    # running the same batch again gives the same answer (counters are re-zeroed)
+    batch.run(min_points=10, **kw)
+    res2 = batch.results()
+    for k in res:
+        assert np.array_equal(res[k], res2[k]), k
+
+
+# ------------------------------------------------------------------ A11 CSV, end to end
+
+class _NpzSource:
+    """The committed sample (sweeps stored as npz) behind the driver's FrameSource interface."""
+
+    def __init__(self, frames):
+        self._frames = frames
+
+    def frames(self):
+        return list(self._frames)
+
+    def points(self, frame):
+        return load_frame(frame)
+
+    def boxes(self, frame):
+        return load_boxes(frame)
+
+
+def test_master_csv_is_byte_identical_with_the_reference(LF, calib, golden, tmp_path):
+    """cfg2: all sample frames -> master_car_statistics.csv, compared byte for byte
+    with the file the unmodified cvs_erosion.process_frames wrote (timestamp frozen)."""
+    from lidar_object_detection_b200 import driver
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames']
+
+    def detections(frame):
+        m, b, c = standin(frame, cam)
+        if len(c) == 0:
+            return None
+        perm = np.random.default_rng(frame).permutation(len(c))      # "YOLO order", as gen_golden fed it
+        return m[perm], b[perm], c[perm]
+
+    path = str(tmp_path / 'results' / 'master_car_statistics.csv')
+    out = driver.process_frames(_NpzSource(frames), detections, cam, TVC, TVR, master_csv_path=path,
+                                timestamp=golden['_meta']['frozen_timestamp'])
+    want = open(os.path.join(GOLDEN, 'master_car_statistics_erosion3.csv')).read()
+    assert open(path).read() == want
+    assert 2717 not in out                                             # missing box file -> frame skipped
+    agg = LF.analyze_master_csv(path)
+    ref = P.analyze_master_csv(path)
+    assert agg['frames'] == ref['frames'] and agg['detections'] == ref['detections']
+    assert agg['matched'] == ref['matched'] and agg['unmatched'] == ref['unmatched']
+    for k in ('matching_rate', 'avg_points_per_car', 'avg_inside_pct', 'min_inside_pct', 'max_inside_pct'):
+        assert abs(agg[k] - ref[k]) <= 1e-9 * max(1.0, abs(ref[k]))
+
+
+# ------------------------------------------------------------------ A10 depth maps
+
+def test_depth_maps_match_reference_and_oracle(LF, calib, golden, golden_arrays):
+    cam, TVC, TVR = calib
+    checked = 0
+    for fr in [100, 250, 1866]:
+        g = golden[str(fr)]
+        masks, _, conf = standin(fr, cam)
+        perm = np.random.default_rng(fr).permutation(len(conf))
+        pts = load_frame(fr)
+        maps, full = LF.per_car_depth_maps(pts, TVR, masks[perm], cam, max_depth=30, policy='last', full=True)
+        u, v, d = P.project_points(pts, TVR, cam)
+        want = P.per_car_depth_maps(u, v, d, masks[perm], cam, max_depth=30, policy='last')
+        for (car, dm), (wcar, wdm) in zip(maps, want):
+            assert car == wcar and dm.dtype == np.float64 and np.array_equal(dm, wdm)
+            nz = np.flatnonzero(dm)
+            if car in g.get('depthmap_cars', []):
+                assert np.array_equal(nz.astype(np.int32), golden_arrays['depthmap_pix_%d_%d' % (fr, car)])
+                got, ref = dm.reshape(-1)[nz], golden_arrays['depthmap_val_%d_%d' % (fr, car)]
+                np.testing.assert_allclose(got, ref, rtol=1e-6, atol=0)
+                assert np.array_equal(got, ref)
+                checked += 1
+            else:
+                assert len(nz) == 0
+        valid = P.filter_valid(u, v, d, cam, 30)
+        ref_full = np.zeros((cam.height, cam.width))
+        ref_full[v[valid], u[valid]] = d[valid]
+        assert np.array_equal(full, ref_full)
+        near = LF.per_car_depth_maps(pts, TVR, masks[perm], cam, max_depth=30, policy='nearest')
+        wnear = P.per_car_depth_maps(u, v, d, masks[perm], cam, max_depth=30, policy='nearest')
+        for (car, dm), (wcar, wdm) in zip(near, wnear):
+            assert np.array_equal(dm, wdm)
+            assert np.all(dm[dm > 0] <= maps[car - 1][1][dm > 0])     # nearest <= last, same support
+            assert np.array_equal(dm > 0, maps[car - 1][1] > 0)
+    assert checked >= 5
+    assert LF.per_car_depth_maps(load_frame(100), TVR, np.zeros((0, cam.height, cam.width), np.float32), cam) == []
+
+
+# ------------------------------------------------------------------ synthetic batches (cfg3-shaped)
+
+def test_synthetic_batch_matches_oracle_and_invariants(LF, calib):
+    """A small cfg3-shaped batch generated on the device: a few frames against the
+    oracle (all counters bit-exact), the rest through size-independent properties."""
+    from lidar_object_detection_b200 import synthetic as S
+    cam, TVC, TVR = calib
+    sb = S.SyntheticBatch(24, cam, TVC, TVR, ncars=16, seed=1234)
+    sb.batch.run(3, 1, 50, 10, True)
+    res = sb.batch.results()
+    b = sb.batch
+    for f in (0, 7, 23):
+        pts, masks, boxes = sb.host_frame(f)
+        want = P.process_frame(pts, boxes, masks.astype(np.float32), cam, TVC, TVR)
+        assert len(want['boxes']) == sb.n_boxes[f]
+        assert res['n_valid'][f] == want['valid'].sum()
+        assert np.array_equal(res['total'][b.h_mask_off[f]:b.h_mask_off[f + 1]], want['total'])
+        assert np.array_equal(res['n_in_box'][b.h_box_off[f]:b.h_box_off[f + 1]], want['n_in_box'])
+        got = res['inside'][b.h_cnt_off[f]:b.h_cnt_off[f + 1]].reshape(16, sb.n_boxes[f])
+        assert np.array_equal(got, want['inside'])
+        assert _norm_stats(b.frame_stats(res, f)) == _norm_stats(want['stats'])
+    tot = res['total'].reshape(24, 16)
+    assert np.all(res['n_valid'] > 0.05 * sb.n) and np.all(res['n_valid'] < 0.5 * sb.n)
+    assert np.all(tot <= res['n_valid'][:, None])
+    for f in range(24):
+        ins = res['inside'][b.h_cnt_off[f]:b.h_cnt_off[f + 1]].reshape(16, sb.n_boxes[f])
+        assert np.all(ins <= tot[f][:, None])
+        assert np.all(ins <= res['n_in_box'][b.h_box_off[f]:b.h_box_off[f + 1]][None, :])
+    # erosion is anti-extensive: totals can only shrink (SURVEY Appendix B observation)
+    sb.batch.run(0, 0, 50, 10, True)
+    res0 = sb.batch.results()
+    assert np.all(res0['total'] >= res['total']) and np.any(res0['total'] > res['total'])
+    sb.batch.run(7, 1, 50, 10, True)
+    assert np.all(sb.batch.results()['total'] <= res['total'])
+    assert np.array_equal(res0['n_valid'], res['n_valid']) and np.array_equal(res0['n_in_box'], res['n_in_box'])
