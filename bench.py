@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""points/s through project + mask (erode + gather) + bbox evaluation on synthetic
+HDL-64-shaped frames (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A step = one pass of the hot path over one batch per GPU: counter memset,
+erode+pack of the uint8 masks, the fused point pass and the per-car decision
+(4 launches), plus -- at N > 1 -- the single all-reduce of the per-car table.
+N = 1 runs BASELINE configs[2]: 1024 frames x 131072 points x 16 masks
+(1408x376) x 16 boxes, all resident in HBM (10.8 GB >> 126 MB L2, so no L2
+flush is needed between steps).  N > 1 is weak scaling: every rank holds its
+own 1024-frame shard (cfg4's frames-per-chunk).
+
+--impl reference times the reference's CPU path (the numpy/OpenCV oracle port
+of cvs_erosion.py's per-frame body) on the host cores, on the same kind of
+frames, and prints the same JSON line.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CALIB_ROOT = os.path.join(ROOT, 'tests', 'golden', 'kitti360_sample')
+METRIC = 'points/sec (project+mask+bbox eval)'
+FRAMES, NCARS, RINGS, AZ = 1024, 16, 64, 2048
+W_IMG, H_IMG = 1408, 376
+SEED = 0x5EED0000
+
+
+def algorithmic_bytes_per_frame(n_points, n_masks, n_boxes):
+    """compulsory reads + writes, each counted once."""
+    return 16 * n_points + n_masks * H_IMG * W_IMG + 192 * n_boxes + 8 * n_masks * (n_boxes + 3)
+
+
+# --------------------------------------------------------------------------- CPU arm
+
+def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue):
+    """One host process: generate ``nframes`` synthetic frames with numpy (untimed),
+    then run ``warm`` + ``steps`` frames of the oracle's per-frame pipeline
+    (cycling over its frames); only the ``steps`` part is timed."""
+    os.environ['OPENBLAS_NUM_THREADS'] = '1'
+    os.environ['OMP_NUM_THREADS'] = '1'
+    import numpy as np
+    import cv2
+    cv2.setNumThreads(1)
+    from lidar_object_detection_b200 import kitti360 as K, synthetic as S
+    from oracle import pipeline as P
+    cam, TVC, TVR = K.calibration_chain(CALIB_ROOT)
+    cars = S.sort_cars_by_image_area(S.make_cars(nframes, NCARS, seed + 7919 * rank), cam, TVR)
+    boxes = S.reference_boxes(cars, cam, TVC)
+    frames = []
+    for f in range(nframes):
+        pts = S.numpy_frame(cars[f], seed + 7919 * rank + f, RINGS, AZ)
+        masks = S.numpy_masks(cars[f], cam, TVR).astype(np.float32)     # YOLO hands float32 masks over
+        raw = [{'corners_cam0': b['corners_cam0']} for b in boxes[f]]
+        frames.append((pts, raw, masks))
+    rows = 0
+    for i in range(warm):
+        P.process_frame(*frames[i % nframes], cam, TVC, TVR)
+    barrier.wait()
+    t0 = time.time()
+    for i in range(steps):
+        out = P.process_frame(*frames[i % nframes], cam, TVC, TVR)
+        rows += len(out['stats'])
+    t1 = time.time()
+    queue.put((rank, t0, t1, steps * len(frames[0][0]), rows))
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_reference_throughput(steps, warm=1, distinct_frames=2, workers=None):
+    """points/s of the CPU path, one process per host core, each timing ``steps``
+    frames (a bounded sample of the workload)."""
+    import multiprocessing as mp
+    workers = workers or host_cores()
+    ctx = mp.get_context('spawn')
+    barrier, queue = ctx.Barrier(workers), ctx.Queue()
+    procs = [ctx.Process(target=_cpu_worker, args=(r, distinct_frames, warm, steps, SEED, barrier, queue))
+             for r in range(workers)]
+    for p in procs:
+        p.start()
+    res = [queue.get() for _ in procs]
+    for p in procs:
+        p.join()
+    t0 = min(r[1] for r in res)
+    t1 = max(r[2] for r in res)
+    points = sum(r[3] for r in res)
+    return {'value': points / (t1 - t0), 'seconds': t1 - t0, 'points': points, 'cores': workers,
+            'frames': steps * workers, 'rows': sum(r[4] for r in res)}
+
+
+# --------------------------------------------------------------------------- clocks
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t_begin, t_end):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [l for (t, l) in self.lines if t_begin - 0.05 <= t <= t_end + 0.15] or [l for (_, l) in self.lines]
+        mhz, mx, reasons = [], None, set()
+        for l in rows:
+            p = [x.strip() for x in l.split(',')]
+            try:
+                mhz.append(float(p[0])); mx = float(p[1])
+            except Exception:
+                continue
+            for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), p[2:6]):
+                if val.lower().startswith('active'):
+                    reasons.add(name)
+        return {'sm_mhz': statistics.median(mhz) if mhz else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(mhz)}
+
+
+# --------------------------------------------------------------------------- GPU arm
+
+def run_gpu(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    frames = args.frames
+
+    # CPU baseline first (rank 0, N = 1 only): spawned host processes, GPU idle meanwhile
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        c = cpu_reference_throughput(steps=args.cpu_frames, warm=1)
+        cpu = {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': 'port',
+               'sample': '%d synthetic frames (%d per host process, %d processes, OPENBLAS/cv2 threads = 1), '
+                         '%.1f s wall' % (c['frames'], args.cpu_frames, c['cores'], c['seconds'])}
+
+    from lidar_object_detection_b200 import distributed as D, kitti360 as K, synthetic as S
+    cam, TVC, TVR = K.calibration_chain(CALIB_ROOT)
+    sb = S.SyntheticBatch(frames, cam, TVC, TVR, ncars=NCARS, seed=SEED, rings=RINGS, azimuths=AZ, device=local,
+                          first_frame=rank * frames)
+    batch = sb.batch
+    n_pts = sb.n
+    exch = None
+    if world > 1:
+        exch = D.CounterExchange(world * frames, NCARS, rank, world, dev)
+        exch.bind(batch.h_mask_off, sb.n_boxes)
+
+    def step(mark=None):
+        batch.run(3, 1, 50, 10, True, mark=mark)
+        if exch is not None:
+            exch.exchange_batch(batch)
+
+    stream = torch.cuda.current_stream(dev)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync_all()
+
+    # parity spot check against the oracle (checker only): two frames of this very batch
+    parity_frames = 0
+    if rank == 0 and not args.no_parity:
+        from oracle import pipeline as P
+        res = batch.results()
+        for f in (0, frames - 1):
+            pts, masks, boxes = sb.host_frame(f)
+            want = P.process_frame(pts, boxes, masks.astype(np.float32), cam, TVC, TVR)
+            got_t = res['total'][batch.h_mask_off[f]:batch.h_mask_off[f + 1]]
+            got_i = res['inside'][batch.h_cnt_off[f]:batch.h_cnt_off[f + 1]].reshape(want['inside'].shape)
+            if not (np.array_equal(got_t, want['total']) and np.array_equal(got_i, want['inside'])
+                    and res['n_valid'][f] == want['valid'].sum()):
+                raise SystemExit('PARITY FAILURE on synthetic frame %d: refusing to report a number' % f)
+            parity_frames += 1
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    K_steps = args.steps
+    marks = []
+
+    def make_mark(lst):
+        def mark(name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            lst.append((name, e))
+        return mark
+
+    sync_all()
+    t_begin = time.time()
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(K_steps):
+        lst = []
+        step(make_mark(lst))
+        marks.append(lst)
+    ev1.record(stream)
+    sync_all()
+    t_end = time.time()
+    ms_total = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / K_steps
+    value = world * frames * n_pts / (ms_step * 1e-3)
+
+    # per-kernel device time from the marks (same stream, same timed region)
+    kern = {}
+    for lst in marks:
+        d = dict(lst)
+        for a, b in (('zero', 'erode_pack'), ('erode_pack', 'fuse'), ('fuse', 'car_stats')):
+            kern.setdefault(b, []).append(d[a].elapsed_time(d[b]))
+    kern_ms = {k: sum(v) / len(v) for k, v in kern.items()}
+
+    # ---- end to end: host buffers in, host counters out, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        h_pts = torch.empty(batch.points.shape, dtype=batch.points.dtype, pin_memory=True)
+        h_masks = torch.empty(batch.masks.shape, dtype=batch.masks.dtype, pin_memory=True)
+        h_out = torch.empty(batch.counters.shape, dtype=batch.counters.dtype, pin_memory=True)
+        h_pts.copy_(batch.points)
+        h_masks.copy_(batch.masks)
+        torch.cuda.synchronize(dev)
+
+        def e2e_step():
+            batch.points.copy_(h_pts, non_blocking=True)
+            batch.masks.copy_(h_masks, non_blocking=True)
+            step()
+            h_out.copy_(batch.counters, non_blocking=True)
+            stream.synchronize()
+
+        e2e_step()
+        sync_all()
+        n_e2e = max(1, min(args.e2e_steps, K_steps))
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        sync_all()
+        dt = (time.perf_counter() - t0) / n_e2e
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {'value': world * frames * n_pts / dt, 'unit': 'points/s',
+               'h2d_bytes_per_step': int(h_pts.numel() * 4 + h_masks.numel()),
+               'd2h_bytes_per_step': int(h_out.numel() * 4), 'steps': n_e2e, 'ms_per_step': dt * 1e3,
+               'api': 'lidarfuse.FrameBatch.run (pinned host points + uint8 masks -> counters on host)'}
+        t_end = time.time()
+
+    clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
+    if rank == 0:
+        peaks, peak_src = None, 'fallback'
+        try:
+            with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as fh:
+                peaks = json.load(fh)
+            peak, peak_src = float(peaks['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+        except Exception:
+            peak = 6650.0
+        mask_bytes = frames * NCARS * H_IMG * W_IMG                       # algorithmic bytes of the erode launch
+        ach = mask_bytes / (kern_ms['erode_pack'] * 1e-3) / 1e9
+        step_bytes = sum(algorithmic_bytes_per_frame(n_pts, NCARS, b) for b in sb.n_boxes)
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as fh:
+                traffic = json.load(fh).get('lf_erode_bulk_kernel_bytes_per_launch')
+        except Exception:
+            pass
+        line = {
+            'metric': METRIC, 'value': value, 'unit': 'points/s', 'n_gpus': world, 'steps': K_steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f64 projection/containment, u32 bit-masks, i32 counters',
+            'data': 'synthetic',
+            'config': {'workload': 'cfg3: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes per GPU, '
+                                   '3x3 ellipse erosion, 50 m gate' % (frames, n_pts, NCARS, W_IMG, H_IMG, NCARS),
+                       'frames_per_gpu': frames, 'points_per_frame': n_pts, 'masks_per_frame': NCARS,
+                       'l2_policy': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush' % (step_bytes / 1e9),
+                       'parallelism': 'frames sharded, dp%d' % world},
+            'gpu_launches': int(batch.launches_per_run - 1) * K_steps,
+            'kernel_ms': kern_ms,
+            'step_hbm': {'algorithmic_bytes_per_step': step_bytes, 'achieved_gbs': step_bytes / (ms_step * 1e-3) / 1e9,
+                         'frac_of_measured_peak': step_bytes / (ms_step * 1e-3) / 1e9 / peak,
+                         'frac_of_8000_nominal': step_bytes / (ms_step * 1e-3) / 1e9 / 8000.0},
+            'roofline': {'kernel': 'lf_erode_bulk_kernel', 'bound': 'hbm', 'achieved': ach, 'peak': peak,
+                         'unit': 'GB/s', 'frac': ach / peak, 'traffic': traffic, 'peak_source': peak_src,
+                         'algorithmic_bytes_per_launch': mask_bytes},
+            'e2e': e2e, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------- reference arm
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', 0))
+    if rank != 0:
+        return
+    steps = min(args.steps, 60)              # ~0.4 s of CPU work per step and process
+    c = cpu_reference_throughput(steps=steps, warm=min(max(args.warmup, 1), 3))
+    n_pts = RINGS * AZ
+    line = {'impl': 'reference', 'metric': METRIC, 'value': c['value'], 'unit': 'points/s',
+            'n_gpus': int(os.environ.get('WORLD_SIZE', args.gpus)), 'steps': steps, 'warmup': min(max(args.warmup, 1), 3),
+            'ms_per_step': c['seconds'] / steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f64 (numpy) + u8 (cv2)', 'data': 'synthetic',
+            'config': {'workload': 'cfg3-shaped frames: %d pts x %d masks (%dx%d) x <=%d boxes; one step = one '
+                                   'frame per host process' % (n_pts, NCARS, W_IMG, H_IMG, NCARS),
+                       'points_per_frame': n_pts, 'masks_per_frame': NCARS},
+            'cpu_baseline': {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': 'port',
+                             'sample': '%d frames over %d host processes, %.1f s' % (c['frames'], c['cores'], c['seconds'])},
+            'e2e': {'value': c['value'], 'unit': 'points/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--frames', type=int, default=FRAMES, help='frames per GPU (default: cfg3, 1024)')
+    ap.add_argument('--cpu-frames', type=int, default=2, help='frames each host process times for cpu_baseline')
+    ap.add_argument('--e2e-steps', type=int, default=3)
+    ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-parity', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,109 @@
+"""Frame sharding over one process per GPU.
+
+Frames are independent, so the data path has no collective: rank r of G owns
+the contiguous frame block [r*F/G, (r+1)*F/G).  Only the small per-car counter
+tables are combined, with ONE ``all_reduce(SUM)`` per batch over a zero-filled
+integer table in which each rank writes only its own rows (a sum over disjoint
+supports is an all-gather that tolerates uneven shards), plus the int64
+``analyze_master_csv`` aggregates.  Backend: NCCL over NVLink on GPUs, gloo in
+the CPU tests.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+TABLE_COLS = 4          # total_points, best_count, best_idx + 1, frame has boxes (a CSV row exists)
+
+
+def shard_range(n_frames, rank, world):
+    """Contiguous block of frames owned by ``rank``."""
+    lo = (n_frames * rank) // world
+    hi = (n_frames * (rank + 1)) // world
+    return lo, hi
+
+
+def local_table(total, best_cnt, best_idx, box_counts, mask_off, max_cars):
+    """Per-car table of the local frames: int32 [F_local, max_cars, 4] (torch ops
+    on whatever device the counters live on)."""
+    F = len(mask_off) - 1
+    dev = total.device
+    table = torch.zeros((F, max_cars, TABLE_COLS), dtype=torch.int32, device=dev)
+    if total.numel() == 0:
+        return table
+    mo = torch.as_tensor(mask_off, device=dev, dtype=torch.int64)
+    counts = mo[1:] - mo[:-1]
+    frame_of = torch.repeat_interleave(torch.arange(F, device=dev), counts)
+    car_of = torch.arange(total.numel(), device=dev) - mo[frame_of]
+    table[frame_of, car_of, 0] = total.to(torch.int32)
+    table[frame_of, car_of, 1] = best_cnt.to(torch.int32)
+    table[frame_of, car_of, 2] = best_idx.to(torch.int32) + 1
+    has_boxes = (torch.as_tensor(box_counts, device=dev) > 0).to(torch.int32)
+    table[frame_of, car_of, 3] = has_boxes[frame_of]
+    return table
+
+
+class CounterExchange:
+    """Pre-allocated global table + aggregate vector and the single all-reduce."""
+
+    def __init__(self, n_frames_global, max_cars, rank, world, device):
+        self.rank, self.world = rank, world
+        self.lo, self.hi = shard_range(n_frames_global, rank, world)
+        self.max_cars = max_cars
+        n = n_frames_global * max_cars * TABLE_COLS
+        # one flat int64 buffer: [table as int64 | agg(8)] -> a single collective
+        self.flat = torch.zeros(n + 8, dtype=torch.int64, device=device)
+        self.table = self.flat[:n].view(n_frames_global, max_cars, TABLE_COLS)
+        self.agg = self.flat[n:]
+
+    def bind(self, mask_off, box_counts):
+        """Pre-compute where the local cars land in the global table (once per batch layout)."""
+        dev = self.flat.device
+        mo = torch.as_tensor(np.asarray(mask_off), device=dev, dtype=torch.int64)
+        F = mo.numel() - 1
+        counts = mo[1:] - mo[:-1]
+        frame_of = torch.repeat_interleave(torch.arange(F, device=dev), counts)
+        car_of = torch.arange(int(mo[-1]), device=dev) - mo[frame_of]
+        self._dest = ((self.lo + frame_of) * self.max_cars + car_of) * TABLE_COLS
+        self._has_boxes = (torch.as_tensor(np.asarray(box_counts), device=dev) > 0).to(torch.int64)[frame_of]
+        self._n_cars = int(mo[-1])
+
+    def exchange_batch(self, batch):
+        """Scatter the local counters of a lidarfuse.FrameBatch into the table and
+        all-reduce it: five small device ops and ONE collective per batch."""
+        n = self._n_cars
+        self.flat.zero_()
+        self.flat[self._dest] = batch.total[:n].to(torch.int64)
+        self.flat[self._dest + 1] = batch.best_cnt[:n].to(torch.int64)
+        self.flat[self._dest + 2] = batch.best_idx[:n].to(torch.int64) + 1
+        self.flat[self._dest + 3] = self._has_boxes
+        self.agg.copy_(batch.agg)
+        if self.world > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+        return self.table, self.agg
+
+    def exchange(self, table_local, agg_local):
+        """Fill this rank's rows, sum across ranks (async on the current stream
+        for NCCL).  Afterwards every rank holds the full table."""
+        self.flat.zero_()
+        self.table[self.lo:self.hi] = table_local.to(torch.int64)
+        self.agg.copy_(agg_local.to(torch.int64))
+        if self.world > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+        return self.table, self.agg
+
+
+def rows_from_table(table, frame_ids, min_points=10):
+    """Global per-car rows (frame, car_id, matched_bbox_id, total, inside, outside)
+    from the reduced table -- what rank 0 turns into CSV lines."""
+    t = table.cpu().numpy() if isinstance(table, torch.Tensor) else np.asarray(table)
+    rows = []
+    for fi, frame in enumerate(frame_ids):
+        for c in range(t.shape[1]):
+            total, best, idx1 = int(t[fi, c, 0]), int(t[fi, c, 1]), int(t[fi, c, 2])
+            if total == 0 or t[fi, c, 3] == 0:          # no points, or no boxes (cvs_erosion.py:169-170, 178-179)
+                continue
+            if idx1 > 0 and best >= min_points:
+                rows.append((frame, c, idx1 - 1, total, best, total - best))
+            else:
+                rows.append((frame, c, -1, total, 0, total))
+    return rows

@@ -536,14 +536,17 @@ class FrameBatch:
         self.launches_per_run = 0
 
     def run(self, erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True,
-            shape=MORPH_ELLIPSE, float_threshold='ge_one'):
+            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None):
         """memset + erode/pack + fused point pass + per-car decision, all async
         on the current stream.  Returns nothing; read ``results()``."""
         ctx, lib = self.ctx, self.ctx.lib
         ctx.set_camera(self.TrVeloToRect, self.camera.K, self.camera.width, self.camera.height)
         st = ctx.stream
         launches = 1
+        mark = mark or (lambda name: None)
+        mark('begin')
         check(lib.lf_zero_counters(ctx.h, ptr(self.counters), self.counters.numel() * 4, st), ctx.h)
+        mark('zero')
         if not isinstance(self.masks, PackedMasks) and self.masks is not None and len(self.masks):
             iters = int(erosion_iterations) if erosion_kernel_size else 0
             se = structuring_element(shape, erosion_kernel_size) if iters else None
@@ -553,16 +556,19 @@ class FrameBatch:
                                     se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
                                     ptr(self.packed.words), st), ctx.h)
             launches += 1
+        mark('erode_pack')
         if self.F and self.max_n:
             check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words),
                                     ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
                                     self.F, self.max_n, self.max_m, self.max_b, float(max_depth),
                                     int(use_oriented), ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
                                     ptr(self.n_valid), ptr(self.car_bits), st), ctx.h)
+            mark('fuse')
             check(lib.lf_car_stats(ctx.h, ptr(self.total), ptr(self.inside), ptr(self.mask_off),
                                    ptr(self.box_off), ptr(self.cnt_off), self.F, int(min_points),
                                    ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), st), ctx.h)
             launches += 2
+        mark('car_stats')
         self.launches_per_run = launches
 
     def results(self):

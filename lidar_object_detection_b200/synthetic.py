@@ -119,9 +119,10 @@ def numpy_frame(cars_f, seed, rings=RINGS, azimuths=AZIMUTHS):
     t = np.full(n, np.inf)
     down = d[:, 2] < -1e-4
     t[down] = GROUND_Z / d[down, 2]
-    tc = _ray_cars(cars_f, np.zeros(3), d, 1.0)
-    tc = np.where(tc > 0, tc, np.inf).min(-1) if tc.shape[1] else np.full(n, np.inf)
-    t = np.minimum(t, tc)
+    if len(cars_f):
+        for i0 in range(0, n, 16384):                        # bounded temporaries
+            tc = _ray_cars(cars_f, np.zeros(3), d[i0:i0 + 16384], 1.0)
+            t[i0:i0 + 16384] = np.minimum(t[i0:i0 + 16384], np.where(tc > 0, tc, np.inf).min(-1))
     clutter = 5.0 + 75.0 * rng.random(n)
     t = np.where(t > 120.0, clutter, t) + rng.normal(0.0, 0.02, n)
     pts = np.empty((n, 4), np.float32)
@@ -134,12 +135,15 @@ def numpy_masks(cars_f, camera, TrVeloToRect, inflate=INFLATE):
     """uint8 [C,H,W] silhouettes of the inflated cars."""
     H, W = camera.height, camera.width
     Tinv = np.linalg.inv(TrVeloToRect)
-    ys, xs = np.mgrid[0:H, 0:W]
-    r = np.stack([(xs.ravel() - camera.K[0, 2]) / camera.K[0, 0], (ys.ravel() - camera.K[1, 2]) / camera.K[1, 1],
-                  np.ones(H * W)], -1)
-    d = r @ Tinv[:3, :3].T
-    t = _ray_cars(cars_f, Tinv[:3, 3], d, inflate)
-    return np.isfinite(t).T.reshape(len(cars_f), H, W).astype(np.uint8)
+    out = np.zeros((len(cars_f), H, W), np.uint8)
+    xs = (np.arange(W) - camera.K[0, 2]) / camera.K[0, 0]
+    for y0 in range(0, H, 16):                               # bounded temporaries
+        y1 = min(H, y0 + 16)
+        ys = (np.arange(y0, y1) - camera.K[1, 2]) / camera.K[1, 1]
+        r = np.stack([np.tile(xs, y1 - y0), np.repeat(ys, W), np.ones((y1 - y0) * W)], -1)
+        t = _ray_cars(cars_f, Tinv[:3, 3], r @ Tinv[:3, :3].T, inflate)
+        out[:, y0:y1, :] = np.isfinite(t).T.reshape(len(cars_f), y1 - y0, W)
+    return out
 
 
 # ------------------------------------------------------------------ device generator
