@@ -10,7 +10,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, '_lib', 'liblidarfuse.so')
 SOURCES = ['ctx.cu', 'project.cu', 'erode.cu', 'fuse.cu', 'points.cu', 'synth.cu']
-HEADERS = [os.path.join(CSRC, 'common.cuh'), os.path.join(ROOT, 'include', 'lidarfuse.h')]
+HEADERS = [os.path.join(CSRC, 'common.cuh'), os.path.join(CSRC, 'bulk.cuh'), os.path.join(ROOT, 'include', 'lidarfuse.h')]
 
 
 def _nvcc():

@@ -74,6 +74,39 @@ __device__ __forceinline__ void lf_project_point(const LfCam& c, float x, float 
     vq = rint(__ddiv_rn(q[1], ad));
 }
 
+// The same projection in two steps, for kernels that gate on depth before
+// paying for the two divisions: step 1 gives the undivided image coordinates
+// and the depth (identical chains, identical bits), step 2 the rounded quotients.
+__device__ __forceinline__ void lf_project_xyd(const LfCam& c, float x, float y, float z, double& qx, double& qy,
+                                               double& depth) {
+    const double X = (double)x, Y = (double)y, Z = (double)z;
+    double p[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double a = __dmul_rn(c.T[4 * i + 0], X);
+        a = __fma_rn(c.T[4 * i + 1], Y, a);
+        a = __fma_rn(c.T[4 * i + 2], Z, a);
+        a = __fma_rn(c.T[4 * i + 3], 1.0, a);
+        p[i] = a;
+    }
+    double q[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double a = __dmul_rn(c.K[3 * i + 0], p[0]);
+        a = __fma_rn(c.K[3 * i + 1], p[1], a);
+        a = __fma_rn(c.K[3 * i + 2], p[2], a);
+        q[i] = a;
+    }
+    qx = q[0]; qy = q[1];
+    depth = q[2];
+    if (depth == 0.0) depth = -1e-6;
+}
+__device__ __forceinline__ void lf_project_uv(double qx, double qy, double depth, double& uq, double& vq) {
+    const double ad = fabs(depth);
+    uq = rint(__ddiv_rn(qx, ad));
+    vq = rint(__ddiv_rn(qy, ad));
+}
+
 // numpy's float64 -> int64 cast (x86 cvttsd2si): NaN and out-of-range give INT64_MIN.
 __device__ __forceinline__ long long lf_np_f64_to_i64(double r) {
     if (!(fabs(r) < 9.2233720368547758e18)) return (long long)0x8000000000000000ULL;

@@ -11,6 +11,7 @@
 // mbarrier ring, so ~24-32 KB per CTA are in flight with no register cost.
 // Generic path (any W, uint8 or float32): coalesced loads + __ballot_sync.
 #include "common.cuh"
+#include "bulk.cuh"
 
 namespace {
 
@@ -24,38 +25,12 @@ struct ErodeParams {
     int rows_per_strip, strips;
     int k, r, iterations, halo;
     int buf_words;                       // words per packed smem buffer
+    unsigned wpr_magic;                  // ceil(2^32 / wpr): it / wpr == __umulhi(it, magic) for it < 2^16
+    int spans_ok;                        // every SE row is one contiguous run (RECT / CROSS / ELLIPSE are)
     unsigned short se_rows[LF_MAX_SE];   // bit j of se_rows[i] = SE[i][j]
+    signed char span_a[LF_MAX_SE];       // row i covers dx in [-span_a[i], +span_b[i]]; span_a < 0: empty row
+    signed char span_b[LF_MAX_SE];
 };
-
-// ---- mbarrier / bulk-copy PTX (sm_90+; SASS: SYNCS.*, UBLKCP) -----------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-            smem_u32(dst)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar))
-        : "memory");
-}
 
 // 4 bytes -> 4 bits (bit j = byte j non-zero), returned in bits 28..31.
 __device__ __forceinline__ uint32_t nz_nibble_hi(uint32_t w) {
@@ -110,13 +85,75 @@ __device__ __forceinline__ void erode_pass(const ErodeParams& P, const uint32_t*
     }
 }
 
+// AND over dx = 0..b of bit (x + dx), for the 32 pixels of word c (r = next word): window doubling
+// on the 64-bit pair.  Zeros shifted in at the top never reach the low word for b <= 15.
+__device__ __forceinline__ uint32_t and_right(uint32_t c, uint32_t r, int b) {
+    unsigned long long v = ((unsigned long long)r << 32) | c;
+    for (int w = 1; w < b + 1;) {
+        const int s = min(w, b + 1 - w);
+        v &= v >> s;
+        w += s;
+    }
+    return (uint32_t)v;
+}
+// AND over dx = 0..a of bit (x - dx) (l = previous word)
+__device__ __forceinline__ uint32_t and_left(uint32_t l, uint32_t c, int a) {
+    unsigned long long v = ((unsigned long long)c << 32) | l;
+    for (int w = 1; w < a + 1;) {
+        const int s = min(w, a + 1 - w);
+        v &= v << s;
+        w += s;
+    }
+    return (uint32_t)(v >> 32);
+}
+
+// Row-span erosion: every SE row i is one run [-a_i, +b_i], so
+// out[y] = AND_i hspan_i(in[y + i - r]).  K > 0 unrolls the row loop.
+template <int K>
+__device__ __forceinline__ void erode_pass_spans(const ErodeParams& P, const uint32_t* __restrict__ src,
+                                                 uint32_t* __restrict__ dst, int ga, int gb) {
+    const int nrows = gb - ga;
+    const int items = nrows * P.wpr;
+    const int k = K > 0 ? K : P.k;
+    const int rad = k / 2;
+    const uint32_t padmask = (P.W & 31) ? ~((1u << (P.W & 31)) - 1u) : 0u;
+    for (int it = threadIdx.x; it < items; it += ER_THREADS) {
+        const int lr = (int)__umulhi((unsigned)it, P.wpr_magic);
+        const int wx = it - lr * P.wpr;
+        uint32_t acc = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < k; ++i) {
+            const int a = P.span_a[i], b = P.span_b[i];
+            if (a < 0) continue;
+            const int lr2 = lr + i - rad;
+            if (lr2 < 0 || lr2 >= nrows) continue;
+            const uint32_t* row = src + lr2 * P.wpr;
+            uint32_t m = row[wx];
+            if (b > 0) m = and_right(m, wx + 1 < P.wpr ? row[wx + 1] : 0xFFFFFFFFu, b);
+            if (a > 0) m &= and_left(wx > 0 ? row[wx - 1] : 0xFFFFFFFFu, row[wx], a);
+            acc &= m;
+        }
+        if (wx == P.wpr - 1) acc |= padmask;
+        dst[it] = acc;
+    }
+}
+
+__device__ __forceinline__ void erode_dispatch(const ErodeParams& P, const uint32_t* src, uint32_t* dst, int ga,
+                                               int gb) {
+    if (!P.spans_ok) erode_pass(P, src, dst, ga, gb);
+    else if (P.k == 3) erode_pass_spans<3>(P, src, dst, ga, gb);
+    else if (P.k == 5) erode_pass_spans<5>(P, src, dst, ga, gb);
+    else if (P.k == 7) erode_pass_spans<7>(P, src, dst, ga, gb);
+    else erode_pass_spans<0>(P, src, dst, ga, gb);
+}
+
 __device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* bufA, uint32_t* bufB, int ga,
                                                 int gb, int r0, int r1, uint32_t* __restrict__ out_mask) {
     uint32_t* cur = bufA;
     uint32_t* nxt = bufB;
     for (int itn = 0; itn < P.iterations; ++itn) {
         __syncthreads();
-        erode_pass(P, cur, nxt, ga, gb);
+        erode_dispatch(P, cur, nxt, ga, gb);
         uint32_t* t = cur; cur = nxt; nxt = t;
     }
     __syncthreads();
@@ -126,7 +163,7 @@ __device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* 
     uint32_t* dstw = out_mask + (int64_t)r0 * P.wpr;
     for (int it = threadIdx.x; it < items; it += ER_THREADS) {
         uint32_t w = srcw[it];
-        if ((it % P.wpr) == P.wpr - 1) w &= keep;
+        if (keep != 0xFFFFFFFFu && (it - (int)__umulhi((unsigned)it, P.wpr_magic) * P.wpr) == P.wpr - 1) w &= keep;
         dstw[it] = w;
     }
 }
@@ -160,7 +197,7 @@ lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < ER_STAGES; ++s) mbar_init(&full_bar[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_fence_init();
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -170,22 +207,39 @@ lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
             bulk_g2s(stage + i * ER_CHUNK, src + (int64_t)i * ER_CHUNK, bytes, &full_bar[i]);
         }
     }
-    for (int i = 0; i < nch; ++i) {
-        const int s = i % ER_STAGES;
-        mbar_wait(&full_bar[s], (uint32_t)((i / ER_STAGES) & 1));
-        const int off = i * ER_CHUNK + 32 * threadIdx.x;
-        if (off < L) {
-            const uint4* q = (const uint4*)(stage + s * ER_CHUNK + 32 * threadIdx.x);
-            bufA[off >> 5] = pack32(q[0], q[1]);
+    // two stages per block barrier: halves the per-byte loop / barrier overhead
+    for (int i = 0; i < nch; i += 2) {
+        const int s0 = i % ER_STAGES, s1 = (i + 1) % ER_STAGES;
+        const uint32_t par = (uint32_t)((i / ER_STAGES) & 1);
+        const int off0 = i * ER_CHUNK + 32 * threadIdx.x;
+        const int off1 = off0 + ER_CHUNK;
+        mbar_wait(&full_bar[s0], par);
+        uint4 a0, a1, b0, b1;
+        if (off0 < L) {
+            const uint4* q = (const uint4*)(stage + s0 * ER_CHUNK + 32 * threadIdx.x);
+            a0 = q[0]; a1 = q[1];
         }
-        __syncthreads();                                  // stage s fully consumed
-        if (threadIdx.x == 0 && i + ER_STAGES < nch) {
-            const int j = i + ER_STAGES;
-            const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - j * ER_CHUNK);
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_expect_tx(&full_bar[s], bytes);
-            bulk_g2s(stage + s * ER_CHUNK, src + (int64_t)j * ER_CHUNK, bytes, &full_bar[s]);
+        if (i + 1 < nch) mbar_wait(&full_bar[s1], par);
+        if (off1 < L) {
+            const uint4* q = (const uint4*)(stage + s1 * ER_CHUNK + 32 * threadIdx.x);
+            b0 = q[0]; b1 = q[1];
         }
+        __syncthreads();                                  // both stages are in registers now
+        if (threadIdx.x == 0) {
+            fence_proxy_async_smem();
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int j = i + t + ER_STAGES;
+                if (j < nch) {
+                    const int sj = j % ER_STAGES;
+                    const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - j * ER_CHUNK);
+                    mbar_expect_tx(&full_bar[sj], bytes);
+                    bulk_g2s(stage + sj * ER_CHUNK, src + (int64_t)j * ER_CHUNK, bytes, &full_bar[sj]);
+                }
+            }
+        }
+        if (off0 < L) bufA[off0 >> 5] = pack32(a0, a1);
+        if (off1 < L) bufA[off1 >> 5] = pack32(b0, b1);
     }
     erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr);
 }
@@ -272,6 +326,19 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
         }
         if (!any) return LF_E_ARG;                        // an empty element has no cv2 meaning
     }
+    P.spans_ok = 1;
+    for (int i = 0; i < P.k; ++i) {
+        const unsigned bits = iterations > 0 ? P.se_rows[i] : (i == 0 ? 1u : 0u);
+        if (!bits) { P.span_a[i] = -1; P.span_b[i] = 0; continue; }
+        int lo = 0, hi = P.k - 1;
+        while (!((bits >> lo) & 1u)) ++lo;
+        while (!((bits >> hi) & 1u)) --hi;
+        for (int j = lo; j <= hi; ++j)
+            if (!((bits >> j) & 1u)) P.spans_ok = 0;
+        if (lo > P.r || hi < P.r) P.spans_ok = 0;         // run must straddle the anchor column
+        P.span_a[i] = (signed char)(P.r - lo);
+        P.span_b[i] = (signed char)(hi - P.r);
+    }
     P.halo = iterations * P.r;
 
     // strip plan: enough CTAs to fill the machine several times over, strips <= ER_MAX_ROWS rows
@@ -283,6 +350,8 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
     P.strips = (H + P.rows_per_strip - 1) / P.rows_per_strip;
     const int buf_rows = P.rows_per_strip + 2 * P.halo;
     P.buf_words = buf_rows * P.wpr;
+    P.wpr_magic = (unsigned)((0x100000000ULL + P.wpr - 1) / P.wpr);
+    if ((int64_t)buf_rows * P.wpr >= 65536) return LF_E_UNSUPPORTED;
     if (m * P.strips > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
 
     const bool fast = mode == 0 && (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;

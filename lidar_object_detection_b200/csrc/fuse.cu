@@ -1,17 +1,25 @@
 // K1+K4+K5 fused pass over the points of a batch of frames, and K6 per-car decision.
 //
-// One CTA = (frame, chunk of FUSE_THREADS*FUSE_PPT consecutive points).  Each
-// point is read once (one 128-bit streaming load, 16 B of HBM traffic); the
-// packed masks (66 KB each) and the boxes are L2 / shared-memory traffic.
-// Counters are privatised in shared memory per CTA and flushed with one global
-// atomic per non-zero counter.
+// One CTA = (frame, segment of FUSE_SEG consecutive points).  The segment is
+// streamed through a 3-stage shared-memory ring by cp.async.bulk (TMA engine):
+// 16 KB sub-chunks of 1024 points, so every point costs exactly 16 B of HBM
+// traffic and two sub-chunks per CTA are always in flight with no register cost.
+// Per point: fp64 projection chain -> depth gate -> two divisions only for
+// points in front of the camera -> packed-mask gather (L2) -> oriented-box test
+// against the boxes a warp-level bounding-box cull leaves over.  Counters are
+// privatised in shared memory and flushed with one global atomic per non-zero
+// counter per CTA.
 #include "common.cuh"
+#include "bulk.cuh"
 
 namespace {
 
 constexpr int FUSE_THREADS = 256;
-constexpr int FUSE_PPT = 4;
-constexpr int FUSE_CHUNK = FUSE_THREADS * FUSE_PPT;
+constexpr int FUSE_PPT = 4;                               // points per thread per sub-chunk
+constexpr int FUSE_SUB = FUSE_THREADS * FUSE_PPT;         // 1024 points = 16 KB per stage
+constexpr int FUSE_STAGES = 3;
+constexpr int FUSE_SUBS_PER_SEG = 16;
+constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 16384 points per CTA
 
 struct FuseArgs {
     const float4* pts;
@@ -29,13 +37,22 @@ struct FuseArgs {
     double max_depth;
     int use_oriented;
     int smem_boxes;      // boxes staged in shared memory (max over frames)
-    int smem_cars;       // min(max masks per frame, 64)
+    int smem_cars;       // max masks per frame (<= LF_MAX_CARS)
 };
 
 __device__ __forceinline__ unsigned long long warp_or64(unsigned long long v) {
     const unsigned lo = __reduce_or_sync(0xFFFFFFFFu, (unsigned)v);
     const unsigned hi = __reduce_or_sync(0xFFFFFFFFu, (unsigned)(v >> 32));
     return ((unsigned long long)hi << 32) | lo;
+}
+
+// float <-> unsigned key with the same ordering (for warp min / max reductions)
+__device__ __forceinline__ unsigned f2key(float f) {
+    const unsigned b = __float_as_uint(f);
+    return b ^ ((unsigned)((int)b >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float key2f(unsigned k) {
+    return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
 }
 
 // closed-interval slab test 0 <= dot(rel,e)/ee <= 1 (cvs_erosion.py:133-138).
@@ -51,25 +68,141 @@ __device__ __forceinline__ bool slab(double rx, double ry, double rz, const doub
     return __ddiv_rn(d, ee) >= 0.0;
 }
 
-__global__ void __launch_bounds__(FUSE_THREADS)
+__device__ __forceinline__ bool point_in_box(const lf_box& bx, float x, float y, float z, int oriented) {
+    const double X = (double)x, Y = (double)y, Z = (double)z;
+    if (oriented) {
+        const double rx = X - bx.c0[0], ry = Y - bx.c0[1], rz = Z - bx.c0[2];
+        return slab(rx, ry, rz, bx.e1, bx.ee[0]) && slab(rx, ry, rz, bx.e2, bx.ee[1]) &&
+               slab(rx, ry, rz, bx.e3, bx.ee[2]);
+    }
+    return X >= bx.amin[0] && X <= bx.amax[0] && Y >= bx.amin[1] && Y <= bx.amax[1] && Z >= bx.amin[2] &&
+           Z <= bx.amax[2];
+}
+
+// Everything one warp does for 32 consecutive points (one per lane).
+__device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArgs& A, float4 p, bool live,
+                                                 int64_t gidx, int lane, int M, int B, const uint32_t* mask_base,
+                                                 int64_t plane, const lf_box* s_box, int32_t* s_inside,
+                                                 int32_t* s_nin, int32_t* s_total, int& my_valid) {
+    const unsigned FULL = 0xFFFFFFFFu;
+    double qx, qy, d;
+    lf_project_xyd(cam, p.x, p.y, p.z, qx, qy, d);
+    const bool front = live && d > 0.0 && d < A.max_depth;            // depth half of cvs_erosion.py:359
+    bool valid = false;
+    double uq = 0.0, vq = 0.0;
+    if (__any_sync(FULL, front)) {
+        if (front) {
+            lf_project_uv(qx, qy, d, uq, vq);
+            valid = (uq >= 0.0) && (uq < (double)cam.W) && (vq >= 0.0) && (vq < (double)cam.H);
+        }
+    }
+    const unsigned vmask = __ballot_sync(FULL, valid);
+    if (!vmask) {
+        if (A.car_bits && live) A.car_bits[gidx] = 0ULL;
+        return;
+    }
+    my_valid += valid ? 1 : 0;
+    // ---- K4: point-in-mask gather (cvs_erosion.py:152-160) ---------------------
+    unsigned long long bits = 0ULL;
+    if (valid && M > 0) {
+        const int ui = (int)uq, vi = (int)vq;
+        const uint32_t* w = mask_base + (int64_t)vi * cam.wpr + (ui >> 5);
+        const int sh = ui & 31;
+        unsigned lo = 0u, hi = 0u;
+        const int m_lo = min(M, 32);
+#pragma unroll 4
+        for (int c = 0; c < m_lo; ++c) lo = __funnelshift_r(lo, __ldg(w + c * plane) >> sh, 1);
+        lo >>= (32 - m_lo);
+        if (M > 32) {
+            for (int c = 32; c < M; ++c) hi = __funnelshift_r(hi, __ldg(w + c * plane) >> sh, 1);
+            hi >>= (64 - M);
+        }
+        bits = ((unsigned long long)hi << 32) | lo;
+    }
+    if (A.car_bits && live) A.car_bits[gidx] = bits;
+    unsigned long long un = warp_or64(bits);
+    while (un) {
+        const int c = __ffsll((long long)un) - 1;
+        un &= un - 1;
+        const unsigned bal = __ballot_sync(FULL, (bits >> c) & 1ULL);
+        if (lane == 0) atomicAdd(&s_total[c], __popc(bal));
+    }
+    if (B == 0) return;
+    // ---- warp bounding box of the valid points, then lanes test boxes in parallel
+    const float INF = __int_as_float(0x7f800000);
+    const float wx0 = key2f(__reduce_min_sync(FULL, f2key(valid ? p.x : INF)));
+    const float wx1 = key2f(__reduce_max_sync(FULL, f2key(valid ? p.x : -INF)));
+    const float wy0 = key2f(__reduce_min_sync(FULL, f2key(valid ? p.y : INF)));
+    const float wy1 = key2f(__reduce_max_sync(FULL, f2key(valid ? p.y : -INF)));
+    const float wz0 = key2f(__reduce_min_sync(FULL, f2key(valid ? p.z : INF)));
+    const float wz1 = key2f(__reduce_max_sync(FULL, f2key(valid ? p.z : -INF)));
+    for (int g = 0; g < B; g += 32) {
+        const int bl = g + lane;
+        bool cand = false;
+        if (bl < B) {
+            const lf_box& bx = s_box[bl];
+            cand = wx1 >= bx.lo[0] && wx0 <= bx.hi[0] && wy1 >= bx.lo[1] && wy0 <= bx.hi[1] && wz1 >= bx.lo[2] &&
+                   wz0 <= bx.hi[2];
+        }
+        unsigned cmask = __ballot_sync(FULL, cand);
+        // ---- K5: containment (cvs_erosion.py:114-145 / V1:118-139) on the candidates
+        while (cmask) {
+            const int b = g + __ffs((int)cmask) - 1;
+            cmask &= cmask - 1;
+            const lf_box& bx = s_box[b];
+            const bool near = valid && p.x >= bx.lo[0] && p.x <= bx.hi[0] && p.y >= bx.lo[1] && p.y <= bx.hi[1] &&
+                              p.z >= bx.lo[2] && p.z <= bx.hi[2];
+            const bool in = near && point_in_box(bx, p.x, p.y, p.z, A.use_oriented);
+            const unsigned bal = __ballot_sync(FULL, in);
+            if (!bal) continue;
+            if (lane == 0) atomicAdd(&s_nin[b], __popc(bal));
+            unsigned long long un2 = warp_or64(in ? bits : 0ULL);
+            while (un2) {
+                const int c = __ffsll((long long)un2) - 1;
+                un2 &= un2 - 1;
+                const unsigned bb = __ballot_sync(FULL, in && ((bits >> c) & 1ULL));
+                if (lane == 0) atomicAdd(&s_inside[c * A.smem_boxes + b], __popc(bb));
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(FUSE_THREADS, 3)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
-    extern __shared__ __align__(16) uint8_t smem[];
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
     const int f = blockIdx.y;
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
-    const int64_t base = p0 + (int64_t)blockIdx.x * FUSE_CHUNK;
-    if (base >= p1) return;
+    const int64_t seg0 = p0 + (int64_t)blockIdx.x * FUSE_SEG;
+    if (seg0 >= p1) return;
+    const int npts = (int)min((int64_t)FUSE_SEG, p1 - seg0);
+    const int nsub = (npts + FUSE_SUB - 1) / FUSE_SUB;
     const int m0 = A.mask_off[f];
     const int M = A.mask_off[f + 1] - m0;
     const int b0 = A.box_off[f];
     const int B = A.box_off[f + 1] - b0;
 
-    lf_box* s_box = (lf_box*)smem;
-    int32_t* s_inside = (int32_t*)(smem + (size_t)A.smem_boxes * sizeof(lf_box));
+    float4* stage = (float4*)smem;                                               // [FUSE_STAGES][FUSE_SUB]
+    lf_box* s_box = (lf_box*)(smem + FUSE_STAGES * FUSE_SUB * sizeof(float4));
+    int32_t* s_inside = (int32_t*)((uint8_t*)s_box + (size_t)A.smem_boxes * sizeof(lf_box));
     int32_t* s_nin = s_inside + (size_t)A.smem_cars * A.smem_boxes;
     int32_t* s_total = s_nin + A.smem_boxes;
     int32_t* s_nvalid = s_total + A.smem_cars;
+    const float4* src = A.pts + seg0;
 
-    {   // stage the frame's boxes and clear the private counters
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < FUSE_STAGES; ++s) mbar_init(&full_bar[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < FUSE_STAGES && i < nsub; ++i) {
+            const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
+            mbar_expect_tx(&full_bar[i], bytes);
+            bulk_g2s(stage + i * FUSE_SUB, src + (int64_t)i * FUSE_SUB, bytes, &full_bar[i]);
+        }
+    }
+    {   // while the first sub-chunks fly: stage the frame's boxes, clear the private counters
         const double* gsrc = (const double*)(A.boxes + b0);
         double* sdst = (double*)s_box;
         const int nd = B * (int)(sizeof(lf_box) / 8);
@@ -77,106 +210,56 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
         const int nc = A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 1;
         for (int i = threadIdx.x; i < nc; i += FUSE_THREADS) s_inside[i] = 0;
     }
-
-    // all loads of the chunk first: FUSE_PPT independent 16-B requests per thread
-    float4 p[FUSE_PPT];
-    bool live[FUSE_PPT];
-#pragma unroll
-    for (int j = 0; j < FUSE_PPT; ++j) {
-        const int64_t i = base + j * FUSE_THREADS + threadIdx.x;
-        live[j] = i < p1;
-        p[j] = live[j] ? ld_stream_f4(A.pts + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
     const int64_t plane = (int64_t)cam.H * cam.wpr;
+    const uint32_t* mask_base = A.packed + (int64_t)m0 * plane;
     int my_valid = 0;
 
-    for (int g0 = 0; g0 < (M > 0 ? M : 1); g0 += LF_MAX_CARS) {     // >64 masks: extra passes
-        const int Mg = min(LF_MAX_CARS, M - g0);
+    for (int i = 0; i < nsub; ++i) {
+        const int s = i % FUSE_STAGES;
+        mbar_wait(&full_bar[s], (uint32_t)((i / FUSE_STAGES) & 1));
+        const int nhere = min(FUSE_SUB, npts - i * FUSE_SUB);
+        float4 p[FUSE_PPT];
 #pragma unroll
         for (int j = 0; j < FUSE_PPT; ++j) {
-            double uq, vq, d;
-            lf_project_point(cam, p[j].x, p[j].y, p[j].z, uq, vq, d);
-            const bool valid = live[j] && lf_gate(cam, uq, vq, d, A.max_depth);
-            if (g0 == 0) my_valid += valid ? 1 : 0;
-            if (!__any_sync(0xFFFFFFFFu, valid)) {
-                if (A.car_bits && live[j] && g0 == 0) A.car_bits[base + j * FUSE_THREADS + threadIdx.x] = 0ULL;
-                continue;
-            }
-            // ---- K4: point-in-mask gather (cvs_erosion.py:152-160) -------------
-            unsigned long long bits = 0ULL;
-            if (valid && Mg > 0) {
-                const int ui = (int)uq, vi = (int)vq;
-                const uint32_t* w = A.packed + (int64_t)(m0 + g0) * plane + (int64_t)vi * cam.wpr + (ui >> 5);
-                const int sh = ui & 31;
-                for (int c = 0; c < Mg; ++c)
-                    bits |= (unsigned long long)((__ldg(w + c * plane) >> sh) & 1u) << c;
-            }
-            if (A.car_bits && live[j] && g0 == 0) A.car_bits[base + j * FUSE_THREADS + threadIdx.x] = bits;
-            unsigned long long un = warp_or64(bits);
-            while (un) {
-                const int c = __ffsll((long long)un) - 1;
-                un &= un - 1;
-                const unsigned bal = __ballot_sync(0xFFFFFFFFu, (bits >> c) & 1ULL);
-                if (lane == 0) atomicAdd(&s_total[c], __popc(bal));
-            }
-            // ---- K5: containment (cvs_erosion.py:114-145 / V1:118-139) ----------
-            for (int b = 0; b < B; ++b) {
-                const lf_box& bx = s_box[b];
-                const bool near = valid && p[j].x >= bx.lo[0] && p[j].x <= bx.hi[0] && p[j].y >= bx.lo[1] &&
-                                  p[j].y <= bx.hi[1] && p[j].z >= bx.lo[2] && p[j].z <= bx.hi[2];
-                if (!__any_sync(0xFFFFFFFFu, near)) continue;
-                bool in = false;
-                if (near) {
-                    const double X = (double)p[j].x, Y = (double)p[j].y, Z = (double)p[j].z;
-                    if (A.use_oriented) {
-                        const double rx = X - bx.c0[0], ry = Y - bx.c0[1], rz = Z - bx.c0[2];
-                        in = slab(rx, ry, rz, bx.e1, bx.ee[0]) && slab(rx, ry, rz, bx.e2, bx.ee[1]) &&
-                             slab(rx, ry, rz, bx.e3, bx.ee[2]);
-                    } else {
-                        in = X >= bx.amin[0] && X <= bx.amax[0] && Y >= bx.amin[1] && Y <= bx.amax[1] &&
-                             Z >= bx.amin[2] && Z <= bx.amax[2];
-                    }
-                }
-                const unsigned bal = __ballot_sync(0xFFFFFFFFu, in);
-                if (!bal) continue;
-                if (lane == 0 && g0 == 0) atomicAdd(&s_nin[b], __popc(bal));
-                unsigned long long un2 = warp_or64(in ? bits : 0ULL);
-                while (un2) {
-                    const int c = __ffsll((long long)un2) - 1;
-                    un2 &= un2 - 1;
-                    const unsigned bb = __ballot_sync(0xFFFFFFFFu, in && ((bits >> c) & 1ULL));
-                    if (lane == 0) atomicAdd(&s_inside[c * A.smem_boxes + b], __popc(bb));
-                }
-            }
+            const int k = j * FUSE_THREADS + threadIdx.x;
+            p[j] = k < nhere ? stage[s * FUSE_SUB + k] : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        // flush this group of cars
-        const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
-        if (g0 == 0 && lane == 0 && vb) atomicAdd(s_nvalid, (int)vb);
-        __syncthreads();
-        for (int i = threadIdx.x; i < Mg * B; i += FUSE_THREADS) {
-            const int c = i / B, b = i - c * B;
-            const int v = s_inside[c * A.smem_boxes + b];
-            if (v) {
-                atomicAdd(A.inside + A.cnt_off[f] + (int64_t)(g0 + c) * B + b, v);
-                s_inside[c * A.smem_boxes + b] = 0;
-            }
+        __syncthreads();                                   // stage s is in registers everywhere
+        if (threadIdx.x == 0 && i + FUSE_STAGES < nsub) {
+            const int jn = i + FUSE_STAGES;
+            const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - jn * FUSE_SUB) * 16u;
+            fence_proxy_async_smem();
+            mbar_expect_tx(&full_bar[s], bytes);
+            bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)jn * FUSE_SUB, bytes, &full_bar[s]);
         }
-        for (int c = threadIdx.x; c < Mg; c += FUSE_THREADS) {
-            const int v = s_total[c];
-            if (v) { atomicAdd(A.total + m0 + g0 + c, v); s_total[c] = 0; }
+#pragma unroll
+        for (int j = 0; j < FUSE_PPT; ++j) {
+            const int k = j * FUSE_THREADS + threadIdx.x;
+            fuse_warp_points(cam, A, p[j], k < nhere, seg0 + (int64_t)i * FUSE_SUB + k, lane, M, B, mask_base,
+                             plane, s_box, s_inside, s_nin, s_total, my_valid);
         }
-        if (g0 == 0) {
-            for (int b = threadIdx.x; b < B; b += FUSE_THREADS) {
-                const int v = s_nin[b];
-                if (v) atomicAdd(A.n_in_box + b0 + b, v);
-            }
-            if (threadIdx.x == 0 && *s_nvalid) atomicAdd(A.n_valid + f, *s_nvalid);
-        }
-        __syncthreads();
     }
+
+    const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
+    if (lane == 0 && vb) atomicAdd(s_nvalid, (int)vb);
+    __syncthreads();
+    for (int i = threadIdx.x; i < M * B; i += FUSE_THREADS) {
+        const int c = i / B, b = i - c * B;
+        const int v = s_inside[c * A.smem_boxes + b];
+        if (v) atomicAdd(A.inside + A.cnt_off[f] + i, v);
+    }
+    for (int c = threadIdx.x; c < M; c += FUSE_THREADS) {
+        const int v = s_total[c];
+        if (v) atomicAdd(A.total + m0 + c, v);
+    }
+    for (int b = threadIdx.x; b < B; b += FUSE_THREADS) {
+        const int v = s_nin[b];
+        if (v) atomicAdd(A.n_in_box + b0 + b, v);
+    }
+    if (threadIdx.x == 0 && *s_nvalid) atomicAdd(A.n_valid + f, *s_nvalid);
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -254,12 +337,13 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     A.car_bits = (unsigned long long*)car_bits;
     A.max_depth = max_depth; A.use_oriented = use_oriented;
     A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
-    A.smem_cars = max_masks_per_frame > LF_MAX_CARS ? LF_MAX_CARS : (max_masks_per_frame > 0 ? max_masks_per_frame : 1);
-    const size_t smem = (size_t)A.smem_boxes * sizeof(lf_box) +
+    if (max_masks_per_frame > LF_MAX_CARS) return LF_E_UNSUPPORTED;   // callers split the masks of such frames
+    A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
+    const size_t smem = (size_t)FUSE_STAGES * FUSE_SUB * sizeof(float4) + (size_t)A.smem_boxes * sizeof(lf_box) +
                         4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4);
     if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
     LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t chunks = (max_points_per_frame + FUSE_CHUNK - 1) / FUSE_CHUNK;
+    const int64_t chunks = (max_points_per_frame + FUSE_SEG - 1) / FUSE_SEG;
     if (chunks > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
     dim3 grid((unsigned)chunks, (unsigned)F);
     lf_fuse_kernel<<<grid, FUSE_THREADS, smem, (cudaStream_t)stream>>>(ctx->cam, A);
