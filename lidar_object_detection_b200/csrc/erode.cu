@@ -245,6 +245,169 @@ lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
 }
 
 // ---------------------------------------------------------------------------
+// specialised fast path: structuring element known at compile time
+// ---------------------------------------------------------------------------
+// Symmetric row-span elements (every cv2 RECT / CROSS / ELLIPSE up to 7x7):
+// row i and row K-1-i have the same half-width HW(i); HW < 0 = empty row.
+// Packed rows live in shared memory with stride wpr+1: word 0 of every row is an
+// all-ones guard that doubles as the right neighbour of the previous row, and
+// K/2 all-ones guard rows sit above and below, so the erosion loop has no
+// bounds checks at all (out-of-image = ones = cv2's +inf erosion border).
+template <int K, int H0, int H1, int H2, int H3>
+struct SeSpec {
+    static constexpr int k = K;
+    __host__ __device__ static constexpr int hw(int i) {
+        const int j = i <= K / 2 ? i : K - 1 - i;
+        return j == 0 ? H0 : (j == 1 ? H1 : (j == 2 ? H2 : H3));
+    }
+};
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+template <class SE>
+__global__ void __launch_bounds__(ER_THREADS)
+lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __restrict__ masks,
+                     uint32_t* __restrict__ packed) {
+    constexpr int K = SE::k, RAD = K / 2;
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[ER_STAGES];
+    const uint32_t stage_a = smem_u32(smem);
+    uint32_t* bufA = (uint32_t*)(smem + ER_STAGES * ER_CHUNK);
+    uint32_t* bufB = bufA + P.buf_words;
+
+    const int64_t mask = blockIdx.x / P.strips;
+    const int strip = blockIdx.x - (int)(mask * P.strips);
+    int r0, r1, ga, gb;
+    strip_rows(P, strip, r0, r1, ga, gb);
+    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W;
+    const int nrows = gb - ga;
+    const int L = nrows * P.W;
+    const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
+    const int S = P.wpr + 1;                               // row stride in words
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        for (int s = 0; s < ER_STAGES; ++s) mbar_init(&full_bar[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 0; i < ER_STAGES && i < nch; ++i) {
+            const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - i * ER_CHUNK);
+            mbar_expect_tx(&full_bar[i], bytes);
+            bulk_g2s(smem + i * ER_CHUNK, src + (int64_t)i * ER_CHUNK, bytes, &full_bar[i]);
+        }
+    }
+    // guards: RAD rows above and below the window, word 0 of every row, one trailing word
+    if (P.iterations > 0) {
+        const int top = RAD * S, all = (nrows + 2 * RAD) * S + 1;
+        for (int i = tid; i < top; i += ER_THREADS) {
+            bufA[i] = 0xFFFFFFFFu; bufB[i] = 0xFFFFFFFFu;
+            bufA[all - 1 - i] = 0xFFFFFFFFu; bufB[all - 1 - i] = 0xFFFFFFFFu;
+        }
+        for (int r = tid; r <= nrows; r += ER_THREADS) {
+            bufA[(r + RAD) * S] = 0xFFFFFFFFu; bufB[(r + RAD) * S] = 0xFFFFFFFFu;
+        }
+    }
+    const int data0 = RAD * S + 1;                         // word index of (row 0, wx 0)
+
+    for (int i = 0; i < nch; i += 2) {
+        const int s0 = i % ER_STAGES, s1 = (i + 1) % ER_STAGES;
+        const uint32_t par = (uint32_t)((i / ER_STAGES) & 1);
+        const int w0 = i * (ER_CHUNK / 32) + tid;          // flat word index of this thread's 32 px
+        const int w1 = w0 + ER_CHUNK / 32;
+        const bool p0 = w0 * 32 < L, p1 = w1 * 32 < L;
+        uint4 a0, a1, b0, b1;
+        mbar_wait(&full_bar[s0], par);
+        if (p0) { a0 = lds128(stage_a + s0 * ER_CHUNK + 32 * tid); a1 = lds128(stage_a + s0 * ER_CHUNK + 32 * tid + 16); }
+        if (i + 1 < nch) mbar_wait(&full_bar[s1], par);
+        if (p1) { b0 = lds128(stage_a + s1 * ER_CHUNK + 32 * tid); b1 = lds128(stage_a + s1 * ER_CHUNK + 32 * tid + 16); }
+        __syncthreads();                                   // both stages are in registers now
+        if (tid == 0) {
+            fence_proxy_async_smem();
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int j = i + t + ER_STAGES;
+                if (j < nch) {
+                    const int sj = j % ER_STAGES;
+                    const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - j * ER_CHUNK);
+                    mbar_expect_tx(&full_bar[sj], bytes);
+                    bulk_g2s(smem + sj * ER_CHUNK, src + (int64_t)j * ER_CHUNK, bytes, &full_bar[sj]);
+                }
+            }
+        }
+        // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
+        if (p0) bufA[w0 + (int)__umulhi((unsigned)w0, P.wpr_magic) + data0] = pack32(a0, a1);
+        if (p1) bufA[w1 + (int)__umulhi((unsigned)w1, P.wpr_magic) + data0] = pack32(b0, b1);
+    }
+
+    uint32_t* cur = bufA;
+    uint32_t* nxt = bufB;
+    const int items = nrows * P.wpr;
+    for (int itn = 0; itn < P.iterations; ++itn) {
+        __syncthreads();
+        for (int it = tid; it < items; it += ER_THREADS) {
+            const int idx = it + (int)__umulhi((unsigned)it, P.wpr_magic) + data0;
+            uint32_t acc = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                constexpr int dummy = 0; (void)dummy;
+                const int h = SE::hw(i);
+                if (h < 0) continue;
+                const uint32_t* rp = cur + idx + (i - RAD) * S;
+                const uint32_t c = rp[0];
+                acc &= c;
+                if (h > 0) {
+                    const uint32_t l = rp[-1], r = rp[1];
+#pragma unroll
+                    for (int d = 1; d <= h; ++d) acc &= __funnelshift_r(c, r, d) & __funnelshift_l(l, c, d);
+                }
+            }
+            nxt[idx] = acc;
+        }
+        uint32_t* t = cur; cur = nxt; nxt = t;
+    }
+    __syncthreads();
+    uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
+    const int out_items = (r1 - r0) * P.wpr;
+    const int skip = (r0 - ga) * S;
+    for (int it = tid; it < out_items; it += ER_THREADS)
+        dstw[it] = cur[it + (int)__umulhi((unsigned)it, P.wpr_magic) + data0 + skip];
+}
+
+typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)
+typedef SeSpec<3, 1, 1, 0, 0> SeRect3;
+typedef SeSpec<5, 0, 2, 2, 0> SeEllipse5;
+typedef SeSpec<5, 2, 2, 2, 0> SeRect5;
+typedef SeSpec<5, 0, 0, 2, 0> SeCross5;
+typedef SeSpec<7, 0, 2, 3, 3> SeEllipse7;
+typedef SeSpec<7, 3, 3, 3, 3> SeRect7;
+typedef SeSpec<7, 0, 0, 0, 3> SeCross7;
+typedef SeSpec<1, 0, 0, 0, 0> SeNone;       // pack only / 1x1
+
+template <class SE>
+bool se_matches(const ErodeParams& P) {
+    if (P.k != SE::k || !P.spans_ok) return false;
+    for (int i = 0; i < SE::k; ++i)
+        if (P.span_a[i] != SE::hw(i) || P.span_b[i] != SE::hw(i)) return false;
+    return true;
+}
+
+template <class SE>
+cudaError_t launch_fast(const ErodeParams& P, const uint8_t* masks, uint32_t* packed, unsigned grid, size_t smem,
+                        cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(lf_erode_fast_kernel<SE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    lf_erode_fast_kernel<SE><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
 // generic path: MODE 0 = uint8 non-zero, 1 = float >= 1.0 (the uint8 truncation
 // of cvs_erosion.py:101 / V2:197), 2 = float > 0.5 (seg_with_pointcloud.py:167)
 // ---------------------------------------------------------------------------
@@ -355,10 +518,41 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
     if (m * P.strips > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
 
     const bool fast = mode == 0 && (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
+    // compile-time element available?  (guarded smem layout: stride wpr+1, K/2 guard rows each side)
+    int spec = -1;
+    if (fast) {
+        if (iterations == 0 || se_matches<SeNone>(P)) spec = 0;
+        else if (se_matches<SeCross3>(P)) spec = 1;
+        else if (se_matches<SeRect3>(P)) spec = 2;
+        else if (se_matches<SeEllipse5>(P)) spec = 3;
+        else if (se_matches<SeRect5>(P)) spec = 4;
+        else if (se_matches<SeCross5>(P)) spec = 5;
+        else if (se_matches<SeEllipse7>(P)) spec = 6;
+        else if (se_matches<SeRect7>(P)) spec = 7;
+        else if (se_matches<SeCross7>(P)) spec = 8;
+    }
+    if (spec >= 0) P.buf_words = (buf_rows + 2 * P.r) * (P.wpr + 1) + 1;
     size_t smem = (size_t)P.buf_words * 4 * (iterations > 0 ? 2 : 1) + (fast ? ER_STAGES * ER_CHUNK : 0);
     if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
     const unsigned grid = (unsigned)(m * P.strips);
     cudaStream_t s = (cudaStream_t)stream;
+    if (spec >= 0) {
+        const uint8_t* mk = (const uint8_t*)masks;
+        cudaError_t e;
+        switch (spec) {
+            case 0: e = launch_fast<SeNone>(P, mk, packed, grid, smem, s); break;
+            case 1: e = launch_fast<SeCross3>(P, mk, packed, grid, smem, s); break;
+            case 2: e = launch_fast<SeRect3>(P, mk, packed, grid, smem, s); break;
+            case 3: e = launch_fast<SeEllipse5>(P, mk, packed, grid, smem, s); break;
+            case 4: e = launch_fast<SeRect5>(P, mk, packed, grid, smem, s); break;
+            case 5: e = launch_fast<SeCross5>(P, mk, packed, grid, smem, s); break;
+            case 6: e = launch_fast<SeEllipse7>(P, mk, packed, grid, smem, s); break;
+            case 7: e = launch_fast<SeRect7>(P, mk, packed, grid, smem, s); break;
+            default: e = launch_fast<SeCross7>(P, mk, packed, grid, smem, s); break;
+        }
+        LF_CUDA(ctx, e);
+        return LF_OK;
+    }
     if (fast) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)smem));
