@@ -14,9 +14,10 @@
 
 namespace {
 
-constexpr int FUSE_THREADS = 256;
-constexpr int FUSE_PPT = 4;                               // points per thread per sub-chunk
-constexpr int FUSE_SUB = FUSE_THREADS * FUSE_PPT;         // 1024 points = 16 KB per stage
+constexpr int FUSE_CONSUMERS = 8;                         // consumer warps
+constexpr int FUSE_THREADS = 32 * (FUSE_CONSUMERS + 1);   // + one producer warp (bulk-copy issue)
+constexpr int FUSE_SUB = 1024;                            // points per stage = 16 KB
+constexpr int FUSE_GROUPS = FUSE_SUB / 32;                // 32-point groups per stage, handed out dynamically
 constexpr int FUSE_STAGES = 3;
 constexpr int FUSE_SUBS_PER_SEG = 16;
 constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 16384 points per CTA
@@ -110,8 +111,15 @@ __device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArg
         const int sh = ui & 31;
         unsigned lo = 0u, hi = 0u;
         const int m_lo = min(M, 32);
-#pragma unroll 4
-        for (int c = 0; c < m_lo; ++c) lo = __funnelshift_r(lo, __ldg(w + c * plane) >> sh, 1);
+        int c = 0;
+        for (; c + 8 <= m_lo; c += 8) {                    // eight independent L2 requests in flight
+            uint32_t t[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) t[q] = __ldg(w + (c + q) * plane);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) lo = __funnelshift_r(lo, t[q] >> sh, 1);
+        }
+        for (; c < m_lo; ++c) lo = __funnelshift_r(lo, __ldg(w + c * plane) >> sh, 1);
         lo >>= (32 - m_lo);
         if (M > 32) {
             for (int c = 32; c < M; ++c) hi = __funnelshift_r(hi, __ldg(w + c * plane) >> sh, 1);
@@ -167,16 +175,29 @@ __device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArg
     }
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Warp-specialised: warp 8 only issues bulk copies (one elected lane), warps 0-7
+// consume.  A stage holds 32 groups of 32 points; consumer warps take groups in
+// order from a shared counter (frustum points cluster in runs of a few hundred,
+// so a static split leaves most warps idle at a block barrier), copy their point
+// to a register, release the group on the stage's "empty" mbarrier and compute.
+// No block-wide barrier inside the streaming loop.
 __global__ void __launch_bounds__(FUSE_THREADS, 3)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[FUSE_STAGES];
+    __shared__ int s_ctr;
     const int f = blockIdx.y;
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
     const int64_t seg0 = p0 + (int64_t)blockIdx.x * FUSE_SEG;
     if (seg0 >= p1) return;
     const int npts = (int)min((int64_t)FUSE_SEG, p1 - seg0);
     const int nsub = (npts + FUSE_SUB - 1) / FUSE_SUB;
+    const int ngroups = (npts + 31) / 32;
     const int m0 = A.mask_off[f];
     const int M = A.mask_off[f + 1] - m0;
     const int b0 = A.box_off[f];
@@ -189,13 +210,18 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
     int32_t* s_total = s_nin + A.smem_boxes;
     int32_t* s_nvalid = s_total + A.smem_cars;
     const float4* src = A.pts + seg0;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < FUSE_STAGES; ++s) mbar_init(&full_bar[s], 1);
+        for (int s = 0; s < FUSE_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], FUSE_GROUPS);
+        }
+        s_ctr = 0;
         mbar_fence_init();
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (warp == FUSE_CONSUMERS && lane == 0) {
         for (int i = 0; i < FUSE_STAGES && i < nsub; ++i) {
             const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
             mbar_expect_tx(&full_bar[i], bytes);
@@ -212,39 +238,40 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
     }
     __syncthreads();
 
-    const int lane = threadIdx.x & 31;
-    const int64_t plane = (int64_t)cam.H * cam.wpr;
-    const uint32_t* mask_base = A.packed + (int64_t)m0 * plane;
-    int my_valid = 0;
-
-    for (int i = 0; i < nsub; ++i) {
-        const int s = i % FUSE_STAGES;
-        mbar_wait(&full_bar[s], (uint32_t)((i / FUSE_STAGES) & 1));
-        const int nhere = min(FUSE_SUB, npts - i * FUSE_SUB);
-        float4 p[FUSE_PPT];
-#pragma unroll
-        for (int j = 0; j < FUSE_PPT; ++j) {
-            const int k = j * FUSE_THREADS + threadIdx.x;
-            p[j] = k < nhere ? stage[s * FUSE_SUB + k] : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (warp == FUSE_CONSUMERS) {
+        if (lane == 0) {                                   // producer: refill a stage once all its groups were read
+            for (int i = FUSE_STAGES; i < nsub; ++i) {
+                const int s = i % FUSE_STAGES;
+                mbar_wait(&empty_bar[s], (uint32_t)((i / FUSE_STAGES - 1) & 1));
+                const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
+                fence_proxy_async_smem();
+                mbar_expect_tx(&full_bar[s], bytes);
+                bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)i * FUSE_SUB, bytes, &full_bar[s]);
+            }
         }
-        __syncthreads();                                   // stage s is in registers everywhere
-        if (threadIdx.x == 0 && i + FUSE_STAGES < nsub) {
-            const int jn = i + FUSE_STAGES;
-            const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - jn * FUSE_SUB) * 16u;
-            fence_proxy_async_smem();
-            mbar_expect_tx(&full_bar[s], bytes);
-            bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)jn * FUSE_SUB, bytes, &full_bar[s]);
+    } else {
+        const int64_t plane = (int64_t)cam.H * cam.wpr;
+        const uint32_t* mask_base = A.packed + (int64_t)m0 * plane;
+        int my_valid = 0;
+        for (;;) {
+            int g = 0;
+            if (lane == 0) g = atomicAdd(&s_ctr, 1);
+            g = __shfl_sync(0xFFFFFFFFu, g, 0);
+            if (g >= ngroups) break;
+            const int sub = g / FUSE_GROUPS, grp = g - sub * FUSE_GROUPS;
+            const int s = sub % FUSE_STAGES;
+            mbar_wait(&full_bar[s], (uint32_t)((sub / FUSE_STAGES) & 1));
+            const int k = g * 32 + lane;                   // point index inside the segment
+            const bool live = k < npts;
+            const float4 p = live ? stage[s * FUSE_SUB + grp * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);
+            fuse_warp_points(cam, A, p, live, seg0 + k, lane, M, B, mask_base, plane, s_box, s_inside, s_nin,
+                             s_total, my_valid);
         }
-#pragma unroll
-        for (int j = 0; j < FUSE_PPT; ++j) {
-            const int k = j * FUSE_THREADS + threadIdx.x;
-            fuse_warp_points(cam, A, p[j], k < nhere, seg0 + (int64_t)i * FUSE_SUB + k, lane, M, B, mask_base,
-                             plane, s_box, s_inside, s_nin, s_total, my_valid);
-        }
+        const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
+        if (lane == 0 && vb) atomicAdd(s_nvalid, (int)vb);
     }
-
-    const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
-    if (lane == 0 && vb) atomicAdd(s_nvalid, (int)vb);
     __syncthreads();
     for (int i = threadIdx.x; i < M * B; i += FUSE_THREADS) {
         const int c = i / B, b = i - c * B;
