@@ -11,7 +11,9 @@ struct LfCam {
     double T[12];   // rows 0..2 of the 4x4 velo->rect transform
     double K[9];    // K[:3,:3]
     int W, H, wpr;  // image size, packed words per row
-    int pad;
+    float depth_tol;   // relative slack of the fp32 depth pre-gate (see fuse.cu)
+    float Tf[12];   // float copies for that pre-gate only: never decide anything exact
+    float Kf[4];    // K row 2
 };
 
 struct lf_ctx {

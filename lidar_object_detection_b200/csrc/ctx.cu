@@ -56,6 +56,14 @@ extern "C" int lf_set_camera(lf_ctx* ctx, const double TrVeloToRect[16], const d
     ctx->cam.W = W;
     ctx->cam.H = H;
     ctx->cam.wpr = (W + 31) / 32;
+    // fp32 copies for the depth pre-gate of the fused kernel.  Its slack is relative to
+    // |x|+|y|+|z|+1 and scaled by the size of the coefficients involved.
+    double cmax = 1.0;
+    for (int i = 0; i < 12; ++i) { ctx->cam.Tf[i] = (float)TrVeloToRect[i]; cmax = fmax(cmax, fabs(TrVeloToRect[i])); }
+    double kmax = 0.0;
+    for (int c = 0; c < 3; ++c) { ctx->cam.Kf[c] = (float)K[8 + c]; kmax += fabs(K[8 + c]); }
+    ctx->cam.Kf[3] = 0.f;
+    ctx->cam.depth_tol = (float)(64.0 * 1.2e-7 * cmax * fmax(kmax, 1.0) * 4.0);
     ctx->has_camera = 1;
     return LF_OK;
 }

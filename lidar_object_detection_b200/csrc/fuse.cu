@@ -18,7 +18,7 @@ constexpr int FUSE_CONSUMERS = 8;                         // consumer warps
 constexpr int FUSE_THREADS = 32 * (FUSE_CONSUMERS + 1);   // + one producer warp (bulk-copy issue)
 constexpr int FUSE_SUB = 1024;                            // points per stage = 16 KB
 constexpr int FUSE_GROUPS = FUSE_SUB / 32;                // 32-point groups per stage, handed out dynamically
-constexpr int FUSE_STAGES = 3;
+constexpr int FUSE_STAGES = 4;                            // power of two: stage / parity by shifts
 constexpr int FUSE_SUBS_PER_SEG = 16;
 constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 16384 points per CTA
 
@@ -47,13 +47,16 @@ __device__ __forceinline__ unsigned long long warp_or64(unsigned long long v) {
     return ((unsigned long long)hi << 32) | lo;
 }
 
-// float <-> unsigned key with the same ordering (for warp min / max reductions)
-__device__ __forceinline__ unsigned f2key(float f) {
-    const unsigned b = __float_as_uint(f);
-    return b ^ ((unsigned)((int)b >> 31) | 0x80000000u);
+// warp-wide float min / max in one instruction (redux.sync.f32 is sm_100a-only; SASS CREDUX)
+__device__ __forceinline__ float warp_min_f32(float v) {
+    float r;
+    asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+    return r;
 }
-__device__ __forceinline__ float key2f(unsigned k) {
-    return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
+__device__ __forceinline__ float warp_max_f32(float v) {
+    float r;
+    asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+    return r;
 }
 
 // closed-interval slab test 0 <= dot(rel,e)/ee <= 1 (cvs_erosion.py:133-138).
@@ -86,14 +89,38 @@ __device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArg
                                                  int64_t plane, const lf_box* s_box, int32_t* s_inside,
                                                  int32_t* s_nin, int32_t* s_total, int& my_valid) {
     const unsigned FULL = 0xFFFFFFFFu;
-    double qx, qy, d;
-    lf_project_xyd(cam, p.x, p.y, p.z, qx, qy, d);
-    const bool front = live && d > 0.0 && d < A.max_depth;            // depth half of cvs_erosion.py:359
+    // fp32 look at the depth: points certainly behind the camera or certainly beyond the
+    // range gate never reach the fp64 chain.  The margin covers the fp32 evaluation error
+    // (a few ulp of the largest term); NaN compares false and takes the exact path.
+    bool maybe = live;
+    {
+        float dmax32 = (float)A.max_depth;
+        dmax32 += fabsf(dmax32) * 1e-6f;                               // the cast may round down
+        const float px = fmaf(cam.Tf[0], p.x, fmaf(cam.Tf[1], p.y, fmaf(cam.Tf[2], p.z, cam.Tf[3])));
+        const float py = fmaf(cam.Tf[4], p.x, fmaf(cam.Tf[5], p.y, fmaf(cam.Tf[6], p.z, cam.Tf[7])));
+        const float pz = fmaf(cam.Tf[8], p.x, fmaf(cam.Tf[9], p.y, fmaf(cam.Tf[10], p.z, cam.Tf[11])));
+        const float d32 = fmaf(cam.Kf[0], px, fmaf(cam.Kf[1], py, cam.Kf[2] * pz));
+        const float mag = fabsf(p.x) + fabsf(p.y) + fabsf(p.z) + 1.0f;
+        const float tol = cam.depth_tol * mag;
+        if (d32 < -tol || d32 > dmax32 + tol) maybe = false;
+    }
     bool valid = false;
     double uq = 0.0, vq = 0.0;
-    if (__any_sync(FULL, front)) {
+    if (__any_sync(FULL, maybe)) {
+        double qx, qy, d;
+        lf_project_xyd(cam, p.x, p.y, p.z, qx, qy, d);
+        const bool front = maybe && d > 0.0 && d < A.max_depth;        // depth half of cvs_erosion.py:359
         if (front) {
-            lf_project_uv(qx, qy, d, uq, vq);
+            // u = rint(qx / d): one reciprocal instead of two divisions.  q~ = qx * (1/d) is
+            // within 2 ulp of the correctly rounded quotient, so rint() agrees unless q~ sits
+            // within |q~| * 2^-50 of a half-integer; only then the exact division decides.
+            const double r = __drcp_rn(d);
+            const double qu = __dmul_rn(qx, r), qv = __dmul_rn(qy, r);
+            uq = rint(qu);
+            vq = rint(qv);
+            const double eu = fabs(fabs(qu - uq) - 0.5), ev = fabs(fabs(qv - vq) - 0.5);
+            if (eu <= fabs(qu) * 8.9e-16 + 1e-300) uq = rint(__ddiv_rn(qx, d));
+            if (ev <= fabs(qv) * 8.9e-16 + 1e-300) vq = rint(__ddiv_rn(qy, d));
             valid = (uq >= 0.0) && (uq < (double)cam.W) && (vq >= 0.0) && (vq < (double)cam.H);
         }
     }
@@ -138,12 +165,9 @@ __device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArg
     if (B == 0) return;
     // ---- warp bounding box of the valid points, then lanes test boxes in parallel
     const float INF = __int_as_float(0x7f800000);
-    const float wx0 = key2f(__reduce_min_sync(FULL, f2key(valid ? p.x : INF)));
-    const float wx1 = key2f(__reduce_max_sync(FULL, f2key(valid ? p.x : -INF)));
-    const float wy0 = key2f(__reduce_min_sync(FULL, f2key(valid ? p.y : INF)));
-    const float wy1 = key2f(__reduce_max_sync(FULL, f2key(valid ? p.y : -INF)));
-    const float wz0 = key2f(__reduce_min_sync(FULL, f2key(valid ? p.z : INF)));
-    const float wz1 = key2f(__reduce_max_sync(FULL, f2key(valid ? p.z : -INF)));
+    const float wx0 = warp_min_f32(valid ? p.x : INF), wx1 = warp_max_f32(valid ? p.x : -INF);
+    const float wy0 = warp_min_f32(valid ? p.y : INF), wy1 = warp_max_f32(valid ? p.y : -INF);
+    const float wz0 = warp_min_f32(valid ? p.z : INF), wz1 = warp_max_f32(valid ? p.z : -INF);
     for (int g = 0; g < B; g += 32) {
         const int bl = g + lane;
         bool cand = false;
@@ -190,7 +214,6 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[FUSE_STAGES];
-    __shared__ int s_ctr;
     const int f = blockIdx.y;
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
     const int64_t seg0 = p0 + (int64_t)blockIdx.x * FUSE_SEG;
@@ -217,7 +240,6 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], FUSE_GROUPS);
         }
-        s_ctr = 0;
         mbar_fence_init();
     }
     __syncthreads();
@@ -253,13 +275,11 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
         const int64_t plane = (int64_t)cam.H * cam.wpr;
         const uint32_t* mask_base = A.packed + (int64_t)m0 * plane;
         int my_valid = 0;
-        for (;;) {
-            int g = 0;
-            if (lane == 0) g = atomicAdd(&s_ctr, 1);
-            g = __shfl_sync(0xFFFFFFFFu, g, 0);
-            if (g >= ngroups) break;
-            const int sub = g / FUSE_GROUPS, grp = g - sub * FUSE_GROUPS;
-            const int s = sub % FUSE_STAGES;
+        // groups are dealt round-robin: frustum points come in runs of a few hundred, so
+        // every warp gets its share of the expensive ones
+        for (int g = warp; g < ngroups; g += FUSE_CONSUMERS) {
+            const int sub = g / FUSE_GROUPS, grp = g & (FUSE_GROUPS - 1);
+            const int s = sub & (FUSE_STAGES - 1);
             mbar_wait(&full_bar[s], (uint32_t)((sub / FUSE_STAGES) & 1));
             const int k = g * 32 + lane;                   // point index inside the segment
             const bool live = k < npts;
