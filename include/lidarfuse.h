@@ -94,10 +94,14 @@ int lf_project(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, doubl
  * V2 no-erosion variant, V2:197-200).
  * mode: 0 = uint8 masks, non-zero = set; 1 = float32 masks, >= 1.0 = set (the
  * uint8 truncation of cvs_erosion.py:101 and V2:197); 2 = float32 masks,
- * > 0.5 = set (seg_with_pointcloud.py:167). */
+ * > 0.5 = set (seg_with_pointcloud.py:167).
+ * bbox (optional): per mask the bounding box of the set pixels of the result,
+ * encoded {2^20 - x0, 2^20 - y0, x1 + 1, y1 + 1} (all zero = empty mask); it
+ * lets lf_fuse_batch skip masks a group of points cannot touch. */
 int lf_erode_pack(lf_ctx* ctx, const void* masks /*DEVICE [m][H][W]*/, int mode, int64_t m,
                   int H, int W, const uint8_t* se /*HOST [k][k]*/, int k, int iterations,
-                  uint32_t* packed /*DEVICE [m][H][wpr]*/, void* stream);
+                  uint32_t* packed /*DEVICE [m][H][wpr]*/,
+                  int32_t* bbox /*DEVICE [m][4], zeroed by the caller, or NULL*/, void* stream);
 
 /* packed -> uint8 0/1 images (the eroded masks the reference keeps as float32,
  * cvs_erosion.py:103). */
@@ -122,7 +126,9 @@ int lf_prepare_boxes(const double* corners_velo /*HOST [n][8][3]*/, int64_t n, l
  *   car_bits           optional DEVICE uint64 [total points]: bit c = point in mask c of its frame
  *                      (0 for gated-out points); may be NULL                                       */
 int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
-                  const uint32_t* packed /*DEVICE*/, const int32_t* mask_off /*DEVICE [F+1]*/,
+                  const uint32_t* packed /*DEVICE*/,
+                  const int32_t* mask_bbox /*DEVICE [sum M][4] from lf_erode_pack, 16-B aligned, or NULL*/,
+                  const int32_t* mask_off /*DEVICE [F+1]*/,
                   const lf_box* boxes /*DEVICE*/, const int32_t* box_off /*DEVICE [F+1]*/,
                   const int64_t* cnt_off /*DEVICE [F+1]*/, int F, int64_t max_points_per_frame,
                   int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,

@@ -32,10 +32,10 @@ SIGNATURES = {
     'lf_last_cuda_error': (C.c_int, [_vp]),
     'lf_set_camera': (C.c_int, [_vp, _vp, _vp, _i32, _i32]),
     'lf_project': (C.c_int, [_vp, _vp, _i64, _f64, _vp, _vp, _vp, _vp, _vp]),
-    'lf_erode_pack': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp]),
+    'lf_erode_pack': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp]),
     'lf_unpack_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
-    'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
+    'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp]),
     'lf_mask_gather': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp]),
     'lf_points_in_box': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _i32, _vp, _vp]),

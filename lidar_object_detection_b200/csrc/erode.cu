@@ -32,6 +32,30 @@ struct ErodeParams {
     signed char span_b[LF_MAX_SE];
 };
 
+// Bounding box of the set pixels of the (eroded) mask, kept per thread while the
+// packed words go out and merged with four atomics per CTA.  Stored so that an
+// all-zero record means "empty": {2^20 - x0, 2^20 - y0, x1 + 1, y1 + 1}, all
+// combined with atomicMax.  The fused point pass uses it to skip masks whose
+// silhouette the points of a warp cannot touch.
+struct BBoxAcc {
+    int nx0, ny0, x1, y1;
+    __device__ __forceinline__ BBoxAcc() : nx0(0), ny0(0), x1(0), y1(0) {}
+    __device__ __forceinline__ void add(uint32_t w, int row, int wx) {
+        if (!w) return;
+        nx0 = max(nx0, (1 << 20) - (32 * wx + __ffs((int)w) - 1));
+        x1 = max(x1, 32 * wx + 32 - __clz((int)w));
+        ny0 = max(ny0, (1 << 20) - row);
+        y1 = max(y1, row + 1);
+    }
+    __device__ __forceinline__ void flush(int32_t* bbox) {
+        const int a = __reduce_max_sync(0xFFFFFFFFu, nx0), b = __reduce_max_sync(0xFFFFFFFFu, ny0);
+        const int c = __reduce_max_sync(0xFFFFFFFFu, x1), d = __reduce_max_sync(0xFFFFFFFFu, y1);
+        if ((threadIdx.x & 31) == 0 && c > 0) {
+            atomicMax(bbox + 0, a); atomicMax(bbox + 1, b); atomicMax(bbox + 2, c); atomicMax(bbox + 3, d);
+        }
+    }
+};
+
 // 4 bytes -> 4 bits (bit j = byte j non-zero), returned in bits 28..31.
 __device__ __forceinline__ uint32_t nz_nibble_hi(uint32_t w) {
     const uint32_t t = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;   // bit 7 of each byte = byte != 0
@@ -148,7 +172,8 @@ __device__ __forceinline__ void erode_dispatch(const ErodeParams& P, const uint3
 }
 
 __device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* bufA, uint32_t* bufB, int ga,
-                                                int gb, int r0, int r1, uint32_t* __restrict__ out_mask) {
+                                                int gb, int r0, int r1, uint32_t* __restrict__ out_mask,
+                                                int32_t* bbox) {
     uint32_t* cur = bufA;
     uint32_t* nxt = bufB;
     for (int itn = 0; itn < P.iterations; ++itn) {
@@ -161,11 +186,15 @@ __device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* 
     const int items = (r1 - r0) * P.wpr;
     const uint32_t* srcw = cur + (r0 - ga) * P.wpr;
     uint32_t* dstw = out_mask + (int64_t)r0 * P.wpr;
+    BBoxAcc acc;
     for (int it = threadIdx.x; it < items; it += ER_THREADS) {
         uint32_t w = srcw[it];
-        if (keep != 0xFFFFFFFFu && (it - (int)__umulhi((unsigned)it, P.wpr_magic) * P.wpr) == P.wpr - 1) w &= keep;
+        const int lr = (int)__umulhi((unsigned)it, P.wpr_magic), wx = it - lr * P.wpr;
+        if (wx == P.wpr - 1) w &= keep;
         dstw[it] = w;
+        acc.add(w, r0 + lr, wx);
     }
+    if (bbox) acc.flush(bbox);
 }
 
 __device__ __forceinline__ void strip_rows(const ErodeParams& P, int strip, int& r0, int& r1, int& ga, int& gb) {
@@ -180,7 +209,7 @@ __device__ __forceinline__ void strip_rows(const ErodeParams& P, int strip, int&
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(ER_THREADS)
 lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __restrict__ masks,
-                     uint32_t* __restrict__ packed) {
+                     uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[ER_STAGES];
     uint8_t* stage = smem;
@@ -241,7 +270,8 @@ lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
         if (off0 < L) bufA[off0 >> 5] = pack32(a0, a1);
         if (off1 < L) bufA[off1 >> 5] = pack32(b0, b1);
     }
-    erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr);
+    erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr,
+                    bbox ? bbox + 4 * mask : nullptr);
 }
 
 // ---------------------------------------------------------------------------
@@ -271,7 +301,7 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 template <class SE>
 __global__ void __launch_bounds__(ER_THREADS)
 lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __restrict__ masks,
-                     uint32_t* __restrict__ packed) {
+                     uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
     constexpr int K = SE::k, RAD = K / 2;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[ER_STAGES];
@@ -375,8 +405,32 @@ lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
     uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
     const int out_items = (r1 - r0) * P.wpr;
     const int skip = (r0 - ga) * S;
-    for (int it = tid; it < out_items; it += ER_THREADS)
-        dstw[it] = cur[it + (int)__umulhi((unsigned)it, P.wpr_magic) + data0 + skip];
+    BBoxAcc acc;
+    if ((P.wpr & 3) == 0) {
+        // four words per thread: one 128-bit store, one bounding-box test per 128 pixels
+        const int qpr = P.wpr >> 2;                        // quads per row
+        const unsigned qmagic = (unsigned)((0x100000000ULL + qpr - 1) / qpr);
+        const int nq = (r1 - r0) * qpr;
+        for (int q = tid; q < nq; q += ER_THREADS) {
+            const int lr = (int)__umulhi((unsigned)q, qmagic);
+            const int wq = q - lr * qpr;
+            const uint32_t* sp = cur + lr * S + 4 * wq + data0 + skip;
+            const uint4 v = make_uint4(sp[0], sp[1], sp[2], sp[3]);
+            *(uint4*)(dstw + 4 * q) = v;
+            if (v.x | v.y | v.z | v.w) {
+                acc.add(v.x, r0 + lr, 4 * wq); acc.add(v.y, r0 + lr, 4 * wq + 1);
+                acc.add(v.z, r0 + lr, 4 * wq + 2); acc.add(v.w, r0 + lr, 4 * wq + 3);
+            }
+        }
+    } else {
+        for (int it = tid; it < out_items; it += ER_THREADS) {
+            const int lr = (int)__umulhi((unsigned)it, P.wpr_magic);
+            const uint32_t w = cur[it + lr + data0 + skip];
+            dstw[it] = w;
+            acc.add(w, r0 + lr, it - lr * P.wpr);
+        }
+    }
+    if (bbox) acc.flush(bbox + 4 * mask);
 }
 
 typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)
@@ -398,12 +452,12 @@ bool se_matches(const ErodeParams& P) {
 }
 
 template <class SE>
-cudaError_t launch_fast(const ErodeParams& P, const uint8_t* masks, uint32_t* packed, unsigned grid, size_t smem,
-                        cudaStream_t s) {
+cudaError_t launch_fast(const ErodeParams& P, const uint8_t* masks, uint32_t* packed, int32_t* bbox, unsigned grid,
+                        size_t smem, cudaStream_t s) {
     cudaError_t e = cudaFuncSetAttribute(lf_erode_fast_kernel<SE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return e;
-    lf_erode_fast_kernel<SE><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+    lf_erode_fast_kernel<SE><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
     return cudaGetLastError();
 }
 
@@ -418,7 +472,7 @@ template <> struct MaskElem<2> { typedef float type; };
 template <int MODE>
 __global__ void __launch_bounds__(ER_THREADS)
 lf_erode_generic_kernel(const __grid_constant__ ErodeParams P, const void* __restrict__ masks_v,
-                        uint32_t* __restrict__ packed) {
+                        uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
     typedef typename MaskElem<MODE>::type T;
     extern __shared__ __align__(128) uint8_t smem[];
     uint32_t* bufA = (uint32_t*)smem;
@@ -445,7 +499,8 @@ lf_erode_generic_kernel(const __grid_constant__ ErodeParams P, const void* __res
         const uint32_t w = __ballot_sync(0xFFFFFFFFu, bit);
         if (lane == 0) bufA[it] = w;
     }
-    erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr);
+    erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr,
+                    bbox ? bbox + 4 * mask : nullptr);
 }
 
 __global__ void lf_unpack_kernel(const uint32_t* __restrict__ packed, int64_t total_px, int H, int W, int wpr,
@@ -464,7 +519,8 @@ __global__ void lf_unpack_kernel(const uint32_t* __restrict__ packed, int64_t to
 }  // namespace
 
 extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
-                             const uint8_t* se, int k, int iterations, uint32_t* packed, void* stream) {
+                             const uint8_t* se, int k, int iterations, uint32_t* packed, int32_t* bbox,
+                             void* stream) {
     if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 2) return LF_E_ARG;
     if (m > 0 && (!masks || !packed)) return LF_E_ARG;
     if (iterations > 0 && (!se || k < 1 || (k & 1) == 0)) return LF_E_ARG;
@@ -540,15 +596,15 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
         const uint8_t* mk = (const uint8_t*)masks;
         cudaError_t e;
         switch (spec) {
-            case 0: e = launch_fast<SeNone>(P, mk, packed, grid, smem, s); break;
-            case 1: e = launch_fast<SeCross3>(P, mk, packed, grid, smem, s); break;
-            case 2: e = launch_fast<SeRect3>(P, mk, packed, grid, smem, s); break;
-            case 3: e = launch_fast<SeEllipse5>(P, mk, packed, grid, smem, s); break;
-            case 4: e = launch_fast<SeRect5>(P, mk, packed, grid, smem, s); break;
-            case 5: e = launch_fast<SeCross5>(P, mk, packed, grid, smem, s); break;
-            case 6: e = launch_fast<SeEllipse7>(P, mk, packed, grid, smem, s); break;
-            case 7: e = launch_fast<SeRect7>(P, mk, packed, grid, smem, s); break;
-            default: e = launch_fast<SeCross7>(P, mk, packed, grid, smem, s); break;
+            case 0: e = launch_fast<SeNone>(P, mk, packed, bbox, grid, smem, s); break;
+            case 1: e = launch_fast<SeCross3>(P, mk, packed, bbox, grid, smem, s); break;
+            case 2: e = launch_fast<SeRect3>(P, mk, packed, bbox, grid, smem, s); break;
+            case 3: e = launch_fast<SeEllipse5>(P, mk, packed, bbox, grid, smem, s); break;
+            case 4: e = launch_fast<SeRect5>(P, mk, packed, bbox, grid, smem, s); break;
+            case 5: e = launch_fast<SeCross5>(P, mk, packed, bbox, grid, smem, s); break;
+            case 6: e = launch_fast<SeEllipse7>(P, mk, packed, bbox, grid, smem, s); break;
+            case 7: e = launch_fast<SeRect7>(P, mk, packed, bbox, grid, smem, s); break;
+            default: e = launch_fast<SeCross7>(P, mk, packed, bbox, grid, smem, s); break;
         }
         LF_CUDA(ctx, e);
         return LF_OK;
@@ -556,19 +612,19 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
     if (fast) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)smem));
-        lf_erode_bulk_kernel<<<grid, ER_THREADS, smem, s>>>(P, (const uint8_t*)masks, packed);
+        lf_erode_bulk_kernel<<<grid, ER_THREADS, smem, s>>>(P, (const uint8_t*)masks, packed, bbox);
     } else if (mode == 0) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<0>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        lf_erode_generic_kernel<0><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+        lf_erode_generic_kernel<0><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
     } else if (mode == 1) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<1>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        lf_erode_generic_kernel<1><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+        lf_erode_generic_kernel<1><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
     } else {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<2>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        lf_erode_generic_kernel<2><<<grid, ER_THREADS, smem, s>>>(P, masks, packed);
+        lf_erode_generic_kernel<2><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
     }
     LF_CUDA(ctx, cudaGetLastError());
     return LF_OK;

@@ -26,6 +26,7 @@ struct FuseArgs {
     const float4* pts;
     const int64_t* pt_off;
     const uint32_t* packed;
+    const int32_t* mask_bbox;   // optional [sum M][4] from lf_erode_pack, NULL = test every mask
     const int32_t* mask_off;
     const lf_box* boxes;
     const int32_t* box_off;
@@ -85,8 +86,8 @@ __device__ __forceinline__ bool point_in_box(const lf_box& bx, float x, float y,
 
 // Everything one warp does for 32 consecutive points (one per lane).
 __device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArgs& A, float4 p, bool live,
-                                                 int64_t gidx, int lane, int M, int B, const uint32_t* mask_base,
-                                                 int64_t plane, const lf_box* s_box, int32_t* s_inside,
+                                                 int64_t gidx, int lane, int M, int B, int m0, const uint32_t* mask_base,
+                                                 int plane32, const lf_box* s_box, int32_t* s_inside,
                                                  int32_t* s_nin, int32_t* s_total, int& my_valid) {
     const unsigned FULL = 0xFFFFFFFFu;
     // fp32 look at the depth: points certainly behind the camera or certainly beyond the
@@ -131,28 +132,38 @@ __device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArg
     }
     my_valid += valid ? 1 : 0;
     // ---- K4: point-in-mask gather (cvs_erosion.py:152-160) ---------------------
+    // Lanes first test the masks' bounding boxes against the pixel bounds of the warp's
+    // valid points (one mask per lane); only the surviving masks are read.
     unsigned long long bits = 0ULL;
-    if (valid && M > 0) {
-        const int ui = (int)uq, vi = (int)vq;
-        const uint32_t* w = mask_base + (int64_t)vi * cam.wpr + (ui >> 5);
+    if (M > 0) {
+        const int ui = valid ? (int)uq : 0, vi = valid ? (int)vq : 0;
+        const int off = vi * cam.wpr + (ui >> 5);            // word offset inside one packed mask
         const int sh = ui & 31;
-        unsigned lo = 0u, hi = 0u;
-        const int m_lo = min(M, 32);
-        int c = 0;
-        for (; c + 8 <= m_lo; c += 8) {                    // eight independent L2 requests in flight
-            uint32_t t[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) t[q] = __ldg(w + (c + q) * plane);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) lo = __funnelshift_r(lo, t[q] >> sh, 1);
+        int u0 = 0, u1 = 0, v0 = 0, v1 = 0;
+        if (A.mask_bbox) {
+            u0 = __reduce_min_sync(FULL, valid ? ui : 0x7fffffff);
+            u1 = __reduce_max_sync(FULL, valid ? ui : -1);
+            v0 = __reduce_min_sync(FULL, valid ? vi : 0x7fffffff);
+            v1 = __reduce_max_sync(FULL, valid ? vi : -1);
         }
-        for (; c < m_lo; ++c) lo = __funnelshift_r(lo, __ldg(w + c * plane) >> sh, 1);
-        lo >>= (32 - m_lo);
-        if (M > 32) {
-            for (int c = 32; c < M; ++c) hi = __funnelshift_r(hi, __ldg(w + c * plane) >> sh, 1);
-            hi >>= (64 - M);
+        for (int g = 0; g < M; g += 32) {
+            const int cl = g + lane;
+            bool cand = cl < M;
+            if (cand && A.mask_bbox) {
+                const int4 bb = __ldg((const int4*)A.mask_bbox + m0 + cl);
+                const int x0 = (1 << 20) - bb.x, y0 = (1 << 20) - bb.y, x1 = bb.z - 1, y1 = bb.w - 1;
+                cand = u1 >= x0 && u0 <= x1 && v1 >= y0 && v0 <= y1;
+            }
+            unsigned cmask = __ballot_sync(FULL, cand);
+            while (cmask) {
+                const int c = g + __ffs((int)cmask) - 1;
+                cmask &= cmask - 1;
+                if (valid) {
+                    const uint32_t w = __ldg(mask_base + (unsigned)(off + c * plane32));
+                    bits |= (unsigned long long)((w >> sh) & 1u) << c;
+                }
+            }
         }
-        bits = ((unsigned long long)hi << 32) | lo;
     }
     if (A.car_bits && live) A.car_bits[gidx] = bits;
     unsigned long long un = warp_or64(bits);
@@ -272,8 +283,8 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
             }
         }
     } else {
-        const int64_t plane = (int64_t)cam.H * cam.wpr;
-        const uint32_t* mask_base = A.packed + (int64_t)m0 * plane;
+        const int plane32 = cam.H * cam.wpr;               // words per packed mask (< 2^25, see lf_set_camera)
+        const uint32_t* mask_base = A.packed + (int64_t)m0 * plane32;
         int my_valid = 0;
         // groups are dealt round-robin: frustum points come in runs of a few hundred, so
         // every warp gets its share of the expensive ones
@@ -286,7 +297,7 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
             const float4 p = live ? stage[s * FUSE_SUB + grp * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
-            fuse_warp_points(cam, A, p, live, seg0 + k, lane, M, B, mask_base, plane, s_box, s_inside, s_nin,
+            fuse_warp_points(cam, A, p, live, seg0 + k, lane, M, B, m0, mask_base, plane32, s_box, s_inside, s_nin,
                              s_total, my_valid);
         }
         const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
@@ -360,7 +371,7 @@ lf_car_stats_kernel(const int32_t* __restrict__ total, const int32_t* __restrict
 }  // namespace
 
 extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const uint32_t* packed,
-                             const int32_t* mask_off, const lf_box* boxes, const int32_t* box_off,
+                             const int32_t* mask_bbox, const int32_t* mask_off, const lf_box* boxes, const int32_t* box_off,
                              const int64_t* cnt_off, int F, int64_t max_points_per_frame,
                              int max_masks_per_frame, int max_boxes_per_frame, double max_depth,
                              int use_oriented, int32_t* total, int32_t* inside, int32_t* n_in_box,
@@ -373,12 +384,13 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
         return LF_E_ARG;
     if (max_masks_per_frame > 0 && !packed) return LF_E_ARG;
     if (max_boxes_per_frame > 0 && !boxes) return LF_E_ARG;
-    if (((uintptr_t)pts & 15) != 0) return LF_E_ARG;
+    if (((uintptr_t)pts & 15) != 0 || ((uintptr_t)mask_bbox & 15) != 0) return LF_E_ARG;
+    if ((int64_t)ctx->cam.H * ctx->cam.wpr * LF_MAX_CARS >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
     if (F > 65535) return LF_E_UNSUPPORTED;      // gridDim.y; callers split larger batches
     LF_CUDA(ctx, cudaSetDevice(ctx->device));
 
     FuseArgs A;
-    A.pts = (const float4*)pts; A.pt_off = pt_off; A.packed = packed; A.mask_off = mask_off;
+    A.pts = (const float4*)pts; A.pt_off = pt_off; A.packed = packed; A.mask_bbox = mask_bbox; A.mask_off = mask_off;
     A.boxes = boxes; A.box_off = box_off; A.cnt_off = cnt_off;
     A.total = total; A.inside = inside; A.n_in_box = n_in_box; A.n_valid = n_valid;
     A.car_bits = (unsigned long long*)car_bits;

@@ -155,8 +155,9 @@ def structuring_element(shape, ksize):
 class PackedMasks:
     """Bit-packed instance masks on the device: uint32 [M, H, ceil(W/32)]."""
 
-    def __init__(self, words, H, W):
+    def __init__(self, words, H, W, bbox=None):
         self.words, self.H, self.W = words, H, W
+        self.bbox = bbox        # int32 [M,4] {2^20-x0, 2^20-y0, x1+1, y1+1} (zeros = empty) or None
 
     def __len__(self):
         return self.words.shape[0]
@@ -209,8 +210,10 @@ def erode_pack(masks, erosion_kernel_size=3, erosion_iterations=1, shape=MORPH_E
         se_ptr = se_arr.ctypes.data
     else:
         se_arr, k, se_ptr = None, 1, None
-    check(ctx.lib.lf_erode_pack(ctx.h, ptr(t), mode, M, H, W, se_ptr, k, iters, ptr(words), ctx.stream), ctx.h)
-    return PackedMasks(words, H, W)
+    bbox = torch.zeros((M, 4), dtype=torch.int32, device=ctx.device)
+    check(ctx.lib.lf_erode_pack(ctx.h, ptr(t), mode, M, H, W, se_ptr, k, iters, ptr(words), ptr(bbox), ctx.stream),
+          ctx.h)
+    return PackedMasks(words, H, W, bbox)
 
 
 def erode_masks(masks, erosion_kernel_size=3, erosion_iterations=1, shape=MORPH_ELLIPSE, device=None):
@@ -512,14 +515,18 @@ class FrameBatch:
         self.max_m = int(n_masks.max()) if self.F else 0
         self.max_b = int(n_boxes.max()) if self.F else 0
         sm, sb, sc = int(n_masks.sum()), int(n_boxes.sum()), int(self.h_cnt_off[-1])
-        # one allocation for everything the step zeroes: total | n_in_box | n_valid | inside | agg(int64 x8)
-        self._nz = sm + sb + self.F + sc
+        # one allocation for everything the step zeroes:
+        # mask bbox [sm,4] | total | n_in_box | n_valid | inside | agg(int64 x8)
+        self._o = 4 * sm
+        self._nz = self._o + sm + sb + self.F + sc
         self._nz += self._nz & 1
         self.counters = torch.zeros(self._nz + 16, dtype=torch.int32, device=ctx.device)
-        self.total = self.counters[:sm]
-        self.n_in_box = self.counters[sm:sm + sb]
-        self.n_valid = self.counters[sm + sb:sm + sb + self.F]
-        self.inside = self.counters[sm + sb + self.F:sm + sb + self.F + sc]
+        o = self._o
+        self.mask_bbox = self.counters[:o].view(max(sm, 0), 4) if sm else None
+        self.total = self.counters[o:o + sm]
+        self.n_in_box = self.counters[o + sm:o + sm + sb]
+        self.n_valid = self.counters[o + sm + sb:o + sm + sb + self.F]
+        self.inside = self.counters[o + sm + sb + self.F:o + sm + sb + self.F + sc]
         self.agg = self.counters[self._nz:].view(torch.int64)
         self.best_idx = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
         self.best_cnt = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
@@ -554,11 +561,12 @@ class FrameBatch:
             mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
             check(lib.lf_erode_pack(ctx.h, ptr(mt), mode, len(mt), self.camera.height, self.camera.width,
                                     se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
-                                    ptr(self.packed.words), st), ctx.h)
+                                    ptr(self.packed.words), ptr(self.mask_bbox), st), ctx.h)
             launches += 1
         mark('erode_pack')
         if self.F and self.max_n:
-            check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words),
+            bbox = self.packed.bbox if isinstance(self.masks, PackedMasks) else self.mask_bbox
+            check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
                                     ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
                                     self.F, self.max_n, self.max_m, self.max_b, float(max_depth),
                                     int(use_oriented), ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
@@ -575,7 +583,7 @@ class FrameBatch:
         """Host copies: dict of numpy arrays (one D2H of the counter block)."""
         c = self.counters.cpu().numpy()
         sm, sb, sc = int(self.h_mask_off[-1]), int(self.h_box_off[-1]), int(self.h_cnt_off[-1])
-        o = 0
+        o = self._o
         total = c[o:o + sm].astype(np.int64); o += sm
         n_in_box = c[o:o + sb].astype(np.int64); o += sb
         n_valid = c[o:o + self.F].astype(np.int64); o += self.F

@@ -388,3 +388,24 @@ def test_synthetic_batch_matches_oracle_and_invariants(LF, calib):
     sb.batch.run(7, 1, 50, 10, True)
     assert np.all(sb.batch.results()['total'] <= res['total'])
     assert np.array_equal(res0['n_valid'], res['n_valid']) and np.array_equal(res0['n_in_box'], res['n_in_box'])
+
+
+def test_mask_bounding_boxes(LF):
+    """lf_erode_pack's optional per-mask bounding box (the fused pass culls masks with it)."""
+    rng = np.random.default_rng(11)
+    for (H, W) in [(376, 1408), (50, 70)]:
+        masks = MP.random_blob_masks(rng, 6, H, W, n_blobs=2, max_r=20)
+        masks[0] = 0
+        masks[1] = 0
+        masks[1, H - 1, W - 1] = 1
+        masks[2] = 1
+        for k, it in [(0, 0), (3, 1), (5, 2)]:
+            pm = LF.erode_pack(masks, k, it)
+            got = pm.unpack().cpu().numpy()
+            bb = pm.bbox.cpu().numpy()
+            for m in range(len(masks)):
+                ys, xs = np.nonzero(got[m])
+                if len(ys) == 0:
+                    assert bb[m].tolist() == [0, 0, 0, 0]
+                else:
+                    assert bb[m].tolist() == [(1 << 20) - xs.min(), (1 << 20) - ys.min(), xs.max() + 1, ys.max() + 1]
