@@ -305,7 +305,7 @@ def run_gpu(args):
         traffic = None
         try:
             with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as fh:
-                traffic = json.load(fh).get('lf_erode_bulk_kernel_bytes_per_launch')
+                traffic = json.load(fh).get('lf_erode_fast_kernel_dram_bytes_per_launch')
         except Exception:
             pass
         line = {
@@ -323,7 +323,7 @@ def run_gpu(args):
             'step_hbm': {'algorithmic_bytes_per_step': step_bytes, 'achieved_gbs': step_bytes / (ms_step * 1e-3) / 1e9,
                          'frac_of_measured_peak': step_bytes / (ms_step * 1e-3) / 1e9 / peak,
                          'frac_of_8000_nominal': step_bytes / (ms_step * 1e-3) / 1e9 / 8000.0},
-            'roofline': {'kernel': 'lf_erode_bulk_kernel', 'bound': 'hbm', 'achieved': ach, 'peak': peak,
+            'roofline': {'kernel': 'lf_erode_fast_kernel<SeCross3> (lf_erode_pack)', 'bound': 'hbm', 'achieved': ach, 'peak': peak,
                          'unit': 'GB/s', 'frac': ach / peak, 'traffic': traffic, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': mask_bytes},
             'e2e': e2e, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,

@@ -161,3 +161,33 @@ def test_live_reference_if_present(oracle_calib):
     corners = corners - corners.mean(0)
     assert np.array_equal(ref.oriented_point_in_bbox(pts, corners), P.oriented_point_in_bbox(pts, corners))
     assert len(ref.filter_visible_bboxes(load_boxes(100), cam)) == len(P.filter_visible_bboxes(load_boxes(100), cam))
+
+
+def test_c_restatement_matches_numpy_bit_for_bit(oracle_calib):
+    """oracle/oracle_c.c (explicit fma order) == numpy/OpenBLAS on the sample frames: depth bit for bit,
+    u / v exactly; containment flags equal (they are only ULP-sensitive on a face)."""
+    import ctypes as C
+    import subprocess
+    root = os.path.join(os.path.dirname(GOLDEN), '..', 'oracle')
+    subprocess.run(['make', '-s', '-C', root], check=True)
+    lib = C.CDLL(os.path.join(root, '_build', 'liboracle_c.so'))
+    lib.oracle_project.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.oracle_oriented_in.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    cam, TVC, TVR = oracle_calib
+    for fr in (100, 2449):
+        pts = np.ascontiguousarray(load_frame(fr))
+        n = len(pts)
+        u, v, d = np.empty(n, np.int64), np.empty(n, np.int64), np.empty(n, np.float64)
+        T, K = np.ascontiguousarray(TVR), np.ascontiguousarray(cam.K)
+        lib.oracle_project(T.ctypes.data, K.ctypes.data, pts.ctypes.data, n, u.ctypes.data, v.ctypes.data,
+                           d.ctypes.data)
+        ou, ov, od = P.project_points(pts, TVR, cam)
+        assert np.array_equal(u, ou) and np.array_equal(v, ov)
+        assert np.array_equal(d, od), 'numpy/OpenBLAS on this host does not accumulate k=0..3 with fma'
+        boxes = P.transform_bboxes_to_velodyne(P.filter_visible_bboxes(load_boxes(fr), cam), TVC)
+        xyz = np.ascontiguousarray(pts[P.filter_valid(ou, ov, od, cam, 50), :3])
+        for b in boxes[:8]:
+            c = np.ascontiguousarray(np.array(b['corners_velo']))
+            got = np.empty(len(xyz), np.uint8)
+            lib.oracle_oriented_in(xyz.ctypes.data, len(xyz), c.ctypes.data, got.ctypes.data)
+            assert np.array_equal(got.astype(bool), P.oriented_point_in_bbox(xyz, c))
