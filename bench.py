@@ -339,7 +339,7 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', 0))
     if rank != 0:
         return
-    steps = min(args.steps, 60)              # ~0.4 s of CPU work per step and process
+    steps = min(args.steps, 200)             # ~70 ms of CPU work per step and process
     c = cpu_reference_throughput(steps=steps, warm=min(max(args.warmup, 1), 3))
     n_pts = RINGS * AZ
     line = {'impl': 'reference', 'metric': METRIC, 'value': c['value'], 'unit': 'points/s',
@@ -363,7 +363,8 @@ def main():
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--frames', type=int, default=FRAMES, help='frames per GPU (default: cfg3, 1024)')
-    ap.add_argument('--cpu-frames', type=int, default=2, help='frames each host process times for cpu_baseline')
+    ap.add_argument('--cpu-frames', type=int, default=20,
+                    help='frames each host process times for cpu_baseline (~70 ms each: ~1.5 s wall, ~20 core-seconds)')
     ap.add_argument('--e2e-steps', type=int, default=3)
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
