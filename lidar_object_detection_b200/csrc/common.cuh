@@ -11,9 +11,14 @@ struct LfCam {
     double T[12];   // rows 0..2 of the 4x4 velo->rect transform
     double K[9];    // K[:3,:3]
     int W, H, wpr;  // image size, packed words per row
-    float depth_tol;   // relative slack of the fp32 depth pre-gate (see fuse.cu)
-    float Tf[12];   // float copies for that pre-gate only: never decide anything exact
-    float Kf[4];    // K row 2
+    // fp32 pre-gate of the fused kernel (never decides anything exact, see fuse.cu):
+    // rows of K[:3,:3]*T with the image centre folded in.  A point with
+    // max(|x|,|y|,|z|) <= gR can only pass the gate if |Pg[0..3].p| <= hwx*d + tX,
+    // |Pg[4..7].p| <= hwy*d + tY and d = Pg[8..11].p >= -tD.
+    float Pg[12];
+    float hwx, hwy;        // (W+1)/2, (H+1)/2: half extents with a one-pixel margin
+    float tX, tY, tD;      // bounds on the fp32 evaluation error for points within gR
+    float gR;              // points beyond it skip the pre-gate (exact path decides)
 };
 
 struct lf_ctx {

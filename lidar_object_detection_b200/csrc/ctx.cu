@@ -56,14 +56,40 @@ extern "C" int lf_set_camera(lf_ctx* ctx, const double TrVeloToRect[16], const d
     ctx->cam.W = W;
     ctx->cam.H = H;
     ctx->cam.wpr = (W + 31) / 32;
-    // fp32 copies for the depth pre-gate of the fused kernel.  Its slack is relative to
-    // |x|+|y|+|z|+1 and scaled by the size of the coefficients involved.
-    double cmax = 1.0;
-    for (int i = 0; i < 12; ++i) { ctx->cam.Tf[i] = (float)TrVeloToRect[i]; cmax = fmax(cmax, fabs(TrVeloToRect[i])); }
-    double kmax = 0.0;
-    for (int c = 0; c < 3; ++c) { ctx->cam.Kf[c] = (float)K[8 + c]; kmax += fabs(K[8 + c]); }
-    ctx->cam.Kf[3] = 0.f;
-    ctx->cam.depth_tol = (float)(64.0 * 1.2e-7 * cmax * fmax(kmax, 1.0) * 4.0);
+    // fp32 pre-gate rows: P = K[:3,:3] * T (fp64), rows 0/1 shifted by the image centre
+    // ((W-1)/2, (H-1)/2) times row 2.  Error of the fp32 evaluation of one row:
+    // coefficient rounding + three fma roundings <= 4 * 2^-24 * sum|P_j||x_j|
+    // <= 4 * 2^-24 * max|P_j| * mag with mag = |x|+|y|+|z|+1; the bounds below carry a
+    // further factor 4, are taken at the gate radius gR (points beyond it bypass the
+    // pre-gate), and the x / y bounds include the effect of the depth error on the
+    // (W+1)/2 * d term.
+    double P[12];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) {
+            double a = 0.0;
+            for (int k = 0; k < 3; ++k) a += K[4 * r + k] * TrVeloToRect[4 * k + c];
+            P[4 * r + c] = a;
+        }
+    const double cxm = 0.5 * (W - 1), cym = 0.5 * (H - 1);
+    double pm[3] = {0.0, 0.0, 0.0};
+    for (int c = 0; c < 4; ++c) {
+        P[c] -= cxm * P[8 + c];
+        P[4 + c] -= cym * P[8 + c];
+    }
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) {
+            ctx->cam.Pg[4 * r + c] = (float)P[4 * r + c];
+            pm[r] = fmax(pm[r], fabs(P[4 * r + c]));
+        }
+    const double eps = 16.0 * 5.9604644775390625e-08;      // 16 * 2^-24
+    const double gR = 1024.0;                              // metres; HDL-64 range is ~120 m
+    const double mag = 3.0 * gR + 1.0;                     // >= |x|+|y|+|z|+1 inside the gate radius
+    ctx->cam.gR = (float)gR;
+    ctx->cam.hwx = (float)(0.5 * (W + 1));
+    ctx->cam.hwy = (float)(0.5 * (H + 1));
+    ctx->cam.tD = (float)(eps * fmax(pm[2], 1e-30) * mag * 1.0001);
+    ctx->cam.tX = (float)(eps * (pm[0] + (W + 2.0) * pm[2]) * mag * 1.0001 + 1e-30);
+    ctx->cam.tY = (float)(eps * (pm[1] + (H + 2.0) * pm[2]) * mag * 1.0001 + 1e-30);
     ctx->has_camera = 1;
     return LF_OK;
 }

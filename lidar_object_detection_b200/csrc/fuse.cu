@@ -84,33 +84,45 @@ __device__ __forceinline__ bool point_in_box(const lf_box& bx, float x, float y,
            Z <= bx.amax[2];
 }
 
-// Everything one warp does for 32 consecutive points (one per lane).
-__device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArgs& A, float4 p, bool live,
+// fp32 look at a point before any fp64 work (SURVEY A4 gate, cvs_erosion.py:359):
+// false only for points that CERTAINLY fail the gate -- behind the camera, beyond
+// the range limit, or more than a pixel outside the image.  The margins (LfCam
+// tX/tY/tD, lf_set_camera) cover the fp32 evaluation error for points within the
+// radius gR; farther points, NaN and inf stay "maybe", so the exact fp64 path decides
+// everything that matters.  Branch-free on purpose.
+struct PreGate {
+    float c[12], hwx, hwy, tX, tY, ntD, dhi, gR;
+    __device__ __forceinline__ PreGate(const LfCam& cam, double max_depth) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) c[i] = cam.Pg[i];
+        hwx = cam.hwx; hwy = cam.hwy; tX = cam.tX; tY = cam.tY; ntD = -cam.tD; gR = cam.gR;
+        float dmax32 = (float)max_depth;
+        dmax32 += fabsf(dmax32) * 1e-6f;                   // the cast may round down
+        dhi = dmax32 + cam.tD;
+    }
+    __device__ __forceinline__ bool maybe(const float4 p) const {
+        const float d = fmaf(c[8], p.x, fmaf(c[9], p.y, fmaf(c[10], p.z, c[11])));
+        const float x = fmaf(c[0], p.x, fmaf(c[1], p.y, fmaf(c[2], p.z, c[3])));
+        const float y = fmaf(c[4], p.x, fmaf(c[5], p.y, fmaf(c[6], p.z, c[7])));
+        const float big = fmaxf(fmaxf(fabsf(p.x), fabsf(p.y)), fabsf(p.z));
+        const bool out = (d < ntD) | (d > dhi) | (fabsf(x) > fmaf(hwx, d, tX)) | (fabsf(y) > fmaf(hwy, d, tY));
+        return !out | !(big <= gR);
+    }
+};
+
+// Everything one warp does for 32 consecutive points (one per lane) of which at
+// least one passed the pre-gate (`maybe`).
+__device__ __forceinline__ void fuse_warp_points(const LfCam& cam, const FuseArgs& A, float4 p, bool live, bool maybe,
                                                  int64_t gidx, int lane, int M, int B, int m0, const uint32_t* mask_base,
                                                  int plane32, const lf_box* s_box, int32_t* s_inside,
                                                  int32_t* s_nin, int32_t* s_total, int& my_valid) {
     const unsigned FULL = 0xFFFFFFFFu;
-    // fp32 look at the depth: points certainly behind the camera or certainly beyond the
-    // range gate never reach the fp64 chain.  The margin covers the fp32 evaluation error
-    // (a few ulp of the largest term); NaN compares false and takes the exact path.
-    bool maybe = live;
-    {
-        float dmax32 = (float)A.max_depth;
-        dmax32 += fabsf(dmax32) * 1e-6f;                               // the cast may round down
-        const float px = fmaf(cam.Tf[0], p.x, fmaf(cam.Tf[1], p.y, fmaf(cam.Tf[2], p.z, cam.Tf[3])));
-        const float py = fmaf(cam.Tf[4], p.x, fmaf(cam.Tf[5], p.y, fmaf(cam.Tf[6], p.z, cam.Tf[7])));
-        const float pz = fmaf(cam.Tf[8], p.x, fmaf(cam.Tf[9], p.y, fmaf(cam.Tf[10], p.z, cam.Tf[11])));
-        const float d32 = fmaf(cam.Kf[0], px, fmaf(cam.Kf[1], py, cam.Kf[2] * pz));
-        const float mag = fabsf(p.x) + fabsf(p.y) + fabsf(p.z) + 1.0f;
-        const float tol = cam.depth_tol * mag;
-        if (d32 < -tol || d32 > dmax32 + tol) maybe = false;
-    }
     bool valid = false;
     double uq = 0.0, vq = 0.0;
-    if (__any_sync(FULL, maybe)) {
+    if (maybe) {
         double qx, qy, d;
         lf_project_xyd(cam, p.x, p.y, p.z, qx, qy, d);
-        const bool front = maybe && d > 0.0 && d < A.max_depth;        // depth half of cvs_erosion.py:359
+        const bool front = d > 0.0 && d < A.max_depth;        // depth half of cvs_erosion.py:359
         if (front) {
             // u = rint(qx / d): one reciprocal instead of two divisions.  q~ = qx * (1/d) is
             // within 2 ulp of the correctly rounded quotient, so rint() agrees unless q~ sits
@@ -249,7 +261,7 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
     if (threadIdx.x == 0) {
         for (int s = 0; s < FUSE_STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], FUSE_GROUPS);
+            mbar_init(&empty_bar[s], FUSE_CONSUMERS);
         }
         mbar_fence_init();
     }
@@ -286,19 +298,38 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
         const int plane32 = cam.H * cam.wpr;               // words per packed mask (< 2^25, see lf_set_camera)
         const uint32_t* mask_base = A.packed + (int64_t)m0 * plane32;
         int my_valid = 0;
-        // groups are dealt round-robin: frustum points come in runs of a few hundred, so
-        // every warp gets its share of the expensive ones
-        for (int g = warp; g < ngroups; g += FUSE_CONSUMERS) {
-            const int sub = g / FUSE_GROUPS, grp = g & (FUSE_GROUPS - 1);
+        const PreGate pg(cam, A.max_depth);
+        // A stage holds 32 groups of 32 points; warp w owns groups w, w+8, w+16, w+24 of every
+        // stage (frustum points come in runs of a few hundred, so round-robin dealing gives every
+        // warp its share of the expensive ones).  One barrier wait and one release per warp and
+        // stage; the fp32 pre-gate of the four groups runs first, and only groups with a
+        // surviving point are read again for the exact path.
+        const bool all_groups = A.car_bits != nullptr;      // per-point output: every group writes
+        for (int sub = 0; sub < nsub; ++sub) {
             const int s = sub & (FUSE_STAGES - 1);
             mbar_wait(&full_bar[s], (uint32_t)((sub / FUSE_STAGES) & 1));
-            const int k = g * 32 + lane;                   // point index inside the segment
-            const bool live = k < npts;
-            const float4 p = live ? stage[s * FUSE_SUB + grp * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4* sp = stage + s * FUSE_SUB + warp * 32 + lane;
+            const int k0 = sub * FUSE_SUB + warp * 32 + lane;          // point index inside the segment
+            unsigned mb = 0;
+#pragma unroll
+            for (int j = 0; j < FUSE_GROUPS / FUSE_CONSUMERS; ++j) {
+                const float4 p = sp[j * 32 * FUSE_CONSUMERS];
+                const bool live = k0 + j * 32 * FUSE_CONSUMERS < npts;
+                mb |= (unsigned)(live & pg.maybe(p)) << j;
+            }
+            unsigned todo = __reduce_or_sync(0xFFFFFFFFu, mb);
+            if (all_groups) todo = (1u << (FUSE_GROUPS / FUSE_CONSUMERS)) - 1u;
+            while (todo) {
+                const int j = __ffs((int)todo) - 1;
+                todo &= todo - 1;
+                const int k = k0 + j * 32 * FUSE_CONSUMERS;
+                const bool live = k < npts;
+                const float4 p = sp[j * 32 * FUSE_CONSUMERS];
+                fuse_warp_points(cam, A, p, live, (mb >> j) & 1u, seg0 + k, lane, M, B, m0, mask_base, plane32, s_box,
+                                 s_inside, s_nin, s_total, my_valid);
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
-            fuse_warp_points(cam, A, p, live, seg0 + k, lane, M, B, m0, mask_base, plane32, s_box, s_inside, s_nin,
-                             s_total, my_valid);
         }
         const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
         if (lane == 0 && vb) atomicAdd(s_nvalid, (int)vb);
