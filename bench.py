@@ -6,7 +6,8 @@ HDL-64-shaped frames (BASELINE.json metric).
 
 A step = one pass of the hot path over one batch per GPU: counter memset,
 erode+pack of the uint8 masks, the fused point pass and the per-car decision
-(4 launches), plus -- at N > 1 -- the single all-reduce of the per-car table.
+(4 launches; --persistent: erosion and the point pass as one persistent kernel),
+plus -- at N > 1 -- the single all-reduce of the per-car table.
 N = 1 runs BASELINE configs[2]: 1024 frames x 131072 points x 16 masks
 (1408x376) x 16 boxes, all resident in HBM (10.8 GB >> 126 MB L2, so no L2
 flush is needed between steps).  N > 1 is weak scaling: every rank holds its
@@ -183,7 +184,7 @@ def run_gpu(args):
         exch.bind(batch.h_mask_off, sb.n_boxes)
 
     def step(mark=None):
-        batch.run(3, 1, 50, 10, True, mark=mark)
+        batch.run(3, 1, 50, 10, True, mark=mark, persistent=args.persistent)
         if exch is not None:
             exch.exchange_batch(batch)
 
@@ -251,7 +252,9 @@ def run_gpu(args):
     kern = {}
     for lst in marks:
         d = dict(lst)
-        for a, b in (('zero', 'erode_pack'), ('erode_pack', 'fuse'), ('fuse', 'car_stats')):
+        pairs = (('zero', 'erode_pack'), ('erode_pack', 'fuse'), ('fuse', 'car_stats')) if not args.persistent else \
+            (('zero', 'batch'), ('batch', 'car_stats'))
+        for a, b in pairs:
             kern.setdefault(b, []).append(d[a].elapsed_time(d[b]))
     kern_ms = {k: sum(v) / len(v) for k, v in kern.items()}
 
@@ -299,13 +302,19 @@ def run_gpu(args):
             peak, peak_src = float(peaks['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
         except Exception:
             peak = 6650.0
-        mask_bytes = frames * NCARS * H_IMG * W_IMG                       # algorithmic bytes of the erode launch
-        ach = mask_bytes / (kern_ms['erode_pack'] * 1e-3) / 1e9
         step_bytes = sum(algorithmic_bytes_per_frame(n_pts, NCARS, b) for b in sb.n_boxes)
+        if not args.persistent:  # dominant kernel: the erode launch, F*M*H*W bytes in
+            kname, kkey, tkey = 'lf_erode_fast_kernel<SeCross3> (lf_erode_pack)', 'erode_pack', 'lf_erode_fast_kernel'
+            mask_bytes = frames * NCARS * H_IMG * W_IMG
+        else:                   # the persistent kernel does erode + point pass: all algorithmic bytes of the step
+            kname, kkey, tkey = 'lf_batch_kernel<SeCross3> (lf_process_batch: erode+pack and fused point pass)', \
+                'batch', 'lf_batch_kernel'
+            mask_bytes = step_bytes
+        ach = mask_bytes / (kern_ms[kkey] * 1e-3) / 1e9
         traffic = None
         try:
             with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as fh:
-                traffic = json.load(fh).get('lf_erode_fast_kernel_dram_bytes_per_launch')
+                traffic = json.load(fh).get(tkey + '_dram_bytes_per_launch')
         except Exception:
             pass
         line = {
@@ -323,7 +332,7 @@ def run_gpu(args):
             'step_hbm': {'algorithmic_bytes_per_step': step_bytes, 'achieved_gbs': step_bytes / (ms_step * 1e-3) / 1e9,
                          'frac_of_measured_peak': step_bytes / (ms_step * 1e-3) / 1e9 / peak,
                          'frac_of_8000_nominal': step_bytes / (ms_step * 1e-3) / 1e9 / 8000.0},
-            'roofline': {'kernel': 'lf_erode_fast_kernel<SeCross3> (lf_erode_pack)', 'bound': 'hbm', 'achieved': ach, 'peak': peak,
+            'roofline': {'kernel': kname, 'bound': 'hbm', 'achieved': ach, 'peak': peak,
                          'unit': 'GB/s', 'frac': ach / peak, 'traffic': traffic, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': mask_bytes},
             'e2e': e2e, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,
@@ -369,6 +378,9 @@ def main():
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
+    ap.add_argument('--persistent', action='store_true',
+                    help='one persistent erode+fuse kernel (lf_process_batch with scheduler words) instead of '
+                         'the stand-alone erode / fuse launches')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -135,6 +135,27 @@ int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_of
                   int32_t* total /*DEVICE*/, int32_t* inside /*DEVICE*/, int32_t* n_in_box /*DEVICE*/,
                   int32_t* n_valid /*DEVICE*/, uint64_t* car_bits /*DEVICE or NULL*/, void* stream);
 
+/* The whole per-batch body of cvs_erosion.process_frames (:342-372) in one call:
+ * lf_erode_pack + lf_fuse_batch + lf_car_stats with the same arguments and the same
+ * results.  When `sched` is given (DEVICE int32 [F + 2], zeroed by the caller like the
+ * counters), the masks are uint8 at camera resolution and the structuring element is one
+ * of the compiled-in cv2 shapes (RECT / CROSS / ELLIPSE up to 7x7), erosion and the point
+ * pass run as ONE persistent kernel whose CTAs claim "erode mask m" / "fuse segment s of
+ * frame f" work items, a frame's points being released as soon as its last mask is
+ * packed; otherwise the three stand-alone launches are issued.  masks == NULL: `packed`
+ * and `mask_bbox` are inputs (already packed masks).  best_idx / best_cnt / agg as in
+ * lf_car_stats (NULL best_idx skips the decision). */
+int lf_process_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
+                     const void* masks /*DEVICE [n_masks][H][W] or NULL*/, int mask_mode, int64_t n_masks,
+                     const int32_t* mask_off /*DEVICE [F+1]*/, const uint8_t* se /*HOST [k][k]*/, int k,
+                     int iterations, uint32_t* packed /*DEVICE*/, int32_t* mask_bbox /*DEVICE [n_masks][4]*/,
+                     const lf_box* boxes /*DEVICE*/, const int32_t* box_off /*DEVICE [F+1]*/,
+                     const int64_t* cnt_off /*DEVICE [F+1]*/, int F, int64_t max_points_per_frame,
+                     int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,
+                     int min_points, int32_t* total, int32_t* inside, int32_t* n_in_box, int32_t* n_valid,
+                     int32_t* best_idx, int32_t* best_cnt, int64_t* agg, int32_t* sched /*DEVICE or NULL*/,
+                     void* stream);
+
 /* A6 stand-alone: bit c of bits[i] = packed mask c is set at (v[i], u[i])
  * (extract_car_points_by_mask, cvs_erosion.py:148-162).  m <= LF_MAX_CARS. */
 int lf_mask_gather(lf_ctx* ctx, const uint32_t* packed /*DEVICE [m][H][wpr]*/, int m, int H, int W,

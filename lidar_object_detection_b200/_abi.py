@@ -37,6 +37,9 @@ SIGNATURES = {
     'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
     'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp]),
+    'lf_process_batch': (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
+                                   _i32, _i64, _i32, _i32, _f64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                   _vp, _vp]),
     'lf_mask_gather': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp]),
     'lf_points_in_box': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _i32, _vp, _vp]),
     'lf_count_in_boxes': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _vp, _i32, _i32, _vp, _vp]),

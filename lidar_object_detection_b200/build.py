@@ -9,8 +9,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, '_lib', 'liblidarfuse.so')
-SOURCES = ['ctx.cu', 'project.cu', 'erode.cu', 'fuse.cu', 'points.cu', 'synth.cu']
-HEADERS = [os.path.join(CSRC, 'common.cuh'), os.path.join(CSRC, 'bulk.cuh'), os.path.join(ROOT, 'include', 'lidarfuse.h')]
+SOURCES = ['ctx.cu', 'project.cu', 'erode.cu', 'fuse.cu', 'batch.cu', 'points.cu', 'synth.cu']
+HEADERS = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith('.cuh')) + \
+    [os.path.join(ROOT, 'include', 'lidarfuse.h')]
 
 
 def _nvcc():

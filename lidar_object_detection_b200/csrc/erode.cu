@@ -13,65 +13,9 @@
 #include "common.cuh"
 #include "bulk.cuh"
 
+#include "erode_body.cuh"
+
 namespace {
-
-constexpr int ER_THREADS = 256;
-constexpr int ER_STAGES = 4;
-constexpr int ER_CHUNK = 8192;          // bytes per stage: 256 threads x 32 px
-constexpr int ER_MAX_ROWS = 96;         // strip height bound (smem: 2 x (96+2*halo) x wpr x 4)
-
-struct ErodeParams {
-    int H, W, wpr;
-    int rows_per_strip, strips;
-    int k, r, iterations, halo;
-    int buf_words;                       // words per packed smem buffer
-    unsigned wpr_magic;                  // ceil(2^32 / wpr): it / wpr == __umulhi(it, magic) for it < 2^16
-    int spans_ok;                        // every SE row is one contiguous run (RECT / CROSS / ELLIPSE are)
-    unsigned short se_rows[LF_MAX_SE];   // bit j of se_rows[i] = SE[i][j]
-    signed char span_a[LF_MAX_SE];       // row i covers dx in [-span_a[i], +span_b[i]]; span_a < 0: empty row
-    signed char span_b[LF_MAX_SE];
-};
-
-// Bounding box of the set pixels of the (eroded) mask, kept per thread while the
-// packed words go out and merged with four atomics per CTA.  Stored so that an
-// all-zero record means "empty": {2^20 - x0, 2^20 - y0, x1 + 1, y1 + 1}, all
-// combined with atomicMax.  The fused point pass uses it to skip masks whose
-// silhouette the points of a warp cannot touch.
-struct BBoxAcc {
-    int nx0, ny0, x1, y1;
-    __device__ __forceinline__ BBoxAcc() : nx0(0), ny0(0), x1(0), y1(0) {}
-    __device__ __forceinline__ void add(uint32_t w, int row, int wx) {
-        if (!w) return;
-        nx0 = max(nx0, (1 << 20) - (32 * wx + __ffs((int)w) - 1));
-        x1 = max(x1, 32 * wx + 32 - __clz((int)w));
-        ny0 = max(ny0, (1 << 20) - row);
-        y1 = max(y1, row + 1);
-    }
-    __device__ __forceinline__ void flush(int32_t* bbox) {
-        const int a = __reduce_max_sync(0xFFFFFFFFu, nx0), b = __reduce_max_sync(0xFFFFFFFFu, ny0);
-        const int c = __reduce_max_sync(0xFFFFFFFFu, x1), d = __reduce_max_sync(0xFFFFFFFFu, y1);
-        if ((threadIdx.x & 31) == 0 && c > 0) {
-            atomicMax(bbox + 0, a); atomicMax(bbox + 1, b); atomicMax(bbox + 2, c); atomicMax(bbox + 3, d);
-        }
-    }
-};
-
-// 4 bytes -> 4 bits (bit j = byte j non-zero), returned in bits 28..31.
-__device__ __forceinline__ uint32_t nz_nibble_hi(uint32_t w) {
-    const uint32_t t = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;   // bit 7 of each byte = byte != 0
-    return (t * 0x00204081u) & 0xF0000000u;                                     // 7,15,23,31 -> 28,29,30,31
-}
-__device__ __forceinline__ uint32_t pack32(const uint4 a, const uint4 b) {
-    uint32_t acc = nz_nibble_hi(a.x);
-    acc = (acc >> 4) | nz_nibble_hi(a.y);
-    acc = (acc >> 4) | nz_nibble_hi(a.z);
-    acc = (acc >> 4) | nz_nibble_hi(a.w);
-    acc = (acc >> 4) | nz_nibble_hi(b.x);
-    acc = (acc >> 4) | nz_nibble_hi(b.y);
-    acc = (acc >> 4) | nz_nibble_hi(b.z);
-    acc = (acc >> 4) | nz_nibble_hi(b.w);
-    return acc;
-}
 
 // One erosion pass, smem -> smem, over the loaded rows [ga, gb) of the image.
 // Pixels outside the image are ones (cv2 border value +inf for erosion); rows
@@ -197,13 +141,6 @@ __device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* 
     if (bbox) acc.flush(bbox);
 }
 
-__device__ __forceinline__ void strip_rows(const ErodeParams& P, int strip, int& r0, int& r1, int& ga, int& gb) {
-    r0 = strip * P.rows_per_strip;
-    r1 = min(P.H, r0 + P.rows_per_strip);
-    ga = max(0, r0 - P.halo);
-    gb = min(P.H, r1 + P.halo);
-}
-
 // ---------------------------------------------------------------------------
 // fast path
 // ---------------------------------------------------------------------------
@@ -274,181 +211,19 @@ lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
                     bbox ? bbox + 4 * mask : nullptr);
 }
 
-// ---------------------------------------------------------------------------
-// specialised fast path: structuring element known at compile time
-// ---------------------------------------------------------------------------
-// Symmetric row-span elements (every cv2 RECT / CROSS / ELLIPSE up to 7x7):
-// row i and row K-1-i have the same half-width HW(i); HW < 0 = empty row.
-// Packed rows live in shared memory with stride wpr+1: word 0 of every row is an
-// all-ones guard that doubles as the right neighbour of the previous row, and
-// K/2 all-ones guard rows sit above and below, so the erosion loop has no
-// bounds checks at all (out-of-image = ones = cv2's +inf erosion border).
-template <int K, int H0, int H1, int H2, int H3>
-struct SeSpec {
-    static constexpr int k = K;
-    __host__ __device__ static constexpr int hw(int i) {
-        const int j = i <= K / 2 ? i : K - 1 - i;
-        return j == 0 ? H0 : (j == 1 ? H1 : (j == 2 ? H2 : H3));
-    }
-};
-
-__device__ __forceinline__ uint4 lds128(uint32_t addr) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-    return v;
-}
-
 template <class SE>
 __global__ void __launch_bounds__(ER_THREADS)
 lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __restrict__ masks,
                      uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
-    constexpr int K = SE::k, RAD = K / 2;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[ER_STAGES];
-    const uint32_t stage_a = smem_u32(smem);
-    uint32_t* bufA = (uint32_t*)(smem + ER_STAGES * ER_CHUNK);
-    uint32_t* bufB = bufA + P.buf_words;
-
-    const int64_t mask = blockIdx.x / P.strips;
-    const int strip = blockIdx.x - (int)(mask * P.strips);
-    int r0, r1, ga, gb;
-    strip_rows(P, strip, r0, r1, ga, gb);
-    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W;
-    const int nrows = gb - ga;
-    const int L = nrows * P.W;
-    const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
-    const int S = P.wpr + 1;                               // row stride in words
-    const int tid = threadIdx.x;
-
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
         for (int s = 0; s < ER_STAGES; ++s) mbar_init(&full_bar[s], 1);
         mbar_fence_init();
     }
     __syncthreads();
-    if (tid == 0) {
-        for (int i = 0; i < ER_STAGES && i < nch; ++i) {
-            const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - i * ER_CHUNK);
-            mbar_expect_tx(&full_bar[i], bytes);
-            bulk_g2s(smem + i * ER_CHUNK, src + (int64_t)i * ER_CHUNK, bytes, &full_bar[i]);
-        }
-    }
-    // guards: RAD rows above and below the window, word 0 of every row, one trailing word
-    if (P.iterations > 0) {
-        const int top = RAD * S, all = (nrows + 2 * RAD) * S + 1;
-        for (int i = tid; i < top; i += ER_THREADS) {
-            bufA[i] = 0xFFFFFFFFu; bufB[i] = 0xFFFFFFFFu;
-            bufA[all - 1 - i] = 0xFFFFFFFFu; bufB[all - 1 - i] = 0xFFFFFFFFu;
-        }
-        for (int r = tid; r <= nrows; r += ER_THREADS) {
-            bufA[(r + RAD) * S] = 0xFFFFFFFFu; bufB[(r + RAD) * S] = 0xFFFFFFFFu;
-        }
-    }
-    const int data0 = RAD * S + 1;                         // word index of (row 0, wx 0)
-
-    for (int i = 0; i < nch; i += 2) {
-        const int s0 = i % ER_STAGES, s1 = (i + 1) % ER_STAGES;
-        const uint32_t par = (uint32_t)((i / ER_STAGES) & 1);
-        const int w0 = i * (ER_CHUNK / 32) + tid;          // flat word index of this thread's 32 px
-        const int w1 = w0 + ER_CHUNK / 32;
-        const bool p0 = w0 * 32 < L, p1 = w1 * 32 < L;
-        uint4 a0, a1, b0, b1;
-        mbar_wait(&full_bar[s0], par);
-        if (p0) { a0 = lds128(stage_a + s0 * ER_CHUNK + 32 * tid); a1 = lds128(stage_a + s0 * ER_CHUNK + 32 * tid + 16); }
-        if (i + 1 < nch) mbar_wait(&full_bar[s1], par);
-        if (p1) { b0 = lds128(stage_a + s1 * ER_CHUNK + 32 * tid); b1 = lds128(stage_a + s1 * ER_CHUNK + 32 * tid + 16); }
-        __syncthreads();                                   // both stages are in registers now
-        if (tid == 0) {
-            fence_proxy_async_smem();
-#pragma unroll
-            for (int t = 0; t < 2; ++t) {
-                const int j = i + t + ER_STAGES;
-                if (j < nch) {
-                    const int sj = j % ER_STAGES;
-                    const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - j * ER_CHUNK);
-                    mbar_expect_tx(&full_bar[sj], bytes);
-                    bulk_g2s(smem + sj * ER_CHUNK, src + (int64_t)j * ER_CHUNK, bytes, &full_bar[sj]);
-                }
-            }
-        }
-        // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
-        if (p0) bufA[w0 + (int)__umulhi((unsigned)w0, P.wpr_magic) + data0] = pack32(a0, a1);
-        if (p1) bufA[w1 + (int)__umulhi((unsigned)w1, P.wpr_magic) + data0] = pack32(b0, b1);
-    }
-
-    uint32_t* cur = bufA;
-    uint32_t* nxt = bufB;
-    const int items = nrows * P.wpr;
-    for (int itn = 0; itn < P.iterations; ++itn) {
-        __syncthreads();
-        for (int it = tid; it < items; it += ER_THREADS) {
-            const int idx = it + (int)__umulhi((unsigned)it, P.wpr_magic) + data0;
-            uint32_t acc = 0xFFFFFFFFu;
-#pragma unroll
-            for (int i = 0; i < K; ++i) {
-                constexpr int dummy = 0; (void)dummy;
-                const int h = SE::hw(i);
-                if (h < 0) continue;
-                const uint32_t* rp = cur + idx + (i - RAD) * S;
-                const uint32_t c = rp[0];
-                acc &= c;
-                if (h > 0) {
-                    const uint32_t l = rp[-1], r = rp[1];
-#pragma unroll
-                    for (int d = 1; d <= h; ++d) acc &= __funnelshift_r(c, r, d) & __funnelshift_l(l, c, d);
-                }
-            }
-            nxt[idx] = acc;
-        }
-        uint32_t* t = cur; cur = nxt; nxt = t;
-    }
-    __syncthreads();
-    uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
-    const int out_items = (r1 - r0) * P.wpr;
-    const int skip = (r0 - ga) * S;
-    BBoxAcc acc;
-    if ((P.wpr & 3) == 0) {
-        // four words per thread: one 128-bit store, one bounding-box test per 128 pixels
-        const int qpr = P.wpr >> 2;                        // quads per row
-        const unsigned qmagic = (unsigned)((0x100000000ULL + qpr - 1) / qpr);
-        const int nq = (r1 - r0) * qpr;
-        for (int q = tid; q < nq; q += ER_THREADS) {
-            const int lr = (int)__umulhi((unsigned)q, qmagic);
-            const int wq = q - lr * qpr;
-            const uint32_t* sp = cur + lr * S + 4 * wq + data0 + skip;
-            const uint4 v = make_uint4(sp[0], sp[1], sp[2], sp[3]);
-            *(uint4*)(dstw + 4 * q) = v;
-            if (v.x | v.y | v.z | v.w) {
-                acc.add(v.x, r0 + lr, 4 * wq); acc.add(v.y, r0 + lr, 4 * wq + 1);
-                acc.add(v.z, r0 + lr, 4 * wq + 2); acc.add(v.w, r0 + lr, 4 * wq + 3);
-            }
-        }
-    } else {
-        for (int it = tid; it < out_items; it += ER_THREADS) {
-            const int lr = (int)__umulhi((unsigned)it, P.wpr_magic);
-            const uint32_t w = cur[it + lr + data0 + skip];
-            dstw[it] = w;
-            acc.add(w, r0 + lr, it - lr * P.wpr);
-        }
-    }
-    if (bbox) acc.flush(bbox + 4 * mask);
-}
-
-typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)
-typedef SeSpec<3, 1, 1, 0, 0> SeRect3;
-typedef SeSpec<5, 0, 2, 2, 0> SeEllipse5;
-typedef SeSpec<5, 2, 2, 2, 0> SeRect5;
-typedef SeSpec<5, 0, 0, 2, 0> SeCross5;
-typedef SeSpec<7, 0, 2, 3, 3> SeEllipse7;
-typedef SeSpec<7, 3, 3, 3, 3> SeRect7;
-typedef SeSpec<7, 0, 0, 0, 3> SeCross7;
-typedef SeSpec<1, 0, 0, 0, 0> SeNone;       // pack only / 1x1
-
-template <class SE>
-bool se_matches(const ErodeParams& P) {
-    if (P.k != SE::k || !P.spans_ok) return false;
-    for (int i = 0; i < SE::k; ++i)
-        if (P.span_a[i] != SE::hw(i) || P.span_b[i] != SE::hw(i)) return false;
-    return true;
+    uint32_t cbase = 0;
+    erode_fast_item<SE, ER_STAGES>(P, masks, packed, bbox, blockIdx.x, smem, full_bar, cbase);
 }
 
 template <class SE>
@@ -518,17 +293,10 @@ __global__ void lf_unpack_kernel(const uint32_t* __restrict__ packed, int64_t to
 
 }  // namespace
 
-extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
-                             const uint8_t* se, int k, int iterations, uint32_t* packed, int32_t* bbox,
-                             void* stream) {
-    if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 2) return LF_E_ARG;
-    if (m > 0 && (!masks || !packed)) return LF_E_ARG;
-    if (iterations > 0 && (!se || k < 1 || (k & 1) == 0)) return LF_E_ARG;
-    if (iterations > 0 && k > LF_MAX_SE) return LF_E_UNSUPPORTED;
-    if (m == 0) return LF_OK;
-    LF_CUDA(ctx, cudaSetDevice(ctx->device));
-
-    ErodeParams P;
+int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W, const uint8_t* se, int k,
+                  int iterations, int max_rows, int stages, ErodeParams* Pout, int* spec_out, int* fast_out,
+                  size_t* smem_out) {
+    ErodeParams& P = *Pout;
     memset(&P, 0, sizeof(P));
     P.H = H; P.W = W; P.wpr = (W + 31) / 32;
     P.iterations = iterations;
@@ -562,7 +330,7 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
 
     // strip plan: enough CTAs to fill the machine several times over, strips <= ER_MAX_ROWS rows
     int64_t want = ((int64_t)ctx->sm_count * 8 + m - 1) / m;
-    int min_strips = (H + ER_MAX_ROWS - 1) / ER_MAX_ROWS;
+    int min_strips = (H + max_rows - 1) / max_rows;
     int max_strips = (H + 15) / 16;
     int strips = (int)(want < min_strips ? min_strips : (want > max_strips ? max_strips : want));
     P.rows_per_strip = (H + strips - 1) / strips;
@@ -573,10 +341,10 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
     if ((int64_t)buf_rows * P.wpr >= 65536) return LF_E_UNSUPPORTED;
     if (m * P.strips > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
 
-    const bool fast = mode == 0 && (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
+    const bool fastp = mode == 0 && (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
     // compile-time element available?  (guarded smem layout: stride wpr+1, K/2 guard rows each side)
     int spec = -1;
-    if (fast) {
+    if (fastp) {
         if (iterations == 0 || se_matches<SeNone>(P)) spec = 0;
         else if (se_matches<SeCross3>(P)) spec = 1;
         else if (se_matches<SeRect3>(P)) spec = 2;
@@ -588,8 +356,26 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
         else if (se_matches<SeCross7>(P)) spec = 8;
     }
     if (spec >= 0) P.buf_words = (buf_rows + 2 * P.r) * (P.wpr + 1) + 1;
-    size_t smem = (size_t)P.buf_words * 4 * (iterations > 0 ? 2 : 1) + (fast ? ER_STAGES * ER_CHUNK : 0);
+    const size_t smem = (size_t)P.buf_words * 4 * (iterations > 0 ? 2 : 1) + (fastp ? stages * ER_CHUNK : 0);
     if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
+    *spec_out = spec; *fast_out = fastp ? 1 : 0; *smem_out = smem;
+    return LF_OK;
+}
+
+extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
+                             const uint8_t* se, int k, int iterations, uint32_t* packed, int32_t* bbox,
+                             void* stream) {
+    if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 2) return LF_E_ARG;
+    if (m > 0 && (!masks || !packed)) return LF_E_ARG;
+    if (iterations > 0 && (!se || k < 1 || (k & 1) == 0)) return LF_E_ARG;
+    if (iterations > 0 && k > LF_MAX_SE) return LF_E_UNSUPPORTED;
+    if (m == 0) return LF_OK;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    ErodeParams P;
+    int spec, fast;
+    size_t smem;
+    const int rc = lf_erode_plan(ctx, masks, mode, m, H, W, se, k, iterations, ER_MAX_ROWS, ER_STAGES, &P, &spec, &fast, &smem);
+    if (rc != LF_OK) return rc;
     const unsigned grid = (unsigned)(m * P.strips);
     cudaStream_t s = (cudaStream_t)stream;
     if (spec >= 0) {

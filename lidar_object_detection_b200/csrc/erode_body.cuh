@@ -1,0 +1,277 @@
+// Fast path of K3 (mask binarisation + binary erosion + bit-packing) as a per-item
+// device function, shared by the stand-alone erode kernel (erode.cu) and the
+// persistent batch kernel (batch.cu).  See erode.cu for the algorithm.
+#pragma once
+#include "common.cuh"
+#include "bulk.cuh"
+
+constexpr int ER_THREADS = 256;
+constexpr int ER_STAGES = 4;          // stand-alone kernel
+constexpr int ER_STAGES_BATCH = 4;    // persistent batch kernel: more bytes in flight per CTA, shorter strips
+constexpr int ER_CHUNK = 8192;          // bytes per stage: 256 threads x 32 px
+constexpr int ER_MAX_ROWS = 96;         // strip height bound (smem: 2 x (96+2*halo) x wpr x 4)
+constexpr int ER_MAX_ROWS_BATCH = 96;
+
+struct ErodeParams {
+    int H, W, wpr;
+    int rows_per_strip, strips;
+    int k, r, iterations, halo;
+    int buf_words;                       // words per packed smem buffer
+    unsigned wpr_magic;                  // ceil(2^32 / wpr): it / wpr == __umulhi(it, magic) for it < 2^16
+    int spans_ok;                        // every SE row is one contiguous run (RECT / CROSS / ELLIPSE are)
+    unsigned short se_rows[LF_MAX_SE];   // bit j of se_rows[i] = SE[i][j]
+    signed char span_a[LF_MAX_SE];       // row i covers dx in [-span_a[i], +span_b[i]]; span_a < 0: empty row
+    signed char span_b[LF_MAX_SE];
+};
+
+// Host-side plan of one lf_erode_pack call (erode.cu): fills P, picks the compile-time
+// structuring element (`spec` >= 0: index into the SeSpec list below, -1: run-time
+// element), says whether the bulk-copy fast path applies and how much dynamic shared
+// memory a CTA needs.  Returns LF_OK or an LF_E_* code.
+int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W, const uint8_t* se, int k,
+                  int iterations, int max_rows, int stages, ErodeParams* P, int* spec, int* fast, size_t* smem);
+
+namespace {
+
+
+
+// Bounding box of the set pixels of the (eroded) mask, kept per thread while the
+// packed words go out and merged with four atomics per CTA.  Stored so that an
+// all-zero record means "empty": {2^20 - x0, 2^20 - y0, x1 + 1, y1 + 1}, all
+// combined with atomicMax.  The fused point pass uses it to skip masks whose
+// silhouette the points of a warp cannot touch.
+struct BBoxAcc {
+    int nx0, ny0, x1, y1;
+    __device__ __forceinline__ BBoxAcc() : nx0(0), ny0(0), x1(0), y1(0) {}
+    __device__ __forceinline__ void add(uint32_t w, int row, int wx) {
+        if (!w) return;
+        nx0 = max(nx0, (1 << 20) - (32 * wx + __ffs((int)w) - 1));
+        x1 = max(x1, 32 * wx + 32 - __clz((int)w));
+        ny0 = max(ny0, (1 << 20) - row);
+        y1 = max(y1, row + 1);
+    }
+    __device__ __forceinline__ void flush(int32_t* bbox) {
+        const int a = __reduce_max_sync(0xFFFFFFFFu, nx0), b = __reduce_max_sync(0xFFFFFFFFu, ny0);
+        const int c = __reduce_max_sync(0xFFFFFFFFu, x1), d = __reduce_max_sync(0xFFFFFFFFu, y1);
+        if ((threadIdx.x & 31) == 0 && c > 0) {
+            atomicMax(bbox + 0, a); atomicMax(bbox + 1, b); atomicMax(bbox + 2, c); atomicMax(bbox + 3, d);
+        }
+    }
+};
+
+// 4 bytes -> 4 bits (bit j = byte j non-zero) in bits 0..3; the bits above are garbage.
+// bit 7 of each byte of t = byte != 0; the high half of t * (2^25+2^18+2^11+2^4) lines bits
+// 7, 15, 23, 31 up at 32..35 (no two partial products share a bit below, so no carries).
+__device__ __forceinline__ uint32_t nz_nibble_lo(uint32_t w) {
+    const uint32_t t = (((w & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w) & 0x80808080u;
+    return __umulhi(t, 0x02040810u);
+}
+// 32 bytes -> 32 bits, LSB = first byte.  Each step shifts the word right by four and
+// drops the next nibble in at the top (one funnel shift: the garbage never gets in).
+// Instance masks are mostly background: 32 zero bytes cost five instructions.
+__device__ __forceinline__ uint32_t pack32(const uint4 a, const uint4 b) {
+    if (((a.x | a.y | a.z) | (a.w | b.x | b.y) | (b.z | b.w)) == 0u) return 0u;
+    uint32_t acc = nz_nibble_lo(a.x) << 28;
+    acc = __funnelshift_r(acc, nz_nibble_lo(a.y), 4);
+    acc = __funnelshift_r(acc, nz_nibble_lo(a.z), 4);
+    acc = __funnelshift_r(acc, nz_nibble_lo(a.w), 4);
+    acc = __funnelshift_r(acc, nz_nibble_lo(b.x), 4);
+    acc = __funnelshift_r(acc, nz_nibble_lo(b.y), 4);
+    acc = __funnelshift_r(acc, nz_nibble_lo(b.z), 4);
+    acc = __funnelshift_r(acc, nz_nibble_lo(b.w), 4);
+    return acc;
+}
+
+__device__ __forceinline__ void strip_rows(const ErodeParams& P, int strip, int& r0, int& r1, int& ga, int& gb) {
+    r0 = strip * P.rows_per_strip;
+    r1 = min(P.H, r0 + P.rows_per_strip);
+    ga = max(0, r0 - P.halo);
+    gb = min(P.H, r1 + P.halo);
+}
+
+// ---------------------------------------------------------------------------
+// specialised fast path: structuring element known at compile time
+// ---------------------------------------------------------------------------
+// Symmetric row-span elements (every cv2 RECT / CROSS / ELLIPSE up to 7x7):
+// row i and row K-1-i have the same half-width HW(i); HW < 0 = empty row.
+// Packed rows live in shared memory with stride wpr+1: word 0 of every row is an
+// all-ones guard that doubles as the right neighbour of the previous row, and
+// K/2 all-ones guard rows sit above and below, so the erosion loop has no
+// bounds checks at all (out-of-image = ones = cv2's +inf erosion border).
+template <int K, int H0, int H1, int H2, int H3>
+struct SeSpec {
+    static constexpr int k = K;
+    __host__ __device__ static constexpr int hw(int i) {
+        const int j = i <= K / 2 ? i : K - 1 - i;
+        return j == 0 ? H0 : (j == 1 ? H1 : (j == 2 ? H2 : H3));
+    }
+};
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+// One work item = (mask, strip) of the fast path.  `smem` = NST * ER_CHUNK bytes of
+// staging followed by the two packed buffers; `full_bar` = NST initialised mbarriers
+// (count 1) whose phases run on from item to item: `cbase` counts the chunks this CTA has
+// streamed so far, chunk c lives in stage c % NST and completes phase c / NST.
+// Executed by the ER_THREADS threads with the lowest thread indices; they meet on named
+// barrier 1, so further warps of the CTA are free to do something else.
+__device__ __forceinline__ void er_sync() { asm volatile("bar.sync 1, %0;" ::"n"(ER_THREADS) : "memory"); }
+
+template <class SE, int NST>
+__device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint8_t* __restrict__ masks,
+                                                uint32_t* __restrict__ packed, int32_t* __restrict__ bbox,
+                                                int64_t item, uint8_t* smem, uint64_t* full_bar, uint32_t& cbase) {
+    constexpr int K = SE::k, RAD = K / 2;
+    const uint32_t stage_a = smem_u32(smem);
+    uint32_t* bufA = (uint32_t*)(smem + NST * ER_CHUNK);
+    uint32_t* bufB = bufA + P.buf_words;
+
+    const int64_t mask = item / P.strips;
+    const int strip = (int)(item - mask * P.strips);
+    int r0, r1, ga, gb;
+    strip_rows(P, strip, r0, r1, ga, gb);
+    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W;
+    const int nrows = gb - ga;
+    const int L = nrows * P.W;
+    const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
+    const int S = P.wpr + 1;                               // row stride in words
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        fence_proxy_async_smem();                          // the previous item read these stages
+        for (int i = 0; i < NST && i < nch; ++i) {
+            const int si = (int)((cbase + i) % NST);
+            const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - i * ER_CHUNK);
+            mbar_expect_tx(&full_bar[si], bytes);
+            bulk_g2s(smem + si * ER_CHUNK, src + (int64_t)i * ER_CHUNK, bytes, &full_bar[si]);
+        }
+    }
+    // guards: RAD rows above and below the window, word 0 of every row, one trailing word
+    if (P.iterations > 0) {
+        const int top = RAD * S, all = (nrows + 2 * RAD) * S + 1;
+        for (int i = tid; i < top; i += ER_THREADS) {
+            bufA[i] = 0xFFFFFFFFu; bufB[i] = 0xFFFFFFFFu;
+            bufA[all - 1 - i] = 0xFFFFFFFFu; bufB[all - 1 - i] = 0xFFFFFFFFu;
+        }
+        for (int r = tid; r <= nrows; r += ER_THREADS) {
+            bufA[(r + RAD) * S] = 0xFFFFFFFFu; bufB[(r + RAD) * S] = 0xFFFFFFFFu;
+        }
+    }
+    const int data0 = RAD * S + 1;                         // word index of (row 0, wx 0)
+
+    for (int i = 0; i < nch; i += 2) {
+        const uint32_t c0 = cbase + (uint32_t)i, c1 = c0 + 1u;
+        const int s0 = (int)(c0 % NST), s1 = (int)(c1 % NST);
+        const uint32_t par0 = (c0 / NST) & 1u, par1 = (c1 / NST) & 1u;
+        const int w0 = i * (ER_CHUNK / 32) + tid;          // flat word index of this thread's 32 px
+        const int w1 = w0 + ER_CHUNK / 32;
+        const bool p0 = w0 * 32 < L, p1 = w1 * 32 < L;
+        uint4 a0, a1, b0, b1;
+        mbar_wait(&full_bar[s0], par0);
+        if (p0) { a0 = lds128(stage_a + s0 * ER_CHUNK + 32 * tid); a1 = lds128(stage_a + s0 * ER_CHUNK + 32 * tid + 16); }
+        if (i + 1 < nch) mbar_wait(&full_bar[s1], par1);
+        if (p1) { b0 = lds128(stage_a + s1 * ER_CHUNK + 32 * tid); b1 = lds128(stage_a + s1 * ER_CHUNK + 32 * tid + 16); }
+        er_sync();                                         // both stages are in registers now
+        if (tid == 0) {
+            fence_proxy_async_smem();
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                const int j = i + t + NST;
+                if (j < nch) {
+                    const int sj = (int)((cbase + j) % NST);
+                    const uint32_t bytes = (uint32_t)min(ER_CHUNK, L - j * ER_CHUNK);
+                    mbar_expect_tx(&full_bar[sj], bytes);
+                    bulk_g2s(smem + sj * ER_CHUNK, src + (int64_t)j * ER_CHUNK, bytes, &full_bar[sj]);
+                }
+            }
+        }
+        // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
+        if (p0) bufA[w0 + (int)__umulhi((unsigned)w0, P.wpr_magic) + data0] = pack32(a0, a1);
+        if (p1) bufA[w1 + (int)__umulhi((unsigned)w1, P.wpr_magic) + data0] = pack32(b0, b1);
+    }
+
+    uint32_t* cur = bufA;
+    uint32_t* nxt = bufB;
+    const int items = nrows * P.wpr;
+    for (int itn = 0; itn < P.iterations; ++itn) {
+        er_sync();
+        for (int it = tid; it < items; it += ER_THREADS) {
+            const int idx = it + (int)__umulhi((unsigned)it, P.wpr_magic) + data0;
+            if (cur[idx] == 0u) {                          // the anchor is part of every element here
+                nxt[idx] = 0u;
+                continue;
+            }
+            uint32_t acc = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                const int h = SE::hw(i);
+                if (h < 0) continue;
+                const uint32_t* rp = cur + idx + (i - RAD) * S;
+                const uint32_t c = rp[0];
+                acc &= c;
+                if (h > 0) {
+                    const uint32_t l = rp[-1], r = rp[1];
+#pragma unroll
+                    for (int d = 1; d <= h; ++d) acc &= __funnelshift_r(c, r, d) & __funnelshift_l(l, c, d);
+                }
+            }
+            nxt[idx] = acc;
+        }
+        uint32_t* t = cur; cur = nxt; nxt = t;
+    }
+    er_sync();
+    uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
+    const int out_items = (r1 - r0) * P.wpr;
+    const int skip = (r0 - ga) * S;
+    BBoxAcc acc;
+    if ((P.wpr & 3) == 0) {
+        // four words per thread: one 128-bit store, one bounding-box test per 128 pixels
+        const int qpr = P.wpr >> 2;                        // quads per row
+        const unsigned qmagic = (unsigned)((0x100000000ULL + qpr - 1) / qpr);
+        const int nq = (r1 - r0) * qpr;
+        for (int q = tid; q < nq; q += ER_THREADS) {
+            const int lr = (int)__umulhi((unsigned)q, qmagic);
+            const int wq = q - lr * qpr;
+            const uint32_t* sp = cur + lr * S + 4 * wq + data0 + skip;
+            const uint4 v = make_uint4(sp[0], sp[1], sp[2], sp[3]);
+            *(uint4*)(dstw + 4 * q) = v;
+            if (v.x | v.y | v.z | v.w) {
+                acc.add(v.x, r0 + lr, 4 * wq); acc.add(v.y, r0 + lr, 4 * wq + 1);
+                acc.add(v.z, r0 + lr, 4 * wq + 2); acc.add(v.w, r0 + lr, 4 * wq + 3);
+            }
+        }
+    } else {
+        for (int it = tid; it < out_items; it += ER_THREADS) {
+            const int lr = (int)__umulhi((unsigned)it, P.wpr_magic);
+            const uint32_t w = cur[it + lr + data0 + skip];
+            dstw[it] = w;
+            acc.add(w, r0 + lr, it - lr * P.wpr);
+        }
+    }
+    if (bbox) acc.flush(bbox + 4 * mask);
+    cbase += (uint32_t)nch;
+}
+
+typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)
+typedef SeSpec<3, 1, 1, 0, 0> SeRect3;
+typedef SeSpec<5, 0, 2, 2, 0> SeEllipse5;
+typedef SeSpec<5, 2, 2, 2, 0> SeRect5;
+typedef SeSpec<5, 0, 0, 2, 0> SeCross5;
+typedef SeSpec<7, 0, 2, 3, 3> SeEllipse7;
+typedef SeSpec<7, 3, 3, 3, 3> SeRect7;
+typedef SeSpec<7, 0, 0, 0, 3> SeCross7;
+typedef SeSpec<1, 0, 0, 0, 0> SeNone;       // pack only / 1x1
+
+template <class SE>
+bool se_matches(const ErodeParams& P) {
+    if (P.k != SE::k || !P.spans_ok) return false;
+    for (int i = 0; i < SE::k; ++i)
+        if (P.span_a[i] != SE::hw(i) || P.span_b[i] != SE::hw(i)) return false;
+    return true;
+}
+
+}  // namespace

@@ -516,9 +516,10 @@ class FrameBatch:
         self.max_b = int(n_boxes.max()) if self.F else 0
         sm, sb, sc = int(n_masks.sum()), int(n_boxes.sum()), int(self.h_cnt_off[-1])
         # one allocation for everything the step zeroes:
-        # mask bbox [sm,4] | total | n_in_box | n_valid | inside | agg(int64 x8)
+        # mask bbox [sm,4] | total | n_in_box | n_valid | inside | sched [F+2] | agg(int64 x8)
         self._o = 4 * sm
-        self._nz = self._o + sm + sb + self.F + sc
+        self._ns = self._o + sm + sb + self.F + sc
+        self._nz = self._ns + self.F + 2
         self._nz += self._nz & 1
         self.counters = torch.zeros(self._nz + 16, dtype=torch.int32, device=ctx.device)
         o = self._o
@@ -527,6 +528,7 @@ class FrameBatch:
         self.n_in_box = self.counters[o + sm:o + sm + sb]
         self.n_valid = self.counters[o + sm + sb:o + sm + sb + self.F]
         self.inside = self.counters[o + sm + sb + self.F:o + sm + sb + self.F + sc]
+        self.sched = self.counters[self._ns:self._ns + self.F + 2]
         self.agg = self.counters[self._nz:].view(torch.int64)
         self.best_idx = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
         self.best_cnt = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
@@ -543,29 +545,56 @@ class FrameBatch:
         self.launches_per_run = 0
 
     def run(self, erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True,
-            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None):
+            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, persistent=False):
         """memset + erode/pack + fused point pass + per-car decision, all async
-        on the current stream.  Returns nothing; read ``results()``."""
+        on the current stream.  Returns nothing; read ``results()``.
+
+        ``persistent=True`` hands ``lf_process_batch`` its scheduler words, so that
+        erosion and the point pass run as ONE persistent kernel when the masks
+        allow it (measured slower than the two launches on B200, see DESIGN.md 5);
+        the default issues the stand-alone launches, ``mark(name)`` between them."""
         ctx, lib = self.ctx, self.ctx.lib
         ctx.set_camera(self.TrVeloToRect, self.camera.K, self.camera.width, self.camera.height)
         st = ctx.stream
         launches = 1
+        timed = mark is not None
         mark = mark or (lambda name: None)
         mark('begin')
         check(lib.lf_zero_counters(ctx.h, ptr(self.counters), self.counters.numel() * 4, st), ctx.h)
         mark('zero')
-        if not isinstance(self.masks, PackedMasks) and self.masks is not None and len(self.masks):
+        raw = not isinstance(self.masks, PackedMasks) and self.masks is not None and len(self.masks) > 0
+        iters, se, mode, mt = 0, None, 0, None
+        if raw:
             iters = int(erosion_iterations) if erosion_kernel_size else 0
             se = structuring_element(shape, erosion_kernel_size) if iters else None
             mode = _mask_mode(self.masks, float_threshold)
             mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
+        bbox = self.packed.bbox if isinstance(self.masks, PackedMasks) else self.mask_bbox
+        if persistent and self.car_bits is None:
+            split = timed and self.F and self.max_n        # time the persistent kernel apart from K6
+            check(lib.lf_process_batch(
+                ctx.h, ptr(self.points), ptr(self.pt_off), ptr(mt) if raw else None, mode, len(mt) if raw else 0,
+                ptr(self.mask_off), se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
+                ptr(self.packed.words), ptr(bbox), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
+                self.F, self.max_n, self.max_m, self.max_b, float(max_depth), int(use_oriented), int(min_points),
+                ptr(self.total), ptr(self.inside), ptr(self.n_in_box), ptr(self.n_valid),
+                None if split else ptr(self.best_idx), None if split else ptr(self.best_cnt),
+                None if split else ptr(self.agg), ptr(self.sched), st), ctx.h)
+            mark('batch')
+            if split:
+                check(lib.lf_car_stats(ctx.h, ptr(self.total), ptr(self.inside), ptr(self.mask_off),
+                                       ptr(self.box_off), ptr(self.cnt_off), self.F, int(min_points),
+                                       ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), st), ctx.h)
+            mark('car_stats')
+            self.launches_per_run = 3 if (self.F and self.max_n) else (2 if raw else 1)
+            return
+        if raw:
             check(lib.lf_erode_pack(ctx.h, ptr(mt), mode, len(mt), self.camera.height, self.camera.width,
                                     se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
                                     ptr(self.packed.words), ptr(self.mask_bbox), st), ctx.h)
             launches += 1
         mark('erode_pack')
         if self.F and self.max_n:
-            bbox = self.packed.bbox if isinstance(self.masks, PackedMasks) else self.mask_bbox
             check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
                                     ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
                                     self.F, self.max_n, self.max_m, self.max_b, float(max_depth),

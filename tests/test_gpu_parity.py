@@ -269,6 +269,61 @@ def test_fused_batch_matches_oracle_on_all_sample_frames(LF, calib, golden, vari
         assert np.array_equal(res[k], res2[k]), k
 
 
+@pytest.mark.parametrize('variant', ['erosion3', 'noerosion', 'erosion7', 'rect5x2_aabb'])
+def test_persistent_batch_kernel_equals_separate_launches(LF, calib, golden, variant):
+    """lf_process_batch (one persistent kernel: erode items and fuse items claimed from a
+    dependency-ordered queue) against the oracle and against the stand-alone launches,
+    on the ragged 20-frame sample batch (M = 0..16 per frame, frames without boxes)."""
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames']
+    pts, masks, boxes, raws = _batch_inputs(frames, cam, TVC, LF)
+    kw = {'erosion3': dict(erosion_kernel_size=3, erosion_iterations=1, max_depth=50, use_oriented=True),
+          'noerosion': dict(erosion_kernel_size=0, erosion_iterations=1, max_depth=50, use_oriented=True),
+          'erosion7': dict(erosion_kernel_size=7, erosion_iterations=1, max_depth=50, use_oriented=True),
+          'rect5x2_aabb': dict(erosion_kernel_size=5, erosion_iterations=2, max_depth=30, use_oriented=False,
+                               shape=LF.MORPH_RECT)}[variant]
+    corners = np.concatenate([np.array([b['corners_velo'] for b in bs], dtype=np.float64).reshape(-1, 8, 3)
+                              for bs in boxes])
+    u8 = (np.concatenate(masks) != 0).astype(np.uint8)
+    batch = LF.FrameBatch(np.concatenate(pts), [len(p) for p in pts], u8, [len(m) for m in masks], corners,
+                          [len(b) for b in boxes], cam, TVR)
+    batch.run(min_points=10, persistent=False, **kw)
+    sep = batch.results()
+    sep_packed = batch.packed.words.cpu().numpy().copy()
+    sep_bbox = batch.mask_bbox.cpu().numpy().copy()
+    batch.packed.words.zero_()
+    for rep in range(3):                       # the queue is re-armed by the counter memset
+        batch.run(min_points=10, persistent=True, **kw)
+        got = batch.results()
+        for k in sep:
+            assert np.array_equal(sep[k], got[k]), (k, rep)
+        assert np.array_equal(batch.packed.words.cpu().numpy(), sep_packed)
+        assert np.array_equal(batch.mask_bbox.cpu().numpy(), sep_bbox)
+    if 'shape' not in kw:
+        for i in (0, 5, 19):
+            want = P.process_frame(pts[i], raws[i], masks[i], cam, TVC, TVR, min_points=10, **kw)
+            m0, m1 = batch.h_mask_off[i], batch.h_mask_off[i + 1]
+            assert got['n_valid'][i] == want['valid'].sum()
+            assert np.array_equal(got['total'][m0:m1], want['total'])
+            gi = got['inside'][batch.h_cnt_off[i]:batch.h_cnt_off[i + 1]].reshape(want['inside'].shape)
+            assert np.array_equal(gi, want['inside'])
+
+
+def test_persistent_batch_kernel_many_frames(LF, calib):
+    """More frames than resident CTAs' worth of work: 300 synthetic frames, persistent
+    kernel == stand-alone launches on every counter."""
+    from lidar_object_detection_b200 import synthetic as S
+    cam, TVC, TVR = calib
+    sb = S.SyntheticBatch(300, cam, TVC, TVR, ncars=16, seed=99)
+    sb.batch.run(3, 1, 50, 10, True, persistent=False)
+    sep = sb.batch.results()
+    sb.batch.run(3, 1, 50, 10, True, persistent=True)
+    got = sb.batch.results()
+    for k in sep:
+        assert np.array_equal(sep[k], got[k]), k
+    assert got['total'].sum() > 0 and got['inside'].sum() > 0
+
+
 # ------------------------------------------------------------------ A11 CSV, end to end
 
 class _NpzSource:
