@@ -87,14 +87,14 @@ struct ClaimHook {
 };
 
 template <class SE>
-__global__ void __launch_bounds__(FUSE_THREADS, 3)
+__global__ void __launch_bounds__(BATCH_THREADS, 3)
 lf_batch_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A,
                 const __grid_constant__ ErodeParams P, const __grid_constant__ BatchSched S,
                 const uint8_t* __restrict__ masks, uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t er_full[ER_STAGES_BATCH];
     __shared__ __align__(8) uint64_t fu_full[FUSE_STAGES];
-    __shared__ __align__(8) uint64_t fu_empty[FUSE_STAGES];
+    __shared__ int fu_cnt[FUSE_STAGES];
     __shared__ WorkItem s_next;
     const int tid = threadIdx.x;
     const bool sched = tid == 32 * FUSE_CONSUMERS;         // lane 0 of the extra warp: scheduler + copy issuer
@@ -102,7 +102,7 @@ lf_batch_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseA
         for (int s = 0; s < ER_STAGES_BATCH; ++s) mbar_init(&er_full[s], 1);
         for (int s = 0; s < FUSE_STAGES; ++s) {
             mbar_init(&fu_full[s], 1);
-            mbar_init(&fu_empty[s], FUSE_CONSUMERS);
+            fu_cnt[s] = 0;
         }
         mbar_fence_init();
     }
@@ -131,7 +131,7 @@ lf_batch_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseA
             __syncthreads();
             if (tid == 0) red_release_gpu_add(S.done + cur.b, 1);     // ... before the frame counts this mask
         } else {
-            fuse_item(cam, A, cur.a, cur.b, smem, fu_full, fu_empty, fbase, ClaimHook{S, A, &s_next});
+            fuse_item<BATCH_THREADS>(cam, A, cur.a, cur.b, smem, fu_full, fu_cnt, fbase, ClaimHook{S, A, &s_next});
             __syncthreads();
         }
     }
@@ -144,7 +144,7 @@ cudaError_t launch_batch(const LfCam& cam, const FuseArgs& A, const ErodeParams&
     cudaError_t e = cudaFuncSetAttribute(lf_batch_kernel<SE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lf_batch_kernel<SE>, FUSE_THREADS, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lf_batch_kernel<SE>, BATCH_THREADS, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;
     const long long grid = (long long)per_sm * sm_count;
@@ -156,7 +156,7 @@ cudaError_t launch_batch(const LfCam& cam, const FuseArgs& A, const ErodeParams&
     const long long nt = ((long long)S.F + S2.lag) * (S.slots_m + S.chunks);
     if (nt >= 0x7FFF0000LL) return cudaErrorInvalidValue;
     S2.n_tickets = (int)nt;
-    lf_batch_kernel<SE><<<(unsigned)grid, FUSE_THREADS, smem, st>>>(cam, A, P, S2, masks, packed, bbox);
+    lf_batch_kernel<SE><<<(unsigned)grid, BATCH_THREADS, smem, st>>>(cam, A, P, S2, masks, packed, bbox);
     return cudaGetLastError();
 }
 

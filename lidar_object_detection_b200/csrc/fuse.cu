@@ -13,21 +13,21 @@
 
 namespace {
 
-__global__ void __launch_bounds__(FUSE_THREADS, 3)
+__global__ void __launch_bounds__(FUSE_THREADS, 5)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
-    __shared__ __align__(8) uint64_t empty_bar[FUSE_STAGES];
+    __shared__ int stage_cnt[FUSE_STAGES];
     if (threadIdx.x == 0) {
         for (int s = 0; s < FUSE_STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], FUSE_CONSUMERS);
+            stage_cnt[s] = 0;
         }
         mbar_fence_init();
     }
     __syncthreads();
     uint32_t fbase = 0;
-    fuse_item(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, empty_bar, fbase, FuseNoHook());
+    fuse_item<FUSE_THREADS>(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, stage_cnt, fbase, FuseNoHook());
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -112,6 +112,7 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
                         4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4) + 16 * (size_t)A.smem_cars;
     if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
     LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     const int64_t chunks = (max_points_per_frame + FUSE_SEG - 1) / FUSE_SEG;
     if (chunks > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
     dim3 grid((unsigned)chunks, (unsigned)F);

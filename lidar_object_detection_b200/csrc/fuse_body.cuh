@@ -8,10 +8,11 @@ namespace {
 
 
 constexpr int FUSE_CONSUMERS = 8;                         // consumer warps
-constexpr int FUSE_THREADS = 32 * (FUSE_CONSUMERS + 1);   // + one producer warp (bulk-copy issue)
+constexpr int FUSE_THREADS = 32 * FUSE_CONSUMERS;         // stand-alone kernel: every warp consumes
+constexpr int BATCH_THREADS = FUSE_THREADS + 32;          // persistent kernel: + one scheduler warp
 constexpr int FUSE_SUB = 1024;                            // points per stage = 16 KB
 constexpr int FUSE_GROUPS = FUSE_SUB / 32;                // 32-point groups per stage, handed out dynamically
-constexpr int FUSE_STAGES = 4;                            // power of two: stage / parity by shifts
+constexpr int FUSE_STAGES = 2;                            // power of two: stage / parity by shifts
 constexpr int FUSE_SUBS_PER_SEG = 16;
 constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 16384 points per CTA
 
@@ -227,23 +228,21 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// Warp-specialised: warp 8 only issues bulk copies (one elected lane), warps 0-7
-// consume.  A stage holds 32 groups of 32 points; consumer warps take groups in
-// order from a shared counter (frustum points cluster in runs of a few hundred,
-// so a static split leaves most warps idle at a block barrier), copy their point
-// to a register, release the group on the stage's "empty" mbarrier and compute.
-// No block-wide barrier inside the streaming loop.
-// One work item = (frame f, segment `seg` of FUSE_SEG points).  Executed by all FUSE_THREADS
-// threads of the CTA.  `full_bar` (count 1) and `empty_bar` (count FUSE_CONSUMERS) are
-// initialised once per CTA; their phases run on from item to item: `fbase` counts the
-// sub-chunks this CTA has streamed so far, sub-chunk c lives in stage c % FUSE_STAGES.
-// `hook()` is called once by the producer lane when it has issued its last copy (the
-// persistent kernel claims its next work item there).
+// One work item = (frame f, segment `seg` of FUSE_SEG points), executed by all NT threads
+// of the CTA; warps 0..FUSE_CONSUMERS-1 consume, further warps only take part in the block
+// barriers.  The segment streams through a ring of FUSE_STAGES bulk-copy stages.  There is
+// no producer warp: each consumer warp counts itself out of a stage on a shared counter
+// and the LAST one out refills that stage, so nobody ever waits for a stage to drain.
+// `full_bar` (count 1) is initialised once per CTA and `stage_cnt` zeroed; the barrier
+// phases run on from item to item: `fbase` counts the sub-chunks this CTA has streamed so
+// far, sub-chunk c lives in stage c % FUSE_STAGES.  `hook()` is called once by thread
+// 32 * FUSE_CONSUMERS, if the CTA has one (the persistent kernel claims its next work item
+// there, overlapped with the item).
 struct FuseNoHook { __device__ __forceinline__ void operator()() const {} };
 
-template <class Hook>
+template <int NT, class Hook>
 __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, int f, int seg, uint8_t* smem,
-                                          uint64_t* full_bar, uint64_t* empty_bar, uint32_t& fbase, Hook hook) {
+                                          uint64_t* full_bar, int* stage_cnt, uint32_t& fbase, Hook hook) {
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
     const int64_t seg0 = p0 + (int64_t)seg * FUSE_SEG;
     if (seg0 >= p1) {
@@ -268,7 +267,7 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
     const float4* src = A.pts + seg0;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    if (warp == FUSE_CONSUMERS && lane == 0) {
+    if (threadIdx.x == 0) {
         fence_proxy_async_smem();                          // the previous item read these stages
         for (int i = 0; i < FUSE_STAGES && i < nsub; ++i) {
             const int s = (int)((fbase + i) % FUSE_STAGES);
@@ -281,10 +280,10 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
         const double* gsrc = (const double*)(A.boxes + b0);
         double* sdst = (double*)s_box;
         const int nd = B * (int)(sizeof(lf_box) / 8);
-        for (int i = threadIdx.x; i < nd; i += FUSE_THREADS) sdst[i] = gsrc[i];
+        for (int i = threadIdx.x; i < nd; i += NT) sdst[i] = gsrc[i];
         const int nc = A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 1;
-        for (int i = threadIdx.x; i < nc; i += FUSE_THREADS) s_inside[i] = 0;
-        for (int c = threadIdx.x; c < M; c += FUSE_THREADS) {
+        for (int i = threadIdx.x; i < nc; i += NT) s_inside[i] = 0;
+        for (int c = threadIdx.x; c < M; c += NT) {
             int4 bb = make_int4(0, 0, cam.W - 1, cam.H - 1);
             if (A.mask_bbox) {                             // record of lf_erode_pack: zeros = empty mask
                 const int4 r = __ldg((const int4*)A.mask_bbox + m0 + c);
@@ -295,19 +294,8 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
     }
     __syncthreads();
 
-    if (warp == FUSE_CONSUMERS) {
-        if (lane == 0) {                                   // producer: refill a stage once all its groups were read
-            for (int i = FUSE_STAGES; i < nsub; ++i) {
-                const uint32_t c = fbase + (uint32_t)i;
-                const int s = (int)(c % FUSE_STAGES);
-                mbar_wait(&empty_bar[s], (c / FUSE_STAGES - 1u) & 1u);
-                const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
-                fence_proxy_async_smem();
-                mbar_expect_tx(&full_bar[s], bytes);
-                bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)i * FUSE_SUB, bytes, &full_bar[s]);
-            }
-            hook();
-        }
+    if (warp >= FUSE_CONSUMERS) {
+        if (threadIdx.x == 32 * FUSE_CONSUMERS) hook();
     } else {
         const int plane32 = cam.H * cam.wpr;               // words per packed mask (< 2^25, see lf_set_camera)
         const uint32_t* mask_base = A.packed + (int64_t)m0 * plane32;
@@ -344,22 +332,32 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
                                  s_inside, s_nin, s_total, my_valid);
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty_bar[s]);
+            if (lane == 0 && atomicAdd(&stage_cnt[s], 1) == FUSE_CONSUMERS - 1) {
+                // last warp out of this stage: every warp's reads are done -> refill it
+                atomicExch(&stage_cnt[s], 0);
+                const int i = sub + FUSE_STAGES;
+                if (i < nsub) {
+                    const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
+                    fence_proxy_async_smem();
+                    mbar_expect_tx(&full_bar[s], bytes);
+                    bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)i * FUSE_SUB, bytes, &full_bar[s]);
+                }
+            }
         }
         const unsigned vb = __reduce_add_sync(0xFFFFFFFFu, (unsigned)my_valid);
         if (lane == 0 && vb) atomicAdd(s_nvalid, (int)vb);
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < M * B; i += FUSE_THREADS) {
+    for (int i = threadIdx.x; i < M * B; i += NT) {
         const int c = i / B, b = i - c * B;
         const int v = s_inside[c * A.smem_boxes + b];
         if (v) atomicAdd(A.inside + A.cnt_off[f] + i, v);
     }
-    for (int c = threadIdx.x; c < M; c += FUSE_THREADS) {
+    for (int c = threadIdx.x; c < M; c += NT) {
         const int v = s_total[c];
         if (v) atomicAdd(A.total + m0 + c, v);
     }
-    for (int b = threadIdx.x; b < B; b += FUSE_THREADS) {
+    for (int b = threadIdx.x; b < B; b += NT) {
         const int v = s_nin[b];
         if (v) atomicAdd(A.n_in_box + b0 + b, v);
     }
