@@ -33,6 +33,16 @@ if ROOT not in sys.path:
 CALIB_ROOT = os.path.join(ROOT, 'tests', 'golden', 'kitti360_sample')
 METRIC = 'points/sec (project+mask+bbox eval)'
 FRAMES, NCARS, RINGS, AZ = 1024, 16, 64, 2048
+KSIZE = 3
+# BASELINE.json configs[2] (the metric's configuration) and configs[4] (dense stress)
+WORKLOADS = {'cfg3': dict(frames=1024, ncars=16, rings=64, az=2048, ksize=3),
+             'cfg5': dict(frames=64, ncars=64, rings=64, az=32768, ksize=7)}
+
+
+def set_workload(name, frames=None):
+    global FRAMES, NCARS, RINGS, AZ, KSIZE
+    w = WORKLOADS[name]
+    FRAMES, NCARS, RINGS, AZ, KSIZE = frames or w['frames'], w['ncars'], w['rings'], w['az'], w['ksize']
 W_IMG, H_IMG = 1408, 376
 SEED = 0x5EED0000
 
@@ -44,7 +54,7 @@ def algorithmic_bytes_per_frame(n_points, n_masks, n_boxes):
 
 # --------------------------------------------------------------------------- CPU arm
 
-def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue):
+def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue, workload='cfg3'):
     """One host process: generate ``nframes`` synthetic frames with numpy (untimed),
     then run ``warm`` + ``steps`` frames of the oracle's per-frame pipeline
     (cycling over its frames); only the ``steps`` part is timed."""
@@ -55,6 +65,7 @@ def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue):
     cv2.setNumThreads(1)
     from lidar_object_detection_b200 import kitti360 as K, synthetic as S
     from oracle import pipeline as P
+    set_workload(workload)
     cam, TVC, TVR = K.calibration_chain(CALIB_ROOT)
     cars = S.sort_cars_by_image_area(S.make_cars(nframes, NCARS, seed + 7919 * rank), cam, TVR)
     boxes = S.reference_boxes(cars, cam, TVC)
@@ -66,11 +77,11 @@ def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue):
         frames.append((pts, raw, masks))
     rows = 0
     for i in range(warm):
-        P.process_frame(*frames[i % nframes], cam, TVC, TVR)
+        P.process_frame(*frames[i % nframes], cam, TVC, TVR, erosion_kernel_size=KSIZE)
     barrier.wait()
     t0 = time.time()
     for i in range(steps):
-        out = P.process_frame(*frames[i % nframes], cam, TVC, TVR)
+        out = P.process_frame(*frames[i % nframes], cam, TVC, TVR, erosion_kernel_size=KSIZE)
         rows += len(out['stats'])
     t1 = time.time()
     queue.put((rank, t0, t1, steps * len(frames[0][0]), rows))
@@ -83,14 +94,14 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_reference_throughput(steps, warm=1, distinct_frames=2, workers=None):
+def cpu_reference_throughput(steps, warm=1, distinct_frames=2, workers=None, workload='cfg3'):
     """points/s of the CPU path, one process per host core, each timing ``steps``
     frames (a bounded sample of the workload)."""
     import multiprocessing as mp
     workers = workers or host_cores()
     ctx = mp.get_context('spawn')
     barrier, queue = ctx.Barrier(workers), ctx.Queue()
-    procs = [ctx.Process(target=_cpu_worker, args=(r, distinct_frames, warm, steps, SEED, barrier, queue))
+    procs = [ctx.Process(target=_cpu_worker, args=(r, distinct_frames, warm, steps, SEED, barrier, queue, workload))
              for r in range(workers)]
     for p in procs:
         p.start()
@@ -162,12 +173,12 @@ def run_gpu(args):
     dev = torch.device('cuda', local)
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
-    frames = args.frames
+    frames = FRAMES
 
     # CPU baseline first (rank 0, N = 1 only): spawned host processes, GPU idle meanwhile
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        c = cpu_reference_throughput(steps=args.cpu_frames, warm=1)
+        c = cpu_reference_throughput(steps=args.cpu_frames, warm=1, workload=args.workload)
         cpu = {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': 'port',
                'sample': '%d synthetic frames (%d per host process, %d processes, OPENBLAS/cv2 threads = 1), '
                          '%.1f s wall' % (c['frames'], args.cpu_frames, c['cores'], c['seconds'])}
@@ -184,7 +195,7 @@ def run_gpu(args):
         exch.bind(batch.h_mask_off, sb.n_boxes)
 
     def step(mark=None):
-        batch.run(3, 1, 50, 10, True, mark=mark, persistent=args.persistent)
+        batch.run(KSIZE, 1, 50, 10, True, mark=mark, persistent=args.persistent)
         if exch is not None:
             exch.exchange_batch(batch)
 
@@ -206,7 +217,7 @@ def run_gpu(args):
         res = batch.results()
         for f in (0, frames - 1):
             pts, masks, boxes = sb.host_frame(f)
-            want = P.process_frame(pts, boxes, masks.astype(np.float32), cam, TVC, TVR)
+            want = P.process_frame(pts, boxes, masks.astype(np.float32), cam, TVC, TVR, erosion_kernel_size=KSIZE)
             got_t = res['total'][batch.h_mask_off[f]:batch.h_mask_off[f + 1]]
             got_i = res['inside'][batch.h_cnt_off[f]:batch.h_cnt_off[f + 1]].reshape(want['inside'].shape)
             if not (np.array_equal(got_t, want['total']) and np.array_equal(got_i, want['inside'])
@@ -303,17 +314,18 @@ def run_gpu(args):
         except Exception:
             peak = 6650.0
         step_bytes = sum(algorithmic_bytes_per_frame(n_pts, NCARS, b) for b in sb.n_boxes)
+        se_name = 'SeCross3' if KSIZE == 3 else 'SeEllipse%d' % KSIZE
         if not args.persistent:  # dominant kernel: the erode launch, F*M*H*W bytes in
-            kname, kkey, tkey = 'lf_erode_fast_kernel<SeCross3> (lf_erode_pack)', 'erode_pack', 'lf_erode_fast_kernel'
+            kname, kkey, tkey = 'lf_erode_fast_kernel<%s> (lf_erode_pack)' % se_name, 'erode_pack', 'lf_erode_fast_kernel'
             mask_bytes = frames * NCARS * H_IMG * W_IMG
         else:                   # the persistent kernel does erode + point pass: all algorithmic bytes of the step
-            kname, kkey, tkey = 'lf_batch_kernel<SeCross3> (lf_process_batch: erode+pack and fused point pass)', \
+            kname, kkey, tkey = 'lf_batch_kernel<%s> (lf_process_batch: erode+pack and fused point pass)' % se_name, \
                 'batch', 'lf_batch_kernel'
             mask_bytes = step_bytes
         ach = mask_bytes / (kern_ms[kkey] * 1e-3) / 1e9
         traffic = None
         try:
-            with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as fh:
+            with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json' if args.workload == 'cfg3' else 'none')) as fh:
                 traffic = json.load(fh).get(tkey + '_dram_bytes_per_launch')
         except Exception:
             pass
@@ -322,8 +334,9 @@ def run_gpu(args):
             'warmup': max(args.warmup, 3), 'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f64 projection/containment, u32 bit-masks, i32 counters',
             'data': 'synthetic',
-            'config': {'workload': 'cfg3: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes per GPU, '
-                                   '3x3 ellipse erosion, 50 m gate' % (frames, n_pts, NCARS, W_IMG, H_IMG, NCARS),
+            'config': {'workload': '%s: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes per GPU, '
+                                   '%dx%d ellipse erosion, 50 m gate' % (args.workload, frames, n_pts, NCARS, W_IMG, H_IMG,
+                                                                        NCARS, KSIZE, KSIZE),
                        'frames_per_gpu': frames, 'points_per_frame': n_pts, 'masks_per_frame': NCARS,
                        'l2_policy': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush' % (step_bytes / 1e9),
                        'parallelism': 'frames sharded, dp%d' % world},
@@ -349,14 +362,15 @@ def run_reference(args):
     if rank != 0:
         return
     steps = min(args.steps, 200)             # ~70 ms of CPU work per step and process
-    c = cpu_reference_throughput(steps=steps, warm=min(max(args.warmup, 1), 3))
+    c = cpu_reference_throughput(steps=steps, warm=min(max(args.warmup, 1), 3), workload=args.workload)
     n_pts = RINGS * AZ
     line = {'impl': 'reference', 'metric': METRIC, 'value': c['value'], 'unit': 'points/s',
             'n_gpus': int(os.environ.get('WORLD_SIZE', args.gpus)), 'steps': steps, 'warmup': min(max(args.warmup, 1), 3),
             'ms_per_step': c['seconds'] / steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f64 (numpy) + u8 (cv2)', 'data': 'synthetic',
-            'config': {'workload': 'cfg3-shaped frames: %d pts x %d masks (%dx%d) x <=%d boxes; one step = one '
-                                   'frame per host process' % (n_pts, NCARS, W_IMG, H_IMG, NCARS),
+            'config': {'workload': '%s-shaped frames: %d pts x %d masks (%dx%d) x <=%d boxes, %dx%d ellipse erosion; '
+                                   'one step = one frame per host process' % (args.workload, n_pts, NCARS, W_IMG, H_IMG,
+                                                                              NCARS, KSIZE, KSIZE),
                        'points_per_frame': n_pts, 'masks_per_frame': NCARS},
             'cpu_baseline': {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': 'port',
                              'sample': '%d frames over %d host processes, %.1f s' % (c['frames'], c['cores'], c['seconds'])},
@@ -371,7 +385,9 @@ def main():
     ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--frames', type=int, default=FRAMES, help='frames per GPU (default: cfg3, 1024)')
+    ap.add_argument('--frames', type=int, default=None, help='frames per GPU (default: the workload\'s, cfg3 1024)')
+    ap.add_argument('--workload', default='cfg3', choices=sorted(WORKLOADS),
+                    help='cfg3 = the metric\'s configuration (default); cfg5 = dense stress, 2M points x 64 masks, 7x7')
     ap.add_argument('--cpu-frames', type=int, default=20,
                     help='frames each host process times for cpu_baseline (~70 ms each: ~1.5 s wall, ~20 core-seconds)')
     ap.add_argument('--e2e-steps', type=int, default=3)
@@ -382,6 +398,7 @@ def main():
                     help='one persistent erode+fuse kernel (lf_process_batch with scheduler words) instead of '
                          'the stand-alone erode / fuse launches')
     args = ap.parse_args()
+    set_workload(args.workload, args.frames)
     if args.impl == 'reference':
         run_reference(args)
     else:

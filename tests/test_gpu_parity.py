@@ -445,6 +445,31 @@ def test_synthetic_batch_matches_oracle_and_invariants(LF, calib):
     assert np.array_equal(res0['n_valid'], res['n_valid']) and np.array_equal(res0['n_in_box'], res['n_in_box'])
 
 
+def test_dense_stress_shape_cfg5(LF, calib):
+    """BASELINE configs[4] in small: 2 097 152-point frames x 64 instances, 7x7 ellipse
+    erosion.  Frame 0 against the oracle (every counter bit-exact); persistent kernel ==
+    stand-alone launches on all frames."""
+    from lidar_object_detection_b200 import synthetic as S
+    cam, TVC, TVR = calib
+    sb = S.SyntheticBatch(3, cam, TVC, TVR, ncars=64, seed=4242, rings=64, azimuths=32768)
+    assert sb.n == 2097152
+    b = sb.batch
+    b.run(7, 1, 50, 10, True)
+    res = b.results()
+    pts, masks, boxes = sb.host_frame(0)
+    want = P.process_frame(pts, boxes, masks.astype(np.float32), cam, TVC, TVR, erosion_kernel_size=7)
+    assert res['n_valid'][0] == want['valid'].sum()
+    assert np.array_equal(res['total'][:64], want['total'])
+    assert np.array_equal(res['n_in_box'][:sb.n_boxes[0]], want['n_in_box'])
+    assert np.array_equal(res['inside'][:b.h_cnt_off[1]].reshape(64, sb.n_boxes[0]), want['inside'])
+    assert _norm_stats(b.frame_stats(res, 0)) == _norm_stats(want['stats'])
+    assert res['total'].sum() > 10000
+    b.run(7, 1, 50, 10, True, persistent=True)
+    got = b.results()
+    for k in res:
+        assert np.array_equal(res[k], got[k]), k
+
+
 def test_mask_bounding_boxes(LF):
     """lf_erode_pack's optional per-mask bounding box (the fused pass culls masks with it)."""
     rng = np.random.default_rng(11)
