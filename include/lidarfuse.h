@@ -195,6 +195,46 @@ int lf_depth_maps(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, do
                   uint64_t* scratch /*DEVICE*/, double* full /*DEVICE or NULL*/,
                   double* per_car /*DEVICE or NULL*/, void* stream);
 
+/* ---- next rows: box projection and 2D matching matrices ---------- */
+
+#define LF_VIEW_VALID           0   /* secondtest.py:350 'valid' */
+#define LF_VIEW_ALL_BEHIND      1   /* :304-305 no corner inside the depth range */
+#define LF_VIEW_NO_INTERSECTION 2   /* :326-334 */
+#define LF_VIEW_TOO_SMALL       3   /* :337-348 projected area < 100 px^2 */
+
+/* What the three reference filters derive from camera.cam2image(corners_cam0.T). */
+typedef struct lf_box2d {
+    int64_t x0, y0, x1, y1;     /* V5 project_3d_bbox_to_2d: min / max pixel over corners with depth > 0 */
+    double avg_depth;           /* np.mean(depth[depth > 0]) (V5:243); 0 when n_front == 0 */
+    double range_avg_depth;     /* np.mean(depth[in range]) (secondtest.py:354) */
+    int32_t n_front;            /* corners with depth > 0; 0 = project_3d_bbox_to_2d returns None */
+    int32_t n_visible;          /* corners with depth > 0.1 inside the image: filter_visible_bboxes keeps >= 2 */
+    int32_t n_in_range;         /* secondtest corners_with_valid_depth */
+    int32_t corners_in_view;    /* secondtest corners_in_view */
+    int32_t view_code;          /* LF_VIEW_* : is_bbox_in_camera_view keeps LF_VIEW_VALID */
+    int32_t pad_;
+} lf_box2d;                     /* 72 bytes */
+
+/* Projects the 8 cam0 corners of n boxes with K (no rectification, as the reference does:
+ * cvs_erosion.py:64, V5:222, secondtest.py:298) and evaluates filter_visible_bboxes
+ * (cvs_erosion.py:55-74), project_3d_bbox_to_2d (V5:215-252) and is_bbox_in_camera_view
+ * (secondtest.py:277-359; depth range and min_points_in_view as there).  u, v, depth
+ * (optional, all or none): the raw per-corner projections, int64 / f64 [n][8]. */
+int lf_project_boxes(lf_ctx* ctx, const double* corners_cam0 /*DEVICE [n][8][3]*/, int64_t n, double depth_min,
+                     double depth_max, int min_points_in_view, lf_box2d* out /*DEVICE [n]*/,
+                     int64_t* u /*DEVICE or NULL*/, int64_t* v /*DEVICE or NULL*/, double* depth /*DEVICE or NULL*/,
+                     void* stream);
+
+/* Per frame f the D_f x B_f matrices of calculate_iou_2d (V4:118-137) and
+ * calculate_matching_score (V5:277-304; weights as there: 0.5, 0.3, 0.2) between the 2D
+ * detections [x1,y1,x2,y2] (f64) and the projected rectangles.  Boxes with n_front == 0
+ * get iou 0 and score -inf.  out_off[f] = start of frame f's row-major [D_f][B_f] block. */
+int lf_match_matrices(lf_ctx* ctx, const double* dets /*DEVICE [sum D][4]*/, const int32_t* det_off /*DEVICE [F+1]*/,
+                      const lf_box2d* rects /*DEVICE [sum B]*/, const int32_t* box_off /*DEVICE [F+1]*/,
+                      const int64_t* out_off /*DEVICE [F+1]*/, int F, int max_pairs_per_frame, double w_iou,
+                      double w_center, double w_size, double* iou /*DEVICE*/, double* score /*DEVICE*/,
+                      void* stream);
+
 /* Synthetic HDL-64-shaped workload (bench / tests only).
  * cars: DEVICE f64 [F][ncars][8] = {cx, cy, cz, yaw, l, w, h, pad} in the velodyne frame. */
 int lf_synth_points(lf_ctx* ctx, const double* cars /*DEVICE*/, int ncars, int F, int rings, int azimuths,

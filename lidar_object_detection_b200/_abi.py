@@ -21,6 +21,12 @@ BOX_DTYPE = np.dtype([('c0', '<f8', 3), ('e1', '<f8', 3), ('e2', '<f8', 3), ('e3
                       ('ee', '<f8', 3), ('amin', '<f8', 3), ('amax', '<f8', 3),
                       ('lo', '<f4', 3), ('hi', '<f4', 3)])
 assert BOX_DTYPE.itemsize == 192
+# numpy mirror of struct lf_box2d (72 bytes)
+BOX2D_DTYPE = np.dtype([('x0', '<i8'), ('y0', '<i8'), ('x1', '<i8'), ('y1', '<i8'), ('avg_depth', '<f8'),
+                        ('range_avg_depth', '<f8'), ('n_front', '<i4'), ('n_visible', '<i4'), ('n_in_range', '<i4'),
+                        ('corners_in_view', '<i4'), ('view_code', '<i4'), ('pad_', '<i4')])
+assert BOX2D_DTYPE.itemsize == 72
+VIEW_VALID, VIEW_ALL_BEHIND, VIEW_NO_INTERSECTION, VIEW_TOO_SMALL = 0, 1, 2, 3
 
 _vp, _i32, _i64, _f64, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_uint64
 
@@ -46,6 +52,8 @@ SIGNATURES = {
     'lf_car_stats': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     'lf_zero_counters': (C.c_int, [_vp, _vp, _i64, _vp]),
     'lf_depth_maps': (C.c_int, [_vp, _vp, _i64, _f64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    'lf_project_boxes': (C.c_int, [_vp, _vp, _i64, _f64, _f64, _i32, _vp, _vp, _vp, _vp, _vp]),
+    'lf_match_matrices': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _f64, _f64, _f64, _vp, _vp, _vp]),
     'lf_synth_points': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _u64, _vp, _vp]),
     'lf_synth_masks': (C.c_int, [_vp, _vp, _i32, _i32, _vp, _f64, _vp, _vp]),
 }

@@ -1,0 +1,142 @@
+"""SURVEY 8(f) 'next' rows: box projection / 2D matching matrices (rank 2), mask resize
+(rank 1), colour buffers (rank 3), I/O formats (rank 4).
+
+Golden vectors: tests/golden/golden_next.json, produced by oracle/gen_golden_next.py from
+the UNMODIFIED reference (secondtest.py, V4, V5, cvs_erosion.py) in the build container.
+CPU tests pin the host restatements against them; ``-m gpu`` tests pin the CUDA path
+against both.  Bars: integers (pixel rectangles, corner counts, verdicts, kept indices)
+bit-exact; IoU bit-exact; scores and mean depths within 1e-12 relative (one fp64
+rounding of a different but fixed summation order, stated here).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, SAMPLE, load_boxes
+
+REASONS = {'valid': 0, 'all_behind_camera': 1, 'no_intersection': 2, 'too_small': 3}
+
+
+@pytest.fixture(scope='module')
+def gnext():
+    with open(os.path.join(GOLDEN, 'golden_next.json')) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope='module')
+def cam():
+    from lidar_object_detection_b200 import kitti360 as K
+    return K.calibration_chain(SAMPLE)[0]
+
+
+def _frames(gnext):
+    return sorted(int(k) for k in gnext if k != '_meta')
+
+
+# ------------------------------------------------------------------ CPU: host restatements
+
+def test_host_projection_and_scores_match_reference(gnext, cam):
+    from lidar_object_detection_b200 import lidarfuse as LF, matching2d as M
+    for fr in _frames(gnext):
+        g = gnext[str(fr)]
+        raw = load_boxes(fr)
+        assert len(raw) == len(g['view'])
+        kept = LF.filter_visible_bboxes(raw, cam)
+        assert [i for i, b in enumerate(raw) if any(b is k for k in kept)] == g['visible_idx']
+        infos = [M.project_3d_bbox_to_2d(b, cam)[0] for b in raw]
+        for info, want in zip(infos, g['rect']):
+            assert (info is None) == (want is None)
+            if want is not None:
+                assert [int(x) for x in info['bbox']] == want['bbox']
+                assert int(info['area']) == want['area']
+                assert float(info['avg_depth']) == want['avg_depth']
+        for d, wi, ws in zip(g['dets'], g['iou'], g['score']):
+            x1, y1, x2, y2 = d
+            di = {'bbox': d, 'center': [(x1 + x2) / 2, (y1 + y2) / 2], 'size': [x2 - x1, y2 - y1],
+                  'area': (x2 - x1) * (y2 - y1)}
+            for info, a, b in zip(infos, wi, ws):
+                if info is None:
+                    assert b is None
+                    continue
+                assert M.calculate_iou_2d(d, info['bbox']) == a
+                assert M.calculate_matching_score(di, info)[0] == b
+
+
+# ------------------------------------------------------------------ GPU: rank 2
+
+@pytest.mark.gpu
+def test_device_box_projection_matches_reference(gnext, cam):
+    from lidar_object_detection_b200 import matching2d as M
+    frames = _frames(gnext)
+    raws = [load_boxes(fr) for fr in frames]
+    allc = np.array([b['corners_cam0'] for raw in raws for b in raw], dtype=np.float64).reshape(-1, 8, 3)
+    rec, u, v, d = M.project_boxes_batched(allc, cam, return_corners=True)     # ONE launch, 992 boxes
+    o = 0
+    for fr, raw in zip(frames, raws):
+        g = gnext[str(fr)]
+        r = rec[o:o + len(raw)]
+        for i, b in enumerate(raw):
+            uu, vv, dd = cam.cam2image(np.array(b['corners_cam0'], dtype=np.float64).T)
+            assert np.array_equal(u[o + i], uu) and np.array_equal(v[o + i], vv)
+            assert np.array_equal(d[o + i], dd)                                   # bit-exact depths
+        assert [i for i in range(len(raw)) if r['n_visible'][i] >= 2] == g['visible_idx']
+        for i, (view, rect) in enumerate(zip(g['view'], g['rect'])):
+            assert int(r['view_code'][i]) == REASONS[view['reason']], (fr, i)
+            if view['reason'] == 'valid':
+                assert int(r['corners_in_view'][i]) == view['corners_in_view']
+                assert int(r['n_in_range'][i]) == view['corners_with_valid_depth']
+                assert abs(float(r['range_avg_depth'][i]) - view['avg_depth']) <= 1e-12 * abs(view['avg_depth'])
+            assert (int(r['n_front'][i]) == 0) == (rect is None)
+            if rect is not None:
+                assert [int(r[k][i]) for k in ('x0', 'y0', 'x1', 'y1')] == rect['bbox']
+                assert abs(float(r['avg_depth'][i]) - rect['avg_depth']) <= 1e-12 * abs(rect['avg_depth'])
+        # the two list-level filters, as the reference's callers use them
+        assert [raw.index(b) for b in M.filter_visible_bboxes_device(raw, cam)] == g['visible_idx']
+        assert [i for i, b in enumerate(raw) if any(b is k for k in M.filter_bboxes_in_camera_view(raw, cam))] == \
+            [i for i, w in enumerate(g['view']) if w['keep']]
+        o += len(raw)
+
+
+@pytest.mark.gpu
+def test_device_match_matrices_and_assignment(gnext, cam):
+    from lidar_object_detection_b200 import matching2d as M
+    frames = _frames(gnext)
+    raws = [load_boxes(fr) for fr in frames]
+    dets = [gnext[str(fr)]['dets'] for fr in frames]
+    allc = np.array([b['corners_cam0'] for raw in raws for b in raw], dtype=np.float64).reshape(-1, 8, 3)
+    rec = M.project_boxes_batched(allc, cam)
+    mats = M.match_matrices(dets, rec, [len(r) for r in raws])                 # ONE launch, all frames
+    for fr, raw, (iou, score) in zip(frames, raws, mats):
+        g = gnext[str(fr)]
+        assert iou.shape == (len(g['dets']), len(raw))
+        for di in range(iou.shape[0]):
+            for bi in range(iou.shape[1]):
+                assert iou[di, bi] == g['iou'][di][bi], (fr, di, bi)              # bit-exact
+                ws = g['score'][di][bi]
+                if ws is None:
+                    assert score[di, bi] == -np.inf
+                else:
+                    assert abs(score[di, bi] - ws) <= 1e-12 * max(1.0, abs(ws))
+    acc = M.assign_detections_batched(dets, raws, cam)
+    for fr, raw, d, a in zip(frames, raws, dets, acc):
+        assert a == M.assign_detections(d, raw, cam), fr
+
+
+@pytest.mark.gpu
+def test_device_box_projection_edge_cases(cam):
+    from lidar_object_detection_b200 import matching2d as M
+    assert len(M.project_boxes_batched(np.zeros((0, 8, 3)), cam)) == 0
+    c = np.zeros((3, 8, 3))
+    c[0, :, 2] = -5.0                                   # all behind the camera
+    c[1] = np.array([[x, y, z] for z in (10.0, 12.0) for y in (-1.0, 1.0) for x in (-1.0, 1.0)])
+    c[2, :, 2] = 0.0                                    # depth exactly 0 -> -1e-6 (cam2image)
+    rec, u, v, d = M.project_boxes_batched(c, cam, return_corners=True)
+    assert rec['n_front'][0] == 0 and rec['view_code'][0] == 1
+    assert rec['n_front'][1] == 8 and rec['view_code'][1] == 0 and rec['n_visible'][1] == 8
+    assert np.all(d[2] == -1e-6) and rec['n_front'][2] == 0
+    for i in range(3):
+        uu, vv, dd = cam.cam2image(c[i].T.copy())
+        assert np.array_equal(u[i], uu) and np.array_equal(v[i], vv) and np.array_equal(d[i], dd)
+    assert M.match_matrices([], rec[:0], []) == []
