@@ -195,6 +195,16 @@ int lf_depth_maps(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, do
                   uint64_t* scratch /*DEVICE*/, double* full /*DEVICE or NULL*/,
                   double* per_car /*DEVICE or NULL*/, void* stream);
 
+/* ---- next rows: mask resize to camera resolution ------------------ */
+
+/* cv2.resize(mask.astype(np.uint8), (W, H)) with the default INTER_LINEAR
+ * (cvs_erosion.py:153; V4:293; V5:531), bit-exact with OpenCV's uint8 path: copy when the
+ * sizes agree, the 2x2 average OpenCV substitutes for an exact 2x downscale, otherwise
+ * the 11-bit fixed-point bilinear.  src uint8 [m][h][w] -> dst uint8 [m][H][W]; feed dst
+ * to lf_erode_pack (mode 0, iterations 0) to get the "> 0.5" mask the gather reads. */
+int lf_resize_masks(lf_ctx* ctx, const uint8_t* src /*DEVICE*/, int64_t m, int h, int w, uint8_t* dst /*DEVICE*/,
+                    int H, int W, void* stream);
+
 /* ---- next rows: box projection and 2D matching matrices ---------- */
 
 #define LF_VIEW_VALID           0   /* secondtest.py:350 'valid' */

@@ -230,16 +230,49 @@ def erode_masks(masks, erosion_kernel_size=3, erosion_iterations=1, shape=MORPH_
 # A6  point-in-mask gather
 # --------------------------------------------------------------------------
 
+def resize_masks(masks, size, device=None):
+    """``cv2.resize(mask.astype(np.uint8), (W, H))`` for a stack of masks, on the device
+    and bit-exact with OpenCV's default INTER_LINEAR (cvs_erosion.py:153; V4:293; V5:531).
+
+    masks [M,h,w]: uint8 / bool as they are, float32 truncated like ``astype(np.uint8)``
+    (only values >= 1 survive; the reference's masks are 0.0 / 1.0).  ``size`` = (W, H),
+    OpenCV's argument order, or a camera.  Returns uint8 [M,H,W] (numpy in -> numpy out)."""
+    ctx = get_ctx(device)
+    W, H = (size.width, size.height) if hasattr(size, 'width') else (int(size[0]), int(size[1]))
+    was_np = _is_np(masks)
+    if isinstance(masks, (list, tuple)):
+        masks = np.stack(masks) if len(masks) else np.zeros((0, 1, 1), np.uint8)
+    t = _dev(masks, ctx)
+    if t.ndim != 3:
+        raise ValueError('masks must be [M,h,w]')
+    if t.dtype == torch.bool:
+        t = t.view(torch.uint8)
+    elif t.dtype != torch.uint8:
+        t = t.clamp(0, 255).to(torch.uint8)              # astype(np.uint8) truncation of 0.0 / 1.0 masks
+    M, h, w = t.shape
+    out = torch.empty((M, H, W), dtype=torch.uint8, device=ctx.device)
+    check(ctx.lib.lf_resize_masks(ctx.h, ptr(t), M, h, w, ptr(out), H, W, ctx.stream), ctx.h)
+    return out.cpu().numpy() if was_np else out
+
+
 def _as_packed(masks, camera, ctx, float_threshold='ge_one'):
     if isinstance(masks, PackedMasks):
         pm = masks
-    else:
-        pm = erode_pack(masks, 0, 0, float_threshold=float_threshold, device=ctx.device)
-    if len(pm) and (pm.H != camera.height or pm.W != camera.width):
-        # cvs_erosion.py:153 resizes with cv2.resize; only the identity case
-        # (retina_masks=True) is on the device path so far.
-        raise ValueError('masks must be at camera resolution %dx%d' % (camera.width, camera.height))
-    return pm
+        if len(pm) and (pm.H != camera.height or pm.W != camera.width):
+            masks = pm.unpack(ctx)                       # 0/1 bytes at the masks' own resolution
+        else:
+            return pm
+    if isinstance(masks, (list, tuple)):
+        masks = np.stack(masks) if len(masks) else np.zeros((0, camera.height, camera.width), np.uint8)
+    shape = tuple(masks.shape[1:]) if len(masks) else (camera.height, camera.width)
+    if len(masks) and shape != (camera.height, camera.width):
+        # cvs_erosion.py:153: cv2.resize(mask.astype(np.uint8), (W, H)), then "> 0.5"
+        if not isinstance(masks, torch.Tensor):
+            masks = np.asarray(masks)
+            if masks.dtype != np.uint8 and masks.dtype != np.bool_:
+                masks = masks.astype(np.uint8)
+        masks = resize_masks(_dev(masks, ctx), camera, device=ctx.device)
+    return erode_pack(masks, 0, 0, float_threshold=float_threshold, device=ctx.device)
 
 
 def mask_membership(u_valid, v_valid, masks, camera, device=None):
@@ -538,8 +571,12 @@ class FrameBatch:
             self.packed = self.masks
         else:
             H, W = camera.height, camera.width
+            self._native = None
             if self.masks is not None and n_m and tuple(self.masks.shape[1:]) != (H, W):
-                raise ValueError('masks must be at camera resolution %dx%d' % (W, H))
+                # masks below camera resolution (YOLO without retina_masks): eroded where they
+                # are, THEN resized, as cvs_erosion.py:96-106 / :153 do -- see run()
+                self._native = self.masks
+                self.masks = torch.empty((n_m, H, W), dtype=torch.uint8, device=ctx.device)
             self.packed = PackedMasks(torch.empty((n_m, H, (W + 31) // 32), dtype=torch.int32,
                                                   device=ctx.device), H, W)
         self.launches_per_run = 0
@@ -564,6 +601,14 @@ class FrameBatch:
         mark('zero')
         raw = not isinstance(self.masks, PackedMasks) and self.masks is not None and len(self.masks) > 0
         iters, se, mode, mt = 0, None, 0, None
+        if raw and getattr(self, '_native', None) is not None:
+            # erode at the masks' own resolution, resize like cv2.resize, pack without erosion
+            # (two extra launches and temporaries: this path is not CUDA-graph capturable)
+            pm = erode_pack(self._native, erosion_kernel_size, erosion_iterations, shape,
+                            float_threshold=float_threshold, device=ctx.device)
+            check(lib.lf_resize_masks(ctx.h, ptr(pm.unpack(ctx)), len(pm), pm.H, pm.W, ptr(self.masks),
+                                      self.camera.height, self.camera.width, st), ctx.h)
+            erosion_kernel_size, erosion_iterations = 0, 0
         if raw:
             iters = int(erosion_iterations) if erosion_kernel_size else 0
             se = structuring_element(shape, erosion_kernel_size) if iters else None

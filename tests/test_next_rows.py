@@ -140,3 +140,59 @@ def test_device_box_projection_edge_cases(cam):
         uu, vv, dd = cam.cam2image(c[i].T.copy())
         assert np.array_equal(u[i], uu) and np.array_equal(v[i], vv) and np.array_equal(d[i], dd)
     assert M.match_matrices([], rec[:0], []) == []
+
+
+# ------------------------------------------------------------------ GPU: rank 1 (mask resize)
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('src', [(376, 1408), (384, 1408), (160, 608), (104, 384), (188, 704), (752, 2816),
+                                 (100, 333), (3, 5), (1, 1)])
+def test_device_resize_is_bit_exact_with_cv2(src):
+    """cv2.resize(u8, (W, H)) (default INTER_LINEAR) against lf_resize_masks: identity,
+    the 2x2-average substitution at exactly 2x, fixed-point bilinear up and down;
+    binary masks (the reference's case) and full-range grey values."""
+    import cv2
+    from lidar_object_detection_b200 import lidarfuse as LF
+    rng = np.random.default_rng(src[0] * 7919 + src[1])
+    h, w = src
+    imgs = [(rng.random((h, w)) < 0.3).astype(np.uint8), rng.integers(0, 256, (h, w), dtype=np.uint8),
+            np.zeros((h, w), np.uint8)]
+    cv2.circle(imgs[2], (w // 2, h // 2), max(1, min(h, w) // 3), 1, -1)
+    stack = np.stack(imgs)
+    for (W, H) in [(1408, 376), (1000, 123), (33, 17)]:
+        got = LF.resize_masks(stack, (W, H))
+        assert got.shape == (3, H, W) and got.dtype == np.uint8
+        for i in range(3):
+            assert np.array_equal(got[i], cv2.resize(imgs[i], (W, H))), (src, (W, H), i)
+
+
+@pytest.mark.gpu
+def test_low_resolution_masks_follow_the_reference_order(cam):
+    """Masks below camera resolution: the reference erodes them where they are
+    (cvs_erosion.py:96-106) and resizes inside extract_car_points_by_mask (:153).  The
+    batch path and the function surface do the same; all counters bit-exact with the oracle."""
+    import cv2
+    from conftest import load_frame, standin
+    from lidar_object_detection_b200 import kitti360 as K, lidarfuse as LF
+    from oracle import pipeline as P
+    camera, TVC, TVR = K.calibration_chain(SAMPLE)
+    for fr, size in ((100, (704, 188)), (947, (608, 160))):
+        pts, raw = load_frame(fr), load_boxes(fr)
+        full = standin(fr, camera)[0]
+        low = np.stack([cv2.resize(m.astype(np.uint8), size, interpolation=cv2.INTER_NEAREST) for m in full]) \
+            .astype(np.float32)
+        want = P.process_frame(pts, raw, low, camera, TVC, TVR)
+        boxes = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(raw, camera), TVC)
+        got = LF.process_frames_batched(pts, [len(pts)], low, [len(low)], [boxes], camera, TVR)[0]
+        key = ('car_id', 'matched_bbox_id', 'total_points', 'points_inside_bbox', 'points_outside_bbox')
+        assert [[int(s[k]) for k in key] for s in got] == [[int(s[k]) for k in key] for s in want['stats']]
+        assert sum(s['total_points'] for s in got) > 100
+        # function surface: extract_car_points_by_mask resizes like the reference
+        u, v, d = LF.project_points(pts, TVR, camera)
+        valid = LF.filter_valid(u, v, d, camera)
+        er = LF.erode_masks(low)
+        sets = LF.extract_car_points_by_mask(pts[valid, :3], u[valid], v[valid], er, camera)
+        wsets = P.extract_car_points_by_mask(pts[valid, :3], u[valid], v[valid], P.erode_masks(low), camera)
+        assert [len(s) for s in sets] == [len(s) for s in wsets]
+        for a, b in zip(sets, wsets):
+            assert np.array_equal(np.asarray(a, np.float32).reshape(-1, 3), np.asarray(b, np.float32).reshape(-1, 3))
