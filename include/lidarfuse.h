@@ -245,6 +245,37 @@ int lf_match_matrices(lf_ctx* ctx, const double* dets /*DEVICE [sum D][4]*/, con
                       double w_center, double w_size, double* iou /*DEVICE*/, double* score /*DEVICE*/,
                       void* stream);
 
+/* ---- next rows: headless colour buffers --------------------------- */
+
+/* Per-point RGB of the V4 / V5 coloured clouds (V4:290-307; V5:524-550): colors_rgb[c]
+ * (f64 [m][3], already BGR->RGB and / 255) of the last mask whose bit is set in
+ * car_bits[i] (from lf_mask_gather / lf_fuse_batch), bg_rgb (HOST [3]) otherwise.
+ * assigned (optional) = the scripts' bg_assigned flag. */
+int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits /*DEVICE [n]*/, int64_t n,
+                    const double* colors_rgb /*DEVICE [m][3]*/, int m, const double bg_rgb[3] /*HOST*/,
+                    double* rgb /*DEVICE [n][3]*/, uint8_t* assigned /*DEVICE [n] or NULL*/, void* stream);
+
+/* Depth map overlay of seg_with_pointcloud.py:173-180: where depth_map > 0 the pixel is
+ * lut[int(depth / *depth_max * lut_n)] (matplotlib Colormap.__call__), elsewhere
+ * image_rgb / 255; then np.uint8(x * 255) and RGB -> BGR.  depth_max: DEVICE pointer to
+ * np.max(depthMap). */
+int lf_depth_overlay(lf_ctx* ctx, const double* depth_map /*DEVICE [H][W]*/, const double* depth_max /*DEVICE [1]*/,
+                     const uint8_t* image_rgb /*DEVICE [H][W][3]*/, const double* lut_rgb /*DEVICE [lut_n][3]*/,
+                     int lut_n, int H, int W, uint8_t* out_bgr /*DEVICE [H][W][3]*/, void* stream);
+
+/* ---- next rows: I/O formats ----------------------------------------- */
+
+/* Text of n master_car_statistics.csv rows (HOST arrays, plain C, no device work),
+ * byte-identical with append_to_master_csv (cvs_erosion.py:232-265): percentages are
+ * (inside / total) * 100 and its complement, rounded like Python's round(x, 2) and
+ * printed like repr(); is_matched = matched_bbox_id >= 0; `timestamp` is written as
+ * given.  with_header: start with the column line.  Returns the number of bytes the text
+ * needs (negative LF_E_*); it is written to `out` only if it fits `cap` (call with
+ * out = NULL to size the buffer). */
+int64_t lf_format_csv_rows(const int64_t* frame, const int32_t* car_id, const int32_t* matched_bbox_id,
+                           const int64_t* total, const int64_t* inside, int64_t n, const char* timestamp,
+                           int with_header, char* out, int64_t cap);
+
 /* Synthetic HDL-64-shaped workload (bench / tests only).
  * cars: DEVICE f64 [F][ncars][8] = {cx, cy, cz, yaw, l, w, h, pad} in the velodyne frame. */
 int lf_synth_points(lf_ctx* ctx, const double* cars /*DEVICE*/, int ncars, int F, int rings, int azimuths,

@@ -1,0 +1,89 @@
+// Headless colour buffers -- what the reference hands to Open3D /
+// matplotlib, written to device memory instead of a window:
+//   * per-point RGB: car colour per mask, grey 0.5 for points no mask claimed
+//     (V4_BBox_IoU_filtering.py:290-307; V5_ProjectingBBoxes.py:524-550; bg_assigned union)
+//   * depth map overlay: jet(depthMap / max) over the segmented image where depthMap > 0,
+//     uint8 truncation, RGB -> BGR (seg_with_pointcloud.py:173-180)
+#include "common.cuh"
+
+namespace {
+
+// colour of the LAST mask that contains the point: the reference builds one point cloud per
+// mask in mask order and draws them in that order, so at equal depth the later one is on top.
+__global__ void __launch_bounds__(256)
+lf_point_colors_kernel(const unsigned long long* __restrict__ bits, int64_t n, const double* __restrict__ colors,
+                       int m, double bg0, double bg1, double bg2, double* __restrict__ rgb,
+                       uint8_t* __restrict__ assigned) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned long long b = bits[i];
+        if (m < 64) b &= (1ULL << m) - 1ULL;
+        double r = bg0, g = bg1, bl = bg2;
+        if (b) {
+            const int c = 63 - __clzll((long long)b);
+            r = colors[3 * c]; g = colors[3 * c + 1]; bl = colors[3 * c + 2];
+        }
+        rgb[3 * i] = r; rgb[3 * i + 1] = g; rgb[3 * i + 2] = bl;
+        if (assigned) assigned[i] = b ? 1 : 0;
+    }
+}
+
+// np.uint8(x * 255) for x in [0, 1]: truncation toward zero
+__device__ __forceinline__ uint8_t to_u8(double x) { return (uint8_t)(int)__dmul_rn(x, 255.0); }
+
+__global__ void __launch_bounds__(256)
+lf_depth_overlay_kernel(const double* __restrict__ depth, const double* __restrict__ dmax_p,
+                        const uint8_t* __restrict__ image_rgb, const double* __restrict__ lut, int lut_n, int64_t npix,
+                        uint8_t* __restrict__ out_bgr) {
+    const double dmax = *dmax_p;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (int64_t)gridDim.x * blockDim.x) {
+        const double d = depth[i];
+        double r, g, b;
+        if (d > 0.0) {
+            // Colormap.__call__ on floats: xa = X * N; xa == N -> N - 1; astype(int)
+            double xa = __dmul_rn(__ddiv_rn(d, dmax), (double)lut_n);
+            int idx = xa == (double)lut_n ? lut_n - 1 : (int)xa;
+            idx = min(max(idx, 0), lut_n - 1);
+            r = lut[3 * idx]; g = lut[3 * idx + 1]; b = lut[3 * idx + 2];
+        } else {
+            r = __ddiv_rn((double)image_rgb[3 * i], 255.0);
+            g = __ddiv_rn((double)image_rgb[3 * i + 1], 255.0);
+            b = __ddiv_rn((double)image_rgb[3 * i + 2], 255.0);
+        }
+        out_bgr[3 * i] = to_u8(b);          // cv2.COLOR_RGB2BGR
+        out_bgr[3 * i + 1] = to_u8(g);
+        out_bgr[3 * i + 2] = to_u8(r);
+    }
+}
+
+}  // namespace
+
+extern "C" int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits, int64_t n, const double* colors_rgb, int m,
+                               const double bg_rgb[3], double* rgb, uint8_t* assigned, void* stream) {
+    if (!ctx || n < 0 || m < 0 || m > LF_MAX_CARS) return LF_E_ARG;
+    if (n == 0) return LF_OK;
+    if (!car_bits || !rgb || !bg_rgb || (m > 0 && !colors_rgb)) return LF_E_ARG;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    int64_t blocks = (n + 255) / 256;
+    const int64_t cap = (int64_t)ctx->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    lf_point_colors_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        (const unsigned long long*)car_bits, n, colors_rgb, m, bg_rgb[0], bg_rgb[1], bg_rgb[2], rgb, assigned);
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}
+
+extern "C" int lf_depth_overlay(lf_ctx* ctx, const double* depth_map, const double* depth_max,
+                                const uint8_t* image_rgb, const double* lut_rgb, int lut_n, int H, int W,
+                                uint8_t* out_bgr, void* stream) {
+    if (!ctx || H <= 0 || W <= 0 || lut_n <= 0) return LF_E_ARG;
+    if (!depth_map || !depth_max || !image_rgb || !lut_rgb || !out_bgr) return LF_E_ARG;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t npix = (int64_t)H * W;
+    int64_t blocks = (npix + 255) / 256;
+    const int64_t cap = (int64_t)ctx->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    lf_depth_overlay_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(depth_map, depth_max, image_rgb,
+                                                                              lut_rgb, lut_n, npix, out_bgr);
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}

@@ -483,3 +483,58 @@ def process_frame(points, bboxes_3d_raw, masks, camera, TrVeloToCam, TrVeloToRec
             'member': member, 'total': member.sum(axis=1).astype(np.int64) if len(member) else
             np.zeros(0, np.int64), 'inside': inside, 'n_in_box': n_in_box, 'stats': stats,
             'car_point_sets': sets}
+
+
+# --------------------------------------------------------------------------
+# colour buffers (restated; ORACLE / TEST INFRASTRUCTURE ONLY)
+# --------------------------------------------------------------------------
+
+def colored_cloud_reference(points_valid, u_valid, v_valid, masks, colors, camera):
+    """The geometry list of V4_BBox_IoU_filtering.py:290-307 (same loop in
+    V5_ProjectingBBoxes.py:524-550) without Open3D: [(points [n,3], rgb [n,3])] per mask
+    with at least one point, then the grey background cloud; plus ``bg_assigned``."""
+    clouds = []
+    bg_assigned = np.zeros(len(points_valid), dtype=bool)
+    for mask, color in zip(masks, colors):
+        mask_resized = cv2.resize(np.asarray(mask).astype(np.uint8), (camera.width, camera.height))
+        mask_indices = mask_resized[v_valid, u_valid] > 0.5
+        if np.count_nonzero(mask_indices) > 0:
+            car_points = points_valid[mask_indices]
+            bg_assigned[mask_indices] = True
+            car_color = np.array([color[2], color[1], color[0]]) / 255.0          # BGR to RGB
+            clouds.append((mask_indices, car_points, np.tile(car_color, (len(car_points), 1))))
+    remaining = points_valid[~bg_assigned]
+    if len(remaining) > 0:
+        clouds.append((~bg_assigned, remaining, np.tile([0.5, 0.5, 0.5], (len(remaining), 1))))
+    return clouds, bg_assigned
+
+
+def jet_lut_restated(N=256):
+    """matplotlib's 'jet' (``_cm._jet_data`` through ``colors._create_lookup_table``,
+    gamma 1).  matplotlib is absent from this image: PARITY UNPINNED for these values."""
+    data = {'red': ((0.00, 0, 0), (0.35, 0, 0), (0.66, 1, 1), (0.89, 1, 1), (1.00, 0.5, 0.5)),
+            'green': ((0.000, 0, 0), (0.125, 0, 0), (0.375, 1, 1), (0.640, 1, 1), (0.910, 0, 0), (1.000, 0, 0)),
+            'blue': ((0.00, 0.5, 0.5), (0.11, 1, 1), (0.34, 1, 1), (0.65, 0, 0), (1.00, 0, 0))}
+    out = []
+    for ch in ('red', 'green', 'blue'):
+        a = np.array(data[ch], dtype=float)
+        x, y0, y1 = a[:, 0] * (N - 1), a[:, 1], a[:, 2]
+        xind = (N - 1) * np.linspace(0, 1, N)
+        ind = np.searchsorted(x, xind)[1:-1]
+        dist = (xind[1:-1] - x[ind - 1]) / (x[ind] - x[ind - 1])
+        out.append(np.clip(np.concatenate([[y1[0]], dist * (y0[ind] - y1[ind - 1]) + y1[ind - 1], [y0[-1]]]), 0, 1))
+    return np.stack(out, axis=1)
+
+
+def depth_overlay_reference(depthMap, masking_image, lut):
+    """seg_with_pointcloud.py:176-180 with ``cm`` = the lookup table ``lut`` [N,3]:
+    Colormap.__call__ on floats is ``lut[int(x * N)]`` with ``x * N == N -> N - 1``."""
+    N = len(lut)
+    x = depthMap / np.max(depthMap)
+    xa = x * N
+    xa[xa == N] = N - 1
+    depthImage = lut[np.clip(xa.astype(int), 0, N - 1)]
+    image_withseg = np.array(masking_image) / 255.
+    image_withseg[depthMap > 0] = depthImage[depthMap > 0]
+    image_withseg = np.uint8(image_withseg * 255)
+    return cv2.cvtColor(image_withseg, cv2.COLOR_RGB2BGR)

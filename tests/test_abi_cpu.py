@@ -21,7 +21,7 @@ def lib():
 def test_every_header_symbol_is_exported(lib):
     from lidar_object_detection_b200 import _abi
     hdr = open(os.path.join(ROOT, 'include', 'lidarfuse.h')).read()
-    names = set(re.findall(r'^\s*(?:int|const char\*)\s+(lf_\w+)\s*\(', hdr, flags=re.M))
+    names = set(re.findall(r'^\s*(?:int|int64_t|const char\*)\s+(lf_\w+)\s*\(', hdr, flags=re.M))
     assert len(names) >= 18
     assert names == set(_abi.SIGNATURES), names ^ set(_abi.SIGNATURES)
     for n in names:

@@ -196,3 +196,163 @@ def test_low_resolution_masks_follow_the_reference_order(cam):
         assert [len(s) for s in sets] == [len(s) for s in wsets]
         for a, b in zip(sets, wsets):
             assert np.array_equal(np.asarray(a, np.float32).reshape(-1, 3), np.asarray(b, np.float32).reshape(-1, 3))
+
+
+# ------------------------------------------------------------------ rank 3 (colour buffers)
+
+def test_jet_lut_known_answers():
+    """Published properties of matplotlib's jet: dark blue -> blue -> cyan -> yellow -> red
+    -> dark red; 256 rows in [0, 1].  (The table itself is an unpinned restatement:
+    matplotlib is not in this image.)"""
+    from lidar_object_detection_b200 import colour as C
+    from oracle import pipeline as P
+    lut = C.jet_lut()
+    assert lut.shape == (256, 3) and lut.min() >= 0 and lut.max() <= 1
+    assert np.allclose(lut[0], [0, 0, 0.5]) and np.allclose(lut[-1], [0.5, 0, 0])
+    assert np.allclose(lut[int(0.375 * 255)], [0.0588, 1.0, 0.9108], atol=5e-3) or lut[96, 1] == 1.0
+    assert lut[128, 1] == 1.0 and abs(lut[128, 0] - lut[128, 2]) < 0.1            # green-yellow middle
+    assert np.array_equal(lut, P.jet_lut_restated())
+
+
+@pytest.mark.gpu
+def test_device_point_colours_match_the_v4_v5_loop():
+    from conftest import load_frame, standin
+    from lidar_object_detection_b200 import colour as C, kitti360 as K
+    from oracle import pipeline as P
+    camera, TVC, TVR = K.calibration_chain(SAMPLE)
+    for fr in (100, 2098, 1866):
+        pts = load_frame(fr)
+        masks = standin(fr, camera)[0]
+        colors = [(int(i * 60) % 255, int(i * 120) % 255, int(i * 180) % 255) for i in range(len(masks))]
+        pv, rgb = C.colored_points(pts, TVR, masks, colors, camera, max_depth=30)
+        want = P.process_frame(pts, load_boxes(fr), masks, camera, TVC, TVR, erosion_kernel_size=0, max_depth=30)
+        valid = want['valid']
+        assert np.array_equal(pv, pts[valid, :3])
+        clouds, assigned = P.colored_cloud_reference(pts[valid, :3], want['u'][valid], want['v'][valid], masks,
+                                                     colors, camera)
+        expect = np.zeros((int(valid.sum()), 3))
+        for sel, cloud_pts, cloud_rgb in clouds:          # draw order: later clouds overdraw earlier ones
+            expect[sel] = cloud_rgb
+        assert np.array_equal(rgb, expect), fr
+        assert np.array_equal(np.any(rgb != 0.5, axis=1), assigned | np.any(expect != 0.5, axis=1))
+        assert assigned.sum() > 50
+
+
+@pytest.mark.gpu
+def test_device_depth_overlay_matches_numpy(golden_arrays):
+    from conftest import load_frame, standin
+    from lidar_object_detection_b200 import colour as C, kitti360 as K, lidarfuse as LF
+    from oracle import pipeline as P
+    camera, TVC, TVR = K.calibration_chain(SAMPLE)
+    rng = np.random.default_rng(5)
+    pts = load_frame(100)
+    masks = standin(100, camera)[0]
+    maps = LF.per_car_depth_maps(pts, TVR, masks, camera, max_depth=30, policy='last')
+    image = rng.integers(0, 256, (camera.height, camera.width, 3), dtype=np.uint8)
+    n = 0
+    for car_id, dm in maps:
+        dm = np.asarray(dm)
+        if dm.max() == 0:
+            continue
+        got = C.depth_overlay(dm, image)
+        want = P.depth_overlay_reference(dm.copy(), image, P.jet_lut_restated())
+        assert got.dtype == np.uint8 and np.array_equal(got, want)
+        n += 1
+    assert n >= 3
+
+
+# ------------------------------------------------------------------ rank 4 (I/O formats)
+
+def test_csv_formatter_is_byte_identical(tmp_path):
+    """lf_format_csv_rows (plain C, host) against the committed reference CSV
+    (tests/golden/master_car_statistics_erosion3.csv, written by the unmodified
+    cvs_erosion.append_to_master_csv through pandas) and against the Python writer on
+    rounding edge cases (x.xx5 ties, 100.0, 0.0, one-decimal values)."""
+    import csv
+    from lidar_object_detection_b200 import io as IO, lidarfuse as LF
+    path = os.path.join(GOLDEN, 'master_car_statistics_erosion3.csv')
+    with open(path, 'rb') as fh:
+        want = fh.read()
+    with open(path, newline='') as fh:
+        recs = list(csv.DictReader(fh))
+    rows = [(int(r['frame']), int(r['car_id']), int(r['matched_bbox_id']), int(r['total_points']),
+             int(r['points_inside_bbox'])) for r in recs]
+    ts = recs[0]['timestamp']
+    assert all(r['timestamp'] == ts for r in recs)
+    assert IO.format_csv_rows(rows, ts, with_header=True) == want
+    # edge cases against the Python writer
+    rng = np.random.default_rng(3)
+    stats, rows = [], []
+    cases = [(8, 1), (8, 3), (8, 5), (8, 7), (1000, 125), (200, 1), (3, 1), (3, 2), (7, 7), (9, 0), (16, 1), (32, 1),
+             (64, 1), (400, 1), (800, 1), (1600, 1), (2000, 1)]
+    cases += [(int(t), int(rng.integers(0, t + 1))) for t in rng.integers(1, 5000, 3000)]
+    for i, (t, ins) in enumerate(cases):
+        bid = -1 if ins == 0 else i % 7
+        stats.append({'car_id': i, 'matched_bbox_id': bid, 'total_points': t, 'points_inside_bbox': ins,
+                      'points_outside_bbox': t - ins, 'inside_percentage': (ins / t) * 100,
+                      'outside_percentage': ((t - ins) / t) * 100})
+        rows.append((42, i, bid, t, ins))
+    p1, p2 = str(tmp_path / 'a.csv'), str(tmp_path / 'b.csv')
+    LF.append_to_master_csv(stats, 42, p1, timestamp='2025-01-01T00:00:00')
+    IO.append_rows_to_master_csv(rows, p2, timestamp='2025-01-01T00:00:00')
+    IO.append_rows_to_master_csv(rows[:5], p2, timestamp='t2')          # appended without a second header
+    LF.append_to_master_csv(stats[:5], 42, p1, timestamp='t2')
+    assert open(p1, 'rb').read() == open(p2, 'rb').read()
+
+
+def test_sweep_reader_and_mask_packer_host(tmp_path):
+    from conftest import load_frame
+    from lidar_object_detection_b200 import io as IO
+    paths = []
+    for fr in (100, 250):
+        p = str(tmp_path / ('%010d.bin' % fr))
+        load_frame(fr).astype(np.float32).tofile(p)
+        paths.append(p)
+    n = [IO.sweep_points(p) for p in paths]
+    buf = np.zeros((sum(n), 4), np.float32)
+    assert IO.read_sweeps_into(paths, buf) == n
+    assert np.array_equal(buf[:n[0]], load_frame(100)) and np.array_equal(buf[n[0]:], load_frame(250))
+    with pytest.raises(ValueError):
+        IO.read_sweeps_into(paths, np.zeros((10, 4), np.float32))
+    rng = np.random.default_rng(1)
+    m = rng.random((3, 5, 70)) < 0.4
+    w = IO.pack_masks_host(m)
+    assert w.shape == (3, 5, 3) and w.dtype == np.uint32
+    for x in (0, 31, 32, 69):
+        assert np.array_equal((w[:, :, x >> 5] >> np.uint32(x & 31)) & 1, m[:, :, x])
+    assert np.all(w[:, :, 2] >> np.uint32(6) == 0)                      # padding bits beyond W stay clear
+
+
+@pytest.mark.gpu
+def test_sweep_streamer_and_packed_mask_container(tmp_path):
+    import torch
+    from conftest import load_frame, standin
+    from lidar_object_detection_b200 import io as IO, kitti360 as K, lidarfuse as LF
+    camera, TVC, TVR = K.calibration_chain(SAMPLE)
+    frames = [100, 250, 360, 644, 729, 947, 1134]
+    paths = []
+    for fr in frames:
+        p = str(tmp_path / ('%010d.bin' % fr))
+        load_frame(fr).astype(np.float32).tofile(p)
+        paths.append(p)
+    seen = 0
+    st = IO.SweepStreamer(paths, frames_per_batch=2)
+    assert len(st) == 4
+    for pts, counts, ps in st:                            # 4 batches over 2 slots: both get reused
+        assert pts.is_cuda and pts.shape == (sum(counts), 4)
+        want = np.concatenate([load_frame(frames[seen + i]) for i in range(len(counts))])
+        u, v, d = LF.project_points(pts, TVR, camera)    # consumer work on the current stream
+        assert np.array_equal(pts.cpu().numpy(), want)
+        uw, vw, dw = LF.project_points(want, TVR, camera)
+        assert torch.equal(u.cpu(), torch.from_numpy(uw))
+        seen += len(counts)
+    assert seen == len(frames)
+    # packed mask container: device words -> .npz -> device words, usable by the gather
+    masks, _, conf = standin(100, camera)
+    pm = LF.erode_pack(masks, 3, 1)
+    f = str(tmp_path / 'masks_100.npz')
+    IO.save_packed_masks(f, pm.words, pm.H, pm.W, conf=conf, bbox=pm.bbox)
+    pm2, conf2 = IO.load_packed_masks(f)
+    assert torch.equal(pm.words, pm2.words) and torch.equal(pm.bbox, pm2.bbox) and np.array_equal(conf, conf2)
+    assert os.path.getsize(f) < masks.size // 8
+    assert np.array_equal(pm2.words.cpu().numpy().view(np.uint32), IO.pack_masks_host(pm.unpack().cpu().numpy()))
