@@ -1,0 +1,130 @@
+#!/usr/bin/env python
+"""Device timings of the SURVEY 8(f) 'next' rows (not the BASELINE metric: bench.py is).
+
+    python bench_next.py [--reps 20]
+
+One JSON line per kernel: launch time from CUDA events on the launching stream (after
+3 warm-ups, inputs larger than L2 or the buffer re-read cold where it matters), the
+algorithmic bytes of the launch and the resulting GB/s against MEASURED_PEAKS.json.
+Sizes are cfg3-shaped (1024 frames x 16 masks / boxes, 131072 points per frame).
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+CALIB_ROOT = os.path.join(ROOT, 'tests', 'golden', 'kitti360_sample')
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--reps', type=int, default=20)
+    args = ap.parse_args()
+    import numpy as np
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit('bench_next.py needs a CUDA device')
+    from lidar_object_detection_b200 import _abi, io as IO, kitti360 as K, lidarfuse as LF, synthetic as S
+    from lidar_object_detection_b200._abi import check, ptr
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_gbs'])
+    except Exception:
+        peak = 6650.0
+    cam, TVC, TVR = K.calibration_chain(CALIB_ROOT)
+    ctx = LF.get_ctx(0)
+    ctx.set_camera(TVR, cam.K, cam.width, cam.height)
+    dev, st = ctx.device, ctx.stream
+    H, W = cam.height, cam.width
+
+    def timed(fn, nbytes, name, note):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ms = []
+        for _ in range(args.reps):
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        ms.sort()
+        med = ms[len(ms) // 2]
+        gbs = nbytes / (med * 1e-3) / 1e9
+        print(json.dumps({'kernel': name, 'ms': med, 'ms_min': ms[0], 'algorithmic_bytes': int(nbytes),
+                          'achieved_gbs': gbs, 'peak_gbs': peak, 'frac': gbs / peak, 'note': note}))
+
+    # rank 1: resize 16384 half-resolution masks to camera resolution (bilinear), and 2x area
+    M = 1024 * 16
+    g = torch.Generator(device=dev).manual_seed(1)
+    for (h, w), label in (((192, 704), 'bilinear 192x704 -> 376x1408'), ((752, 2816), '2x2 average 752x2816 -> 376x1408')):
+        m = M if h < H else M // 8
+        src = (torch.rand((m, h, w), device=dev, generator=g) < 0.3).to(torch.uint8)
+        dst = torch.empty((m, H, W), dtype=torch.uint8, device=dev)
+        timed(lambda: check(ctx.lib.lf_resize_masks(ctx.h, ptr(src), m, h, w, ptr(dst), H, W, st), ctx.h),
+              m * (h * w + H * W), 'lf_resize_masks', '%d masks, %s' % (m, label))
+        del src, dst
+    # rank 2: project 1M boxes; IoU/score matrices for 65536 frames x 16 x 16
+    nb = 65536 * 16
+    cars = S.make_cars(4096, 16, 7)
+    cv = S.car_corners_velo(cars).reshape(-1, 3)
+    cam0 = (np.hstack([cv, np.ones((len(cv), 1))]) @ TVC.T)[:, :3].reshape(-1, 8, 3)
+    corners = torch.from_numpy(np.ascontiguousarray(np.tile(cam0, (16, 1, 1)))).to(dev)
+    rects = torch.zeros((nb, 72), dtype=torch.uint8, device=dev)
+    timed(lambda: check(ctx.lib.lf_project_boxes(ctx.h, ptr(corners), nb, 0.1, 100.0, 4, ptr(rects), None, None,
+                                                 None, st), ctx.h),
+          nb * (192 + 72), 'lf_project_boxes', '%d boxes (8 corners f64 in, 72-byte record out)' % nb)
+    F = 65536
+    dets = torch.rand((F * 16, 4), dtype=torch.float64, device=dev) * 300
+    dets[:, 2:] += dets[:, :2] + 20
+    off = torch.arange(0, F * 16 + 1, 16, dtype=torch.int32, device=dev)
+    ooff = torch.arange(0, F * 256 + 1, 256, dtype=torch.int64, device=dev)
+    iou = torch.empty(F * 256, dtype=torch.float64, device=dev)
+    score = torch.empty(F * 256, dtype=torch.float64, device=dev)
+    timed(lambda: check(ctx.lib.lf_match_matrices(ctx.h, ptr(dets), ptr(off), ptr(rects), ptr(off), ptr(ooff), 65535,
+                                                  256, 0.5, 0.3, 0.2, ptr(iou), ptr(score), st), ctx.h),
+          65535 * (16 * 32 + 16 * 72 + 2 * 256 * 8), 'lf_match_matrices', '65535 frames x 16 detections x 16 boxes')
+    del corners, rects, dets, iou, score
+    # rank 3: per-point colours for 64M points; depth overlay of 256 frames
+    n = 64 * 1024 * 1024
+    bits = torch.randint(0, 1 << 16, (n,), dtype=torch.int64, device=dev, generator=g)
+    bits[torch.rand(n, device=dev, generator=g) < 0.8] = 0
+    cols = torch.rand((16, 3), dtype=torch.float64, device=dev)
+    rgb = torch.empty((n, 3), dtype=torch.float64, device=dev)
+    bg = np.array([0.5, 0.5, 0.5])
+    timed(lambda: check(ctx.lib.lf_point_colors(ctx.h, ptr(bits), n, ptr(cols), 16, bg.ctypes.data, ptr(rgb), None, st),
+                        ctx.h), n * (8 + 24), 'lf_point_colors', '%d points, 16 masks, f64 RGB out' % n)
+    del bits, rgb
+    from lidar_object_detection_b200 import colour as C
+    lut = torch.from_numpy(C.jet_lut()).to(dev)
+    nf = 64
+    dm = torch.rand((nf, H, W), dtype=torch.float64, device=dev, generator=g) * 30
+    dm[torch.rand((nf, H, W), device=dev, generator=g) < 0.9] = 0
+    img = torch.randint(0, 256, (nf, H, W, 3), dtype=torch.uint8, device=dev, generator=g)
+    out = torch.empty_like(img)
+    mx = dm.reshape(nf, -1).amax(dim=1)
+
+    def overlay():
+        for i in range(nf):
+            check(ctx.lib.lf_depth_overlay(ctx.h, ptr(dm[i]), ptr(mx[i:]), ptr(img[i]), ptr(lut), 256, H, W,
+                                           ptr(out[i]), st), ctx.h)
+    timed(overlay, nf * H * W * (8 + 3 + 3), 'lf_depth_overlay', '%d launches of one %dx%d frame each' % (nf, W, H))
+    # rank 4: CSV rows on the host
+    nrows = 1_000_000
+    rng = np.random.default_rng(0)
+    total = rng.integers(1, 5000, nrows)
+    rows = np.stack([rng.integers(0, 65536, nrows), rng.integers(0, 16, nrows), rng.integers(-1, 16, nrows), total,
+                     (total * rng.random(nrows)).astype(np.int64)], axis=1)
+    t0 = time.perf_counter()
+    text = IO.format_csv_rows(rows, '2025-01-01T00:00:00', with_header=True)
+    dt = time.perf_counter() - t0
+    print(json.dumps({'kernel': 'lf_format_csv_rows (host, 1 thread)', 'ms': dt * 1e3, 'rows': nrows,
+                      'rows_per_s': nrows / dt, 'bytes': len(text)}))
+
+
+if __name__ == '__main__':
+    main()

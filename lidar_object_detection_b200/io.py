@@ -180,9 +180,12 @@ def pack_masks_host(masks):
 def format_csv_rows(rows, timestamp, with_header=False):
     """``rows``: iterable of (frame, car_id, matched_bbox_id, total, inside[, outside]) as
     ``distributed.rows_from_table`` returns them -> bytes of the CSV lines."""
-    rows = list(rows)
-    n = len(rows)
-    a = np.array([r[:5] for r in rows], dtype=np.int64).reshape(n, 5)
+    if isinstance(rows, np.ndarray):
+        a = np.ascontiguousarray(rows[:, :5], dtype=np.int64)
+    else:
+        rows = list(rows)
+        a = np.array([r[:5] for r in rows], dtype=np.int64).reshape(len(rows), 5)
+    n = len(a)
     frame = np.ascontiguousarray(a[:, 0])
     car = np.ascontiguousarray(a[:, 1].astype(np.int32))
     bid = np.ascontiguousarray(a[:, 2].astype(np.int32))

@@ -146,7 +146,7 @@ def test_device_box_projection_edge_cases(cam):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize('src', [(376, 1408), (384, 1408), (160, 608), (104, 384), (188, 704), (752, 2816),
-                                 (100, 333), (3, 5), (1, 1)])
+                                 (100, 333), (3, 5), (1, 1), (20, 5000)])
 def test_device_resize_is_bit_exact_with_cv2(src):
     """cv2.resize(u8, (W, H)) (default INTER_LINEAR) against lf_resize_masks: identity,
     the 2x2-average substitution at exactly 2x, fixed-point bilinear up and down;
