@@ -135,3 +135,18 @@ def test_csv_writer_bytes_without_pandas(golden, tmp_path):
         stats = [dict(s, points_inside_bbox=np.int64(s['points_inside_bbox'])) for s in g['stats_erosion3']]
         LF.append_to_master_csv(stats, fr, path, ts)
     assert open(path).read() == want
+
+
+def test_argument_checks_need_no_device(lib):
+    """Null contexts / bad sizes are rejected before any CUDA call (status codes, no abort)."""
+    from lidar_object_detection_b200 import _abi
+    assert lib.lf_process_batch(None, *([None] * 3), 0, 0, None, None, 3, 1, *([None] * 5), 1, 1, 1, 1, 50.0, 1, 10,
+                                *([None] * 9)) == _abi.LF_E_ARG
+    assert lib.lf_resize_masks(None, None, 1, 4, 4, None, 8, 8, None) == _abi.LF_E_ARG
+    assert lib.lf_project_boxes(None, None, 1, 0.1, 100.0, 4, None, None, None, None, None) == _abi.LF_E_ARG
+    assert lib.lf_point_colors(None, None, 1, None, 1, None, None, None, None) == _abi.LF_E_ARG
+    assert lib.lf_format_csv_rows(None, None, None, None, None, -1, b't', 0, None, 0) == _abi.LF_E_ARG
+    assert lib.lf_format_csv_rows(None, None, None, None, None, 0, b't', 1, None, 0) == \
+        len('frame,car_id,matched_bbox_id,total_points,points_inside_bbox,points_outside_bbox,'
+            'inside_percentage,outside_percentage,is_matched,timestamp\n')
+    assert b'argument' in lib.lf_strerror(_abi.LF_E_ARG).lower() or lib.lf_strerror(_abi.LF_E_ARG)

@@ -489,3 +489,64 @@ def test_mask_bounding_boxes(LF):
                     assert bb[m].tolist() == [0, 0, 0, 0]
                 else:
                     assert bb[m].tolist() == [(1 << 20) - xs.min(), (1 << 20) - ys.min(), xs.max() + 1, ys.max() + 1]
+
+
+# ------------------------------------------------------------------ ragged / degenerate batches
+
+@pytest.mark.parametrize('persistent', [False, True])
+def test_degenerate_frames_in_one_batch(LF, calib, persistent):
+    """Frames without points, without masks, without boxes and with NaN / inf / behind-camera
+    points next to a real frame: per-frame results equal the single-frame results, empty
+    frames produce no rows, nothing reads out of bounds (both launch modes)."""
+    cam, TVC, TVR = calib
+    pts0, raw0 = load_frame(100), load_boxes(100)
+    masks0 = standin(100, cam)[0]
+    boxes0 = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(raw0, cam), TVC)
+    c0 = np.array([b['corners_velo'] for b in boxes0], dtype=np.float64).reshape(-1, 8, 3)
+    weird = np.array([[np.nan, 0, 0, 0], [np.inf, 1, 1, 0], [-np.inf, 2, 2, 0], [0, 0, 0, 0], [-10, 0, 0, 0],
+                      [1e30, 1e30, 1e30, 0], [5, 0.1, -0.5, 0]], dtype=np.float32)
+    pts = np.concatenate([pts0, weird, pts0[:50000]])
+    n_pts = [len(pts0), 0, len(weird), 50000, 0]
+    masks = np.concatenate([masks0, masks0[:2], masks0[:3]])
+    n_masks = [len(masks0), 2, 3, 0, 0]
+    corners = np.concatenate([c0, c0[:4], c0])
+    n_boxes = [len(c0), 4, 0, len(c0), 0]
+    batch = LF.FrameBatch(pts, n_pts, masks, n_masks, corners, n_boxes, cam, TVR)
+    batch.run(3, 1, 50, 10, True, persistent=persistent)
+    res = batch.results()
+    want = P.process_frame(pts0, raw0, masks0, cam, TVC, TVR)
+    M0 = len(masks0)
+    assert res['n_valid'][0] == want['valid'].sum() and res['n_valid'][1] == 0 and res['n_valid'][4] == 0
+    assert np.array_equal(res['total'][:M0], want['total'])
+    assert np.array_equal(res['inside'][:batch.h_cnt_off[1]].reshape(want['inside'].shape), want['inside'])
+    assert not res['total'][M0:M0 + 2].any()                       # frame 1: masks but no points
+    wv = P.process_frame(weird, [], masks0[:3], cam, TVC, TVR)['valid']
+    assert res['n_valid'][2] == wv.sum() == 1                      # only the last weird point is in view
+    assert res['n_valid'][3] == P.process_frame(pts0[:50000], raw0, masks0[:0], cam, TVC, TVR)['valid'].sum()
+    assert _norm_stats(batch.frame_stats(res, 0)) == _norm_stats(want['stats'])
+    for f in (1, 2, 3, 4):
+        assert batch.frame_stats(res, f) == [] or all(s['total_points'] == 0 for s in batch.frame_stats(res, f))
+    # empty batch and oversize frames
+    e = LF.FrameBatch(np.zeros((0, 4), np.float32), [], np.zeros((0, cam.height, cam.width), np.uint8), [],
+                      np.zeros((0, 8, 3)), [], cam, TVR)
+    e.run(persistent=persistent)
+    assert e.results()['total'].size == 0
+    big = LF.FrameBatch(pts0[:1000], [1000], np.zeros((65, cam.height, cam.width), np.uint8), [65], c0[:1], [1], cam,
+                        TVR)
+    with pytest.raises(ValueError):
+        big.run(persistent=persistent)
+
+
+def test_argument_errors_surface_as_python_exceptions(LF, calib):
+    cam, TVC, TVR = calib
+    m = np.zeros((1, cam.height, cam.width), np.uint8)
+    with pytest.raises(ValueError):
+        LF.erode_pack(m, se=np.ones((4, 4), np.uint8), erosion_kernel_size=4)      # even element
+    with pytest.raises(ValueError):
+        LF.erode_pack(m, se=np.zeros((3, 3), np.uint8))                            # empty element
+    with pytest.raises(ValueError):
+        LF.erode_pack(m.astype(np.int32))                                          # unsupported dtype
+    with pytest.raises(ValueError):
+        LF.project_points(np.zeros((5, 2), np.float32), TVR, cam)
+    with pytest.raises(ValueError):
+        LF.FrameBatch(np.zeros((5, 4), np.float32), [4], m, [1], np.zeros((0, 8, 3)), [0], cam, TVR)
