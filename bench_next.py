@@ -68,6 +68,16 @@ def main():
         timed(lambda: check(ctx.lib.lf_resize_masks(ctx.h, ptr(src), m, h, w, ptr(dst), H, W, st), ctx.h),
               m * (h * w + H * W), 'lf_resize_masks', '%d masks, %s' % (m, label))
         del src, dst
+    # the reference's own mask format: float32 0.0 / 1.0 masks through lf_erode_pack (bulk-copy fast path)
+    mf = 2048
+    f32 = torch.zeros((mf, H, W), dtype=torch.float32, device=dev)
+    f32[:, 100:250, 300:900] = 1.0
+    pk = torch.empty((mf, H, (W + 31) // 32), dtype=torch.int32, device=dev)
+    bb = torch.zeros((mf, 4), dtype=torch.int32, device=dev)
+    se = LF.structuring_element(LF.MORPH_ELLIPSE, 3)
+    timed(lambda: check(ctx.lib.lf_erode_pack(ctx.h, ptr(f32), 1, mf, H, W, se.ctypes.data, 3, 1, ptr(pk), ptr(bb), st),
+                        ctx.h), mf * H * W * 4, 'lf_erode_pack (float32 masks)', '%d masks 1408x376 float32, 3x3 ellipse' % mf)
+    del f32, pk
     # rank 2: project 1M boxes; IoU/score matrices for 65536 frames x 16 x 16
     nb = 65536 * 16
     cars = S.make_cars(4096, 16, 7)

@@ -191,7 +191,7 @@ extern "C" int lf_process_batch(lf_ctx* ctx, const float* pts, const int64_t* pt
         rc = lf_erode_plan(ctx, masks, mask_mode, n_masks, H, W, se, k, iterations, ER_MAX_ROWS_BATCH, ER_STAGES_BATCH, &P,
                            &spec, &fast, &er_smem);
         if (rc != LF_OK) return rc;
-        fused = fast && spec >= 0;
+        fused = fast && spec >= 0 && mask_mode == 0;     // the persistent kernel takes uint8 masks
     }
     const int64_t chunks = (max_points_per_frame + FUSE_SEG - 1) / FUSE_SEG;
     if (fused && ((int64_t)F + 2048) * (chunks + LF_MAX_CARS) >= 0x7FFF0000LL) fused = false;

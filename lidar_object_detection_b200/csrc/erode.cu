@@ -211,7 +211,7 @@ lf_erode_bulk_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
                     bbox ? bbox + 4 * mask : nullptr);
 }
 
-template <class SE>
+template <class SE, int MODE>
 __global__ void __launch_bounds__(ER_THREADS)
 lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __restrict__ masks,
                      uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
@@ -223,17 +223,25 @@ lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
     }
     __syncthreads();
     uint32_t cbase = 0;
-    erode_fast_item<SE, ER_STAGES>(P, masks, packed, bbox, blockIdx.x, smem, full_bar, cbase);
+    erode_fast_item<SE, ER_STAGES, MODE>(P, masks, packed, bbox, blockIdx.x, smem, full_bar, cbase);
+}
+
+template <class SE, int MODE>
+cudaError_t launch_fast_mode(const ErodeParams& P, const uint8_t* masks, uint32_t* packed, int32_t* bbox,
+                             unsigned grid, size_t smem, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(lf_erode_fast_kernel<SE, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) return e;
+    lf_erode_fast_kernel<SE, MODE><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
+    return cudaGetLastError();
 }
 
 template <class SE>
-cudaError_t launch_fast(const ErodeParams& P, const uint8_t* masks, uint32_t* packed, int32_t* bbox, unsigned grid,
-                        size_t smem, cudaStream_t s) {
-    cudaError_t e = cudaFuncSetAttribute(lf_erode_fast_kernel<SE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
-    if (e != cudaSuccess) return e;
-    lf_erode_fast_kernel<SE><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
-    return cudaGetLastError();
+cudaError_t launch_fast(const ErodeParams& P, int mode, const uint8_t* masks, uint32_t* packed, int32_t* bbox,
+                        unsigned grid, size_t smem, cudaStream_t s) {
+    if (mode == 0) return launch_fast_mode<SE, 0>(P, masks, packed, bbox, grid, smem, s);
+    if (mode == 1) return launch_fast_mode<SE, 1>(P, masks, packed, bbox, grid, smem, s);
+    return launch_fast_mode<SE, 2>(P, masks, packed, bbox, grid, smem, s);
 }
 
 // ---------------------------------------------------------------------------
@@ -341,7 +349,8 @@ int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int
     if ((int64_t)buf_rows * P.wpr >= 65536) return LF_E_UNSUPPORTED;
     if (m * P.strips > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
 
-    const bool fastp = mode == 0 && (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
+    // bulk-copy fast path: whole words per row, 16-byte aligned rows (uint8 or float32 pixels)
+    const bool fastp = (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
     // compile-time element available?  (guarded smem layout: stride wpr+1, K/2 guard rows each side)
     int spec = -1;
     if (fastp) {
@@ -382,20 +391,20 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
         const uint8_t* mk = (const uint8_t*)masks;
         cudaError_t e;
         switch (spec) {
-            case 0: e = launch_fast<SeNone>(P, mk, packed, bbox, grid, smem, s); break;
-            case 1: e = launch_fast<SeCross3>(P, mk, packed, bbox, grid, smem, s); break;
-            case 2: e = launch_fast<SeRect3>(P, mk, packed, bbox, grid, smem, s); break;
-            case 3: e = launch_fast<SeEllipse5>(P, mk, packed, bbox, grid, smem, s); break;
-            case 4: e = launch_fast<SeRect5>(P, mk, packed, bbox, grid, smem, s); break;
-            case 5: e = launch_fast<SeCross5>(P, mk, packed, bbox, grid, smem, s); break;
-            case 6: e = launch_fast<SeEllipse7>(P, mk, packed, bbox, grid, smem, s); break;
-            case 7: e = launch_fast<SeRect7>(P, mk, packed, bbox, grid, smem, s); break;
-            default: e = launch_fast<SeCross7>(P, mk, packed, bbox, grid, smem, s); break;
+            case 0: e = launch_fast<SeNone>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 1: e = launch_fast<SeCross3>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 2: e = launch_fast<SeRect3>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 3: e = launch_fast<SeEllipse5>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 4: e = launch_fast<SeRect5>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 5: e = launch_fast<SeCross5>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 6: e = launch_fast<SeEllipse7>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            case 7: e = launch_fast<SeRect7>(P, mode, mk, packed, bbox, grid, smem, s); break;
+            default: e = launch_fast<SeCross7>(P, mode, mk, packed, bbox, grid, smem, s); break;
         }
         LF_CUDA(ctx, e);
         return LF_OK;
     }
-    if (fast) {
+    if (fast && mode == 0) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)smem));
         lf_erode_bulk_kernel<<<grid, ER_THREADS, smem, s>>>(P, (const uint8_t*)masks, packed, bbox);

@@ -121,7 +121,25 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // barrier 1, so further warps of the CTA are free to do something else.
 __device__ __forceinline__ void er_sync() { asm volatile("bar.sync 1, %0;" ::"n"(ER_THREADS) : "memory"); }
 
-template <class SE, int NST>
+// 8 floats -> 8 bits (bit j = pixel j set): MODE 1 = value >= 1.0 (what the reference's uint8
+// truncations of its 0.0 / 1.0 masks leave, cvs_erosion.py:101, V2:197), MODE 2 = value > 0.5
+// (seg_with_pointcloud.py:167).  NaN compares false in both.  Eight +0.0 cost three instructions.
+template <int MODE>
+__device__ __forceinline__ uint32_t pack8f(const uint4 a, const uint4 b) {
+    if (((a.x | a.y | a.z) | (a.w | b.x | b.y) | (b.z | b.w)) == 0u) return 0u;
+    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    uint32_t r = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float f = __uint_as_float(w[j]);
+        const bool set = MODE == 1 ? (f >= 1.0f) : (f > 0.5f);
+        r |= (set ? 1u : 0u) << j;
+    }
+    return r;
+}
+
+// MODE 0: uint8 masks (non-zero = set), 1 byte per pixel; MODE 1 / 2: float32 masks, 4 bytes per pixel.
+template <class SE, int NST, int MODE = 0>
 __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint8_t* __restrict__ masks,
                                                 uint32_t* __restrict__ packed, int32_t* __restrict__ bbox,
                                                 int64_t item, uint8_t* smem, uint64_t* full_bar, uint32_t& cbase) {
@@ -134,9 +152,10 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
     const int strip = (int)(item - mask * P.strips);
     int r0, r1, ga, gb;
     strip_rows(P, strip, r0, r1, ga, gb);
-    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W;
+    constexpr int EB = MODE == 0 ? 1 : 4;                  // bytes per pixel
+    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W * EB;
     const int nrows = gb - ga;
-    const int L = nrows * P.W;
+    const int L = nrows * P.W * EB;                        // bytes in the run
     const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
     const int S = P.wpr + 1;                               // row stride in words
     const int tid = threadIdx.x;
@@ -189,9 +208,20 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
                 }
             }
         }
-        // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
-        if (p0) bufA[w0 + (int)__umulhi((unsigned)w0, P.wpr_magic) + data0] = pack32(a0, a1);
-        if (p1) bufA[w1 + (int)__umulhi((unsigned)w1, P.wpr_magic) + data0] = pack32(b0, b1);
+        if (MODE == 0) {
+            // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
+            if (p0) bufA[w0 + (int)__umulhi((unsigned)w0, P.wpr_magic) + data0] = pack32(a0, a1);
+            if (p1) bufA[w1 + (int)__umulhi((unsigned)w1, P.wpr_magic) + data0] = pack32(b0, b1);
+        } else {
+            // float32: the thread's 32 bytes are 8 pixels = one byte of a packed word (w0 / w1 count
+            // 8-pixel groups here); little-endian bytes are in bit order, so a byte store does it
+            uint8_t* bytesA = (uint8_t*)bufA;
+            const int q0 = w0 >> 2, q1 = w1 >> 2;
+            if (p0) bytesA[4 * (q0 + (int)__umulhi((unsigned)q0, P.wpr_magic) + data0) + (w0 & 3)] =
+                (uint8_t)pack8f<MODE>(a0, a1);
+            if (p1) bytesA[4 * (q1 + (int)__umulhi((unsigned)q1, P.wpr_magic) + data0) + (w1 & 3)] =
+                (uint8_t)pack8f<MODE>(b0, b1);
+        }
     }
 
     uint32_t* cur = bufA;

@@ -120,6 +120,17 @@ def test_erosion_matches_cv2(LF, W, H):
     got = LF.erode_masks(f, 3, 1)
     assert got.dtype == np.float32
     assert np.array_equal(got != 0, ref.astype(np.uint8) != 0)     # what the gather sees (cvs_erosion.py:153-154)
+    # float32 masks through every compiled-in element (bulk-copy path when W % 32 == 0), special values
+    f[0, 0, :8] = [np.nan, -0.0, 2.0, np.inf, -np.inf, 1.0, 0.5, 0.50001]
+    for mode, binar in (('ge_one', lambda a: a >= 1.0), ('gt_half', lambda a: a > 0.5)):
+        with np.errstate(invalid='ignore'):
+            b = binar(f).astype(np.uint8)
+        for shape, cvshape in [(LF.MORPH_ELLIPSE, cv2.MORPH_ELLIPSE), (LF.MORPH_RECT, cv2.MORPH_RECT)]:
+            for k, it in ((3, 1), (5, 2), (7, 1)):
+                se = cv2.getStructuringElement(cvshape, (k, k))
+                want = np.stack([cv2.erode(m * 255, se, iterations=it) == 255 for m in b])
+                got = LF.erode_pack(f, k, it, shape, float_threshold=mode).unpack().cpu().numpy().astype(bool)
+                assert np.array_equal(got, want), (W, H, mode, shape, k, it)
     assert len(LF.erode_pack(np.zeros((0, H, W), np.uint8))) == 0
 
 
