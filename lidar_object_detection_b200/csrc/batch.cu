@@ -70,7 +70,7 @@ __device__ __forceinline__ void claim(const BatchSched& S, const FuseArgs& A, Wo
         const int g = q - S.lag, seg = r - S.slots_m;
         if (g < 0) continue;
         const int64_t p0 = A.pt_off[g], p1 = A.pt_off[g + 1];
-        if (p0 + (int64_t)seg * FUSE_SEG >= p1) continue;
+        if (p0 + (int64_t)seg * A.seg_points >= p1) continue;
         const int need = A.mask_off[g + 1] - A.mask_off[g];
         w->a = g; w->b = seg;
         w->need = ld_acquire_gpu(S.done + g) >= need ? 0 : need;
@@ -222,6 +222,7 @@ extern "C" int lf_process_batch(lf_ctx* ctx, const float* pts, const int64_t* pt
         A.max_depth = max_depth; A.use_oriented = use_oriented;
         A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
         A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
+        A.seg_points = FUSE_SEG;
         const size_t fu_smem = (size_t)FUSE_STAGES * FUSE_SUB * sizeof(float4) + (size_t)A.smem_boxes * sizeof(lf_box) +
                                4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4) + 16 * (size_t)A.smem_cars;
         const size_t smem = fu_smem > er_smem ? fu_smem : er_smem;

@@ -113,7 +113,11 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
     LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    const int64_t chunks = (max_points_per_frame + FUSE_SEG - 1) / FUSE_SEG;
+    // small batches: shorter segments, so that one frame still spreads over the machine
+    int seg = FUSE_SEG;
+    while (seg > FUSE_SUB && (int64_t)F * ((max_points_per_frame + seg - 1) / seg) < (int64_t)4 * ctx->sm_count) seg >>= 1;
+    A.seg_points = seg;
+    const int64_t chunks = (max_points_per_frame + seg - 1) / seg;
     if (chunks > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
     dim3 grid((unsigned)chunks, (unsigned)F);
     lf_fuse_kernel<<<grid, FUSE_THREADS, smem, (cudaStream_t)stream>>>(ctx->cam, A);

@@ -34,6 +34,7 @@ struct FuseArgs {
     int use_oriented;
     int smem_boxes;      // boxes staged in shared memory (max over frames)
     int smem_cars;       // max masks per frame (<= LF_MAX_CARS)
+    int seg_points;      // points per work item: a multiple of FUSE_SUB, FUSE_SEG for large batches
 };
 
 __device__ __forceinline__ unsigned long long warp_or64(unsigned long long v) {
@@ -244,12 +245,12 @@ template <int NT, class Hook>
 __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, int f, int seg, uint8_t* smem,
                                           uint64_t* full_bar, int* stage_cnt, uint32_t& fbase, Hook hook) {
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
-    const int64_t seg0 = p0 + (int64_t)seg * FUSE_SEG;
+    const int64_t seg0 = p0 + (int64_t)seg * A.seg_points;
     if (seg0 >= p1) {
         if (threadIdx.x == 32 * FUSE_CONSUMERS) hook();
         return;
     }
-    const int npts = (int)min((int64_t)FUSE_SEG, p1 - seg0);
+    const int npts = (int)min((int64_t)A.seg_points, p1 - seg0);
     const int nsub = (npts + FUSE_SUB - 1) / FUSE_SUB;
     const int ngroups = (npts + 31) / 32;
     const int m0 = A.mask_off[f];

@@ -653,6 +653,21 @@ class FrameBatch:
         mark('car_stats')
         self.launches_per_run = launches
 
+    def capture(self, *args, **kwargs):
+        """Record one ``run(*args, **kwargs)`` into a CUDA graph and return it (``g.replay()``
+        re-executes memset + kernels with one launch).  Every ABI call enqueues on the
+        caller's stream without allocating or synchronising, so the whole step is capturable;
+        worth it for small batches (cfg1: one frame), where launch latency is the step."""
+        kwargs.pop('mark', None)
+        if getattr(self, '_native', None) is not None:
+            raise ValueError('low-resolution masks take temporaries in run(): not capturable')
+        self.run(*args, **kwargs)                      # warm-up: function attributes, lazy module load
+        torch.cuda.synchronize(self.ctx.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.run(*args, **kwargs)
+        return g
+
     def results(self):
         """Host copies: dict of numpy arrays (one D2H of the counter block)."""
         c = self.counters.cpu().numpy()

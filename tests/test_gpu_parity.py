@@ -561,3 +561,27 @@ def test_argument_errors_surface_as_python_exceptions(LF, calib):
         LF.project_points(np.zeros((5, 2), np.float32), TVR, cam)
     with pytest.raises(ValueError):
         LF.FrameBatch(np.zeros((5, 4), np.float32), [4], m, [1], np.zeros((0, 8, 3)), [0], cam, TVR)
+
+
+def test_cuda_graph_replay_of_the_whole_step(LF, calib):
+    """FrameBatch.capture: memset + erode + fuse + decision recorded once, replayed with one
+    launch; results identical with direct launches (cfg1-sized batch, short segments)."""
+    import torch
+    cam, TVC, TVR = calib
+    pts, raw = load_frame(100), load_boxes(100)
+    masks = (standin(100, cam)[0] != 0).astype(np.uint8)
+    boxes = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(raw, cam), TVC)
+    c = np.array([b['corners_velo'] for b in boxes], dtype=np.float64).reshape(-1, 8, 3)
+    b = LF.FrameBatch(pts, [len(pts)], masks, [len(masks)], c, [len(c)], cam, TVR)
+    b.run(3, 1, 50, 10, True)
+    ref = b.results()
+    g = b.capture(3, 1, 50, 10, True)
+    b.counters.fill_(-7)                                   # the graph must re-zero everything itself
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    got = b.results()
+    for k in ref:
+        assert np.array_equal(ref[k], got[k]), k
+    want = P.process_frame(pts, raw, masks.astype(np.float32), cam, TVC, TVR)
+    assert np.array_equal(got['total'], want['total'])
