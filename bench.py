@@ -280,10 +280,9 @@ def run_gpu(args):
         torch.cuda.synchronize(dev)
 
         def e2e_step():
-            batch.points.copy_(h_pts, non_blocking=True)
-            batch.masks.copy_(h_masks, non_blocking=True)
+            batch.upload(h_pts, h_masks)
             step()
-            h_out.copy_(batch.counters, non_blocking=True)
+            batch.download(h_out)
             stream.synchronize()
 
         e2e_step()
@@ -301,8 +300,73 @@ def run_gpu(args):
         e2e = {'value': world * frames * n_pts / dt, 'unit': 'points/s',
                'h2d_bytes_per_step': int(h_pts.numel() * 4 + h_masks.numel()),
                'd2h_bytes_per_step': int(h_out.numel() * 4), 'steps': n_e2e, 'ms_per_step': dt * 1e3,
-               'api': 'lidarfuse.FrameBatch.run (pinned host points + uint8 masks -> counters on host)'}
+               'api': 'FrameBatch.upload (pinned host points + uint8 masks as they are) / run / download (counters)'}
         t_end = time.time()
+
+    # ---- secondary accounting (SURVEY 8(d) "packed-masks-in"): the masks cross PCIe and enter HBM at one
+    # bit per pixel (lf_pack_masks_host on the sending side), erosion runs on the device from the words
+    packed_in = None
+    if world == 1 and not args.no_packed and not args.persistent:
+        from lidar_object_detection_b200 import io as IO, lidarfuse as LF
+        words = LF.erode_pack(batch.masks, 0, 0, device=local).words
+        pb = LF.FrameBatch(batch.points, [n_pts] * frames, LF.PackedMasks(words, H_IMG, W_IMG, raw=True), [NCARS] * frames,
+                           batch.boxes, sb.n_boxes, cam, TVR, device=local)
+        for _ in range(3):
+            pb.run(KSIZE, 1, 50, 10, True)
+        torch.cuda.synchronize(dev)
+        same = all(torch.equal(a, b) for a, b in ((pb.total, batch.total), (pb.inside, batch.inside),
+                                                  (pb.best_idx, batch.best_idx), (pb.packed.words, batch.packed.words)))
+        if not same:
+            raise SystemExit('PARITY FAILURE: packed-masks-in step differs from the uint8 step')
+        pm = []
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record(stream)
+        for _ in range(K_steps):
+            lst = []
+            pb.run(KSIZE, 1, 50, 10, True, mark=make_mark(lst))
+            pm.append(dict(lst))
+        p1.record(stream)
+        torch.cuda.synchronize(dev)
+        pms = p0.elapsed_time(p1) / K_steps
+        wpr = (W_IMG + 31) // 32
+        pbytes = sum(16 * n_pts + NCARS * H_IMG * wpr * 4 + 192 * b + 8 * NCARS * (b + 3) for b in sb.n_boxes)
+        er_ms = sum(d['zero'].elapsed_time(d['erode_pack']) for d in pm) / len(pm)
+        packed_in = {'value': frames * n_pts / (pms * 1e-3), 'unit': 'points/s', 'ms_per_step': pms,
+                     'kernel_ms': {'erode_pack': er_ms,
+                                   'fuse': sum(d['erode_pack'].elapsed_time(d['fuse']) for d in pm) / len(pm)},
+                     'algorithmic_bytes_per_step': pbytes, 'achieved_gbs': pbytes / (pms * 1e-3) / 1e9,
+                     'erode_gbs_in_plus_out': 2 * frames * NCARS * H_IMG * wpr * 4 / (er_ms * 1e-3) / 1e9,
+                     'note': 'lf_erode_pack mode 3 (masks arrive as uint32 words); results identical with the uint8 step'}
+        if e2e is not None:
+            hm = h_masks.numpy()
+            h_words = torch.empty(words.shape, dtype=words.dtype, pin_memory=True)
+            hw = h_words.numpy()
+            threads = os.cpu_count() or 1
+
+            def e2e_packed_step():
+                pb.upload(h_pts, h_masks, threads=threads)         # packs a slice while the previous one is on the wire
+                pb.run(KSIZE, 1, 50, 10, True)
+                pb.download(h_out)
+                stream.synchronize()
+
+            e2e_packed_step()
+            if not torch.equal(h_out, batch.counters.cpu()):
+                raise SystemExit('PARITY FAILURE: host-packed end-to-end step differs')
+            tp0 = time.perf_counter()
+            for _ in range(n_e2e):
+                e2e_packed_step()
+            dtp = (time.perf_counter() - tp0) / n_e2e
+            tq0 = time.perf_counter()
+            IO.pack_masks(hm, threads=threads, out=hw)
+            tq = time.perf_counter() - tq0
+            packed_in['e2e'] = {'value': frames * n_pts / dtp, 'unit': 'points/s', 'ms_per_step': dtp * 1e3,
+                                'h2d_bytes_per_step': int(h_pts.numel() * 4 + words.numel() * 4),
+                                'd2h_bytes_per_step': int(h_out.numel() * 4), 'host_pack_threads': threads,
+                                'host_pack_gbs_alone': hm.nbytes / tq / 1e9,
+                                'api': 'FrameBatch.upload on PackedMasks(raw=True): lf_pack_masks_host in 16 slices '
+                                       'overlapped with their H2D / run / download; pinned uint8 masks in, counters out'}
+        t_end = time.time()
+        del pb
 
     clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
     if rank == 0:
@@ -348,7 +412,7 @@ def run_gpu(args):
             'roofline': {'kernel': kname, 'bound': 'hbm', 'achieved': ach, 'peak': peak,
                          'unit': 'GB/s', 'frac': ach / peak, 'traffic': traffic, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': mask_bytes},
-            'e2e': e2e, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,
+            'e2e': e2e, 'packed_masks_in': packed_in, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,
         }
         print(json.dumps(line))
     if world > 1:
@@ -394,6 +458,7 @@ def main():
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
+    ap.add_argument('--no-packed', action='store_true', help='skip the packed-masks-in secondary measurement')
     ap.add_argument('--persistent', action='store_true',
                     help='one persistent erode+fuse kernel (lf_process_batch with scheduler words) instead of '
                          'the stand-alone erode / fuse launches')

@@ -77,7 +77,17 @@ def main():
     se = LF.structuring_element(LF.MORPH_ELLIPSE, 3)
     timed(lambda: check(ctx.lib.lf_erode_pack(ctx.h, ptr(f32), 1, mf, H, W, se.ctypes.data, 3, 1, ptr(pk), ptr(bb), st),
                         ctx.h), mf * H * W * 4, 'lf_erode_pack (float32 masks)', '%d masks 1408x376 float32, 3x3 ellipse' % mf)
-    del f32, pk
+    del f32
+    # masks that arrive bit-packed (lf_pack_masks_host on the sending side): erosion from the words
+    mp = 16384
+    raw = torch.zeros((mp, H, (W + 31) // 32), dtype=torch.int32, device=dev)
+    raw[:, 100:250, 10:28] = -1
+    pk = torch.empty_like(raw)
+    bb = torch.zeros((mp, 4), dtype=torch.int32, device=dev)
+    timed(lambda: check(ctx.lib.lf_erode_pack(ctx.h, ptr(raw), 3, mp, H, W, se.ctypes.data, 3, 1, ptr(pk), ptr(bb), st),
+                        ctx.h), 2 * raw.numel() * 4, 'lf_erode_pack (packed words in)',
+          '%d masks 1408x376 at 1 bit per pixel, 3x3 ellipse; bytes = words in + words out' % mp)
+    del raw, pk
     # rank 2: project 1M boxes; IoU/score matrices for 65536 frames x 16 x 16
     nb = 65536 * 16
     cars = S.make_cars(4096, 16, 7)

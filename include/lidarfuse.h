@@ -94,14 +94,27 @@ int lf_project(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, doubl
  * V2 no-erosion variant, V2:197-200).
  * mode: 0 = uint8 masks, non-zero = set; 1 = float32 masks, >= 1.0 = set (the
  * uint8 truncation of cvs_erosion.py:101 and V2:197); 2 = float32 masks,
- * > 0.5 = set (seg_with_pointcloud.py:167).
+ * > 0.5 = set (seg_with_pointcloud.py:167); 3 = masks that are bit-packed
+ * already (`masks` = uint32 [m][H][wpr] as `packed` below, e.g. written by
+ * lf_pack_masks_host on the sending side: 1/8 of the bytes over PCIe and from
+ * HBM); `masks` and `packed` must not be the same buffer then.
  * bbox (optional): per mask the bounding box of the set pixels of the result,
  * encoded {2^20 - x0, 2^20 - y0, x1 + 1, y1 + 1} (all zero = empty mask); it
  * lets lf_fuse_batch skip masks a group of points cannot touch. */
-int lf_erode_pack(lf_ctx* ctx, const void* masks /*DEVICE [m][H][W]*/, int mode, int64_t m,
+int lf_erode_pack(lf_ctx* ctx, const void* masks /*DEVICE [m][H][W], mode 3: [m][H][wpr] words*/, int mode, int64_t m,
                   int H, int W, const uint8_t* se /*HOST [k][k]*/, int k, int iterations,
                   uint32_t* packed /*DEVICE [m][H][wpr]*/,
                   int32_t* bbox /*DEVICE [m][4], zeroed by the caller, or NULL*/, void* stream);
+
+/* Host-side transfer encoding of instance masks (plain C++, no device work): binarise
+ * with the rule of `mode` (0, 1, 2 as lf_erode_pack) and pack to one bit per pixel,
+ * uint32 [m][H][wpr], LSB = lowest x, pad bits zero -- the layout lf_erode_pack (mode 3)
+ * and lf_fuse_batch read.  The reference hands masks over as full-resolution arrays
+ * (cvs_erosion.py:93 `masks.cpu().numpy()`); packed they are 1/8 (uint8) or 1/32
+ * (float32) of the bytes.  `threads` <= 0: one per hardware thread.  Erosion is NOT
+ * done here: it stays on the device. */
+int lf_pack_masks_host(const void* masks /*HOST [m][H][W]*/, int mode, int64_t m, int H, int W,
+                       uint32_t* packed /*HOST [m][H][wpr]*/, int threads);
 
 /* packed -> uint8 0/1 images (the eroded masks the reference keeps as float32,
  * cvs_erosion.py:103). */

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(HERE, '_lib', 'liblidarfuse.so')
 
 LF_OK, LF_E_ARG, LF_E_CUDA, LF_E_UNSUPPORTED, LF_E_NOCAMERA = 0, -1, -2, -3, -4
 POLICY_NEAREST, POLICY_LAST = 0, 1
-MODE_U8, MODE_F32_GE1, MODE_F32_GT_HALF = 0, 1, 2
+MODE_U8, MODE_F32_GE1, MODE_F32_GT_HALF, MODE_PACKED = 0, 1, 2, 3
 MAX_CARS = 64
 
 # numpy mirror of struct lf_box (192 bytes)
@@ -40,6 +40,7 @@ SIGNATURES = {
     'lf_project': (C.c_int, [_vp, _vp, _i64, _f64, _vp, _vp, _vp, _vp, _vp]),
     'lf_erode_pack': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp]),
     'lf_unpack_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
+    'lf_pack_masks_host': (C.c_int, [_vp, _i32, _i64, _i32, _i32, _vp, _i32]),
     'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
     'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp]),

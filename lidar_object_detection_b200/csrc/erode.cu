@@ -86,7 +86,7 @@ __device__ __forceinline__ void erode_pass_spans(const ErodeParams& P, const uin
     const int rad = k / 2;
     const uint32_t padmask = (P.W & 31) ? ~((1u << (P.W & 31)) - 1u) : 0u;
     for (int it = threadIdx.x; it < items; it += ER_THREADS) {
-        const int lr = (int)__umulhi((unsigned)it, P.wpr_magic);
+        const int lr = mdiv(it, P.wpr_magic);
         const int wx = it - lr * P.wpr;
         uint32_t acc = 0xFFFFFFFFu;
 #pragma unroll
@@ -133,7 +133,7 @@ __device__ __forceinline__ void erode_and_store(const ErodeParams& P, uint32_t* 
     BBoxAcc acc;
     for (int it = threadIdx.x; it < items; it += ER_THREADS) {
         uint32_t w = srcw[it];
-        const int lr = (int)__umulhi((unsigned)it, P.wpr_magic), wx = it - lr * P.wpr;
+        const int lr = mdiv(it, P.wpr_magic), wx = it - lr * P.wpr;
         if (wx == P.wpr - 1) w &= keep;
         dstw[it] = w;
         acc.add(w, r0 + lr, wx);
@@ -241,6 +241,7 @@ cudaError_t launch_fast(const ErodeParams& P, int mode, const uint8_t* masks, ui
                         unsigned grid, size_t smem, cudaStream_t s) {
     if (mode == 0) return launch_fast_mode<SE, 0>(P, masks, packed, bbox, grid, smem, s);
     if (mode == 1) return launch_fast_mode<SE, 1>(P, masks, packed, bbox, grid, smem, s);
+    if (mode == 3) return launch_fast_mode<SE, 3>(P, masks, packed, bbox, grid, smem, s);
     return launch_fast_mode<SE, 2>(P, masks, packed, bbox, grid, smem, s);
 }
 
@@ -251,6 +252,7 @@ cudaError_t launch_fast(const ErodeParams& P, int mode, const uint8_t* masks, ui
 template <int MODE> struct MaskElem { typedef uint8_t type; };
 template <> struct MaskElem<1> { typedef float type; };
 template <> struct MaskElem<2> { typedef float type; };
+template <> struct MaskElem<3> { typedef uint32_t type; };
 
 template <int MODE>
 __global__ void __launch_bounds__(ER_THREADS)
@@ -266,9 +268,23 @@ lf_erode_generic_kernel(const __grid_constant__ ErodeParams P, const void* __res
     const int strip = blockIdx.x - (int)(mask * P.strips);
     int r0, r1, ga, gb;
     strip_rows(P, strip, r0, r1, ga, gb);
+    const int items = (gb - ga) * P.wpr;
+    if (MODE == 3) {
+        // packed words in: copy the rows, bits beyond W read as ones (erosion border)
+        const uint32_t* srcw = (const uint32_t*)masks_v + (mask * P.H + ga) * (int64_t)P.wpr;
+        const uint32_t padmask = (P.W & 31) ? ~((1u << (P.W & 31)) - 1u) : 0u;
+        for (int it = threadIdx.x; it < items; it += ER_THREADS) {
+            const int lr = mdiv(it, P.wpr_magic);
+            uint32_t w = srcw[it];
+            if (it - lr * P.wpr == P.wpr - 1) w |= padmask;
+            bufA[it] = w;
+        }
+        erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr,
+                        bbox ? bbox + 4 * mask : nullptr);
+        return;
+    }
     const T* src = masks + (mask * P.H + ga) * (int64_t)P.W;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int items = (gb - ga) * P.wpr;
     for (int it = warp; it < items; it += ER_THREADS / 32) {
         const int lr = it / P.wpr, wx = it - lr * P.wpr;
         const int x = 32 * wx + lane;
@@ -349,8 +365,9 @@ int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int
     if ((int64_t)buf_rows * P.wpr >= 65536) return LF_E_UNSUPPORTED;
     if (m * P.strips > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
 
-    // bulk-copy fast path: whole words per row, 16-byte aligned rows (uint8 or float32 pixels)
-    const bool fastp = (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0;
+    // bulk-copy fast path: whole words per row, 16-byte aligned rows (uint8 or float32 pixels; packed
+    // words: every strip must start and end on a 16-byte boundary, i.e. whole quads per row)
+    const bool fastp = (W % 32) == 0 && (((uintptr_t)masks) & 15) == 0 && (mode != 3 || (P.wpr & 3) == 0);
     // compile-time element available?  (guarded smem layout: stride wpr+1, K/2 guard rows each side)
     int spec = -1;
     if (fastp) {
@@ -374,8 +391,9 @@ int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int
 extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
                              const uint8_t* se, int k, int iterations, uint32_t* packed, int32_t* bbox,
                              void* stream) {
-    if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 2) return LF_E_ARG;
+    if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 3) return LF_E_ARG;
     if (m > 0 && (!masks || !packed)) return LF_E_ARG;
+    if (mode == 3 && (const void*)masks == (const void*)packed) return LF_E_ARG;   // strips read their neighbours' rows
     if (iterations > 0 && (!se || k < 1 || (k & 1) == 0)) return LF_E_ARG;
     if (iterations > 0 && k > LF_MAX_SE) return LF_E_UNSUPPORTED;
     if (m == 0) return LF_OK;
@@ -412,6 +430,10 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<0>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         lf_erode_generic_kernel<0><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
+    } else if (mode == 3) {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<3>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lf_erode_generic_kernel<3><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
     } else if (mode == 1) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_generic_kernel<1>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -17,7 +17,7 @@ struct ErodeParams {
     int rows_per_strip, strips;
     int k, r, iterations, halo;
     int buf_words;                       // words per packed smem buffer
-    unsigned wpr_magic;                  // ceil(2^32 / wpr): it / wpr == __umulhi(it, magic) for it < 2^16
+    unsigned wpr_magic;                  // ceil(2^32 / wpr) mod 2^32: it / wpr == mdiv(it, magic) for it < 2^16
     int spans_ok;                        // every SE row is one contiguous run (RECT / CROSS / ELLIPSE are)
     unsigned short se_rows[LF_MAX_SE];   // bit j of se_rows[i] = SE[i][j]
     signed char span_a[LF_MAX_SE];       // row i covers dx in [-span_a[i], +span_b[i]]; span_a < 0: empty row
@@ -33,7 +33,10 @@ int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int
 
 namespace {
 
-
+// x / d for x < 2^16 with magic = ceil(2^32 / d) truncated to 32 bits; d == 1 wraps to 0 and means "x itself"
+__device__ __forceinline__ int mdiv(int x, unsigned magic) {
+    return magic ? (int)__umulhi((unsigned)x, magic) : x;
+}
 
 // Bounding box of the set pixels of the (eroded) mask, kept per thread while the
 // packed words go out and merged with four atomics per CTA.  Stored so that an
@@ -120,6 +123,14 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // Executed by the ER_THREADS threads with the lowest thread indices; they meet on named
 // barrier 1, so further warps of the CTA are free to do something else.
 __device__ __forceinline__ void er_sync() { asm volatile("bar.sync 1, %0;" ::"n"(ER_THREADS) : "memory"); }
+// the same barrier, returning the OR of `pred` over the ER_THREADS threads
+__device__ __forceinline__ bool er_sync_or(bool pred) {
+    uint32_t r;
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %1, 0;\n\tbar.red.or.pred p, 1, %2, q;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(r) : "r"((uint32_t)pred), "n"(ER_THREADS) : "memory");
+    return r != 0;
+}
 
 // 8 floats -> 8 bits (bit j = pixel j set): MODE 1 = value >= 1.0 (what the reference's uint8
 // truncations of its 0.0 / 1.0 masks leave, cvs_erosion.py:101, V2:197), MODE 2 = value > 0.5
@@ -138,7 +149,8 @@ __device__ __forceinline__ uint32_t pack8f(const uint4 a, const uint4 b) {
     return r;
 }
 
-// MODE 0: uint8 masks (non-zero = set), 1 byte per pixel; MODE 1 / 2: float32 masks, 4 bytes per pixel.
+// MODE 0: uint8 masks (non-zero = set), 1 byte per pixel; MODE 1 / 2: float32 masks, 4 bytes per pixel;
+// MODE 3: masks that arrive bit-packed already (uint32 [M][H][wpr], LSB = lowest x), 1/8 byte per pixel.
 template <class SE, int NST, int MODE = 0>
 __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint8_t* __restrict__ masks,
                                                 uint32_t* __restrict__ packed, int32_t* __restrict__ bbox,
@@ -152,10 +164,10 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
     const int strip = (int)(item - mask * P.strips);
     int r0, r1, ga, gb;
     strip_rows(P, strip, r0, r1, ga, gb);
-    constexpr int EB = MODE == 0 ? 1 : 4;                  // bytes per pixel
-    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)P.W * EB;
+    const int row_bytes = MODE == 0 ? P.W : (MODE == 3 ? 4 * P.wpr : 4 * P.W);
+    const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)row_bytes;
     const int nrows = gb - ga;
-    const int L = nrows * P.W * EB;                        // bytes in the run
+    const int L = nrows * row_bytes;                       // bytes in the run (a multiple of 16)
     const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
     const int S = P.wpr + 1;                               // row stride in words
     const int tid = threadIdx.x;
@@ -181,6 +193,7 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
         }
     }
     const int data0 = RAD * S + 1;                         // word index of (row 0, wx 0)
+    uint32_t nz = 0;                                       // OR of every word this thread produced
 
     for (int i = 0; i < nch; i += 2) {
         const uint32_t c0 = cbase + (uint32_t)i, c1 = c0 + 1u;
@@ -210,27 +223,58 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
         }
         if (MODE == 0) {
             // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
-            if (p0) bufA[w0 + (int)__umulhi((unsigned)w0, P.wpr_magic) + data0] = pack32(a0, a1);
-            if (p1) bufA[w1 + (int)__umulhi((unsigned)w1, P.wpr_magic) + data0] = pack32(b0, b1);
+            if (p0) { const uint32_t w = pack32(a0, a1); nz |= w; bufA[w0 + mdiv(w0, P.wpr_magic) + data0] = w; }
+            if (p1) { const uint32_t w = pack32(b0, b1); nz |= w; bufA[w1 + mdiv(w1, P.wpr_magic) + data0] = w; }
+        } else if (MODE == 3) {
+            // packed words in: the thread's 32 bytes are 8 words, moved to the guarded layout as they are
+            // (the run ends on a 16-byte boundary, so the last group may hold four words only)
+            const uint32_t va[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const uint32_t vb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            const int nw = L >> 2;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int x0 = 8 * w0 + j, x1 = 8 * w1 + j;
+                if (p0 && x0 < nw) { nz |= va[j]; bufA[x0 + mdiv(x0, P.wpr_magic) + data0] = va[j]; }
+                if (p1 && x1 < nw) { nz |= vb[j]; bufA[x1 + mdiv(x1, P.wpr_magic) + data0] = vb[j]; }
+            }
         } else {
             // float32: the thread's 32 bytes are 8 pixels = one byte of a packed word (w0 / w1 count
             // 8-pixel groups here); little-endian bytes are in bit order, so a byte store does it
             uint8_t* bytesA = (uint8_t*)bufA;
             const int q0 = w0 >> 2, q1 = w1 >> 2;
-            if (p0) bytesA[4 * (q0 + (int)__umulhi((unsigned)q0, P.wpr_magic) + data0) + (w0 & 3)] =
-                (uint8_t)pack8f<MODE>(a0, a1);
-            if (p1) bytesA[4 * (q1 + (int)__umulhi((unsigned)q1, P.wpr_magic) + data0) + (w1 & 3)] =
-                (uint8_t)pack8f<MODE>(b0, b1);
+            if (p0) {
+                const uint32_t w = pack8f<MODE>(a0, a1);
+                nz |= w;
+                bytesA[4 * (q0 + mdiv(q0, P.wpr_magic) + data0) + (w0 & 3)] = (uint8_t)w;
+            }
+            if (p1) {
+                const uint32_t w = pack8f<MODE>(b0, b1);
+                nz |= w;
+                bytesA[4 * (q1 + mdiv(q1, P.wpr_magic) + data0) + (w1 & 3)] = (uint8_t)w;
+            }
         }
     }
 
+    uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
+    const int out_items = (r1 - r0) * P.wpr;
+    cbase += (uint32_t)nch;
+    // Instance masks are mostly background: a window without a set pixel erodes to nothing, so the
+    // strip is written as zeros straight away (the barrier doubles as the one after the fill).
+    if (!er_sync_or(nz != 0u)) {
+        if ((P.wpr & 3) == 0) {
+            for (int q = tid; q < (out_items >> 2); q += ER_THREADS) *(uint4*)(dstw + 4 * q) = make_uint4(0u, 0u, 0u, 0u);
+        } else {
+            for (int it = tid; it < out_items; it += ER_THREADS) dstw[it] = 0u;
+        }
+        return;
+    }
     uint32_t* cur = bufA;
     uint32_t* nxt = bufB;
     const int items = nrows * P.wpr;
     for (int itn = 0; itn < P.iterations; ++itn) {
-        er_sync();
+        if (itn) er_sync();
         for (int it = tid; it < items; it += ER_THREADS) {
-            const int idx = it + (int)__umulhi((unsigned)it, P.wpr_magic) + data0;
+            const int idx = it + mdiv(it, P.wpr_magic) + data0;
             if (cur[idx] == 0u) {                          // the anchor is part of every element here
                 nxt[idx] = 0u;
                 continue;
@@ -253,9 +297,7 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
         }
         uint32_t* t = cur; cur = nxt; nxt = t;
     }
-    er_sync();
-    uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
-    const int out_items = (r1 - r0) * P.wpr;
+    if (P.iterations > 0) er_sync();
     const int skip = (r0 - ga) * S;
     BBoxAcc acc;
     if ((P.wpr & 3) == 0) {
@@ -264,7 +306,7 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
         const unsigned qmagic = (unsigned)((0x100000000ULL + qpr - 1) / qpr);
         const int nq = (r1 - r0) * qpr;
         for (int q = tid; q < nq; q += ER_THREADS) {
-            const int lr = (int)__umulhi((unsigned)q, qmagic);
+            const int lr = mdiv(q, qmagic);
             const int wq = q - lr * qpr;
             const uint32_t* sp = cur + lr * S + 4 * wq + data0 + skip;
             const uint4 v = make_uint4(sp[0], sp[1], sp[2], sp[3]);
@@ -276,14 +318,13 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
         }
     } else {
         for (int it = tid; it < out_items; it += ER_THREADS) {
-            const int lr = (int)__umulhi((unsigned)it, P.wpr_magic);
+            const int lr = mdiv(it, P.wpr_magic);
             const uint32_t w = cur[it + lr + data0 + skip];
             dstw[it] = w;
             acc.add(w, r0 + lr, it - lr * P.wpr);
         }
     }
     if (bbox) acc.flush(bbox + 4 * mask);
-    cbase += (uint32_t)nch;
 }
 
 typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)

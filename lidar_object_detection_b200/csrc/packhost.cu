@@ -1,0 +1,120 @@
+// lf_pack_masks_host: binarise + bit-pack instance masks on the SENDING side (plain C++,
+// no device work), so that masks cross PCIe and enter HBM at one bit per pixel.  This is
+// a transfer encoding, not a compute fallback: erosion, the gather and everything after
+// it run on the device from the packed words (lf_erode_pack mode 3).
+//
+// uint8 path: 8 bytes -> 8 bits with one 64-bit SWAR step (the same non-zero test as
+// pack32 in erode_body.cuh) and a multiply that gathers the eight byte MSBs; with AVX2
+// (checked at run time) 32 bytes -> 32 bits by compare + movemask.
+#include <stdint.h>
+#include <string.h>
+#include <thread>
+#include <vector>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
+#include "lidarfuse.h"
+
+namespace {
+
+inline uint32_t nz8(uint64_t w) {
+    // bit 7 of every byte = byte != 0, then gather the eight MSBs into one byte
+    const uint64_t t = (((w & 0x7f7f7f7f7f7f7f7fULL) + 0x7f7f7f7f7f7f7f7fULL) | w) & 0x8080808080808080ULL;
+    return (uint32_t)((t * 0x0002040810204081ULL) >> 56);
+}
+
+void pack_row_u8(const uint8_t* src, int W, uint32_t* dst) {
+    const int full = W >> 5;
+    for (int w = 0; w < full; ++w) {
+        uint64_t q[4];
+        memcpy(q, src + 32 * w, 32);
+        dst[w] = nz8(q[0]) | (nz8(q[1]) << 8) | (nz8(q[2]) << 16) | (nz8(q[3]) << 24);
+    }
+    if (W & 31) {
+        uint32_t acc = 0;
+        for (int x = 32 * full; x < W; ++x) acc |= (uint32_t)(src[x] != 0) << (x & 31);
+        dst[full] = acc;
+    }
+}
+
+#if defined(__x86_64__)
+__attribute__((target("avx2"))) void pack_row_u8_avx2(const uint8_t* src, int W, uint32_t* dst) {
+    const int full = W >> 5;
+    const __m256i z = _mm256_setzero_si256();
+    for (int w = 0; w < full; ++w) {
+        const __m256i v = _mm256_loadu_si256((const __m256i*)(src + 32 * w));
+        dst[w] = ~(uint32_t)_mm256_movemask_epi8(_mm256_cmpeq_epi8(v, z));
+    }
+    if (W & 31) {
+        uint32_t acc = 0;
+        for (int x = 32 * full; x < W; ++x) acc |= (uint32_t)(src[x] != 0) << (x & 31);
+        dst[full] = acc;
+    }
+}
+#endif
+
+template <int MODE>
+void pack_row_f32(const float* src, int W, uint32_t* dst) {
+    const int wpr = (W + 31) >> 5;
+    for (int w = 0; w < wpr; ++w) {
+        const int n = W - 32 * w < 32 ? W - 32 * w : 32;
+        uint32_t acc = 0;
+        for (int j = 0; j < n; ++j) {
+            const float f = src[32 * w + j];
+            acc |= (uint32_t)(MODE == 1 ? (f >= 1.0f) : (f > 0.5f)) << j;      // NaN: false in both
+        }
+        dst[w] = acc;
+    }
+}
+
+void pack_rows(const void* masks, int mode, int64_t row0, int64_t row1, int W, uint32_t* packed, bool avx2) {
+    const int wpr = (W + 31) >> 5;
+    for (int64_t r = row0; r < row1; ++r) {
+        uint32_t* dst = packed + r * wpr;
+        if (mode == 0) {
+            const uint8_t* src = (const uint8_t*)masks + r * W;
+#if defined(__x86_64__)
+            if (avx2) { pack_row_u8_avx2(src, W, dst); continue; }
+#endif
+            pack_row_u8(src, W, dst);
+        } else if (mode == 1) {
+            pack_row_f32<1>((const float*)masks + r * W, W, dst);
+        } else {
+            pack_row_f32<2>((const float*)masks + r * W, W, dst);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" int lf_pack_masks_host(const void* masks, int mode, int64_t m, int H, int W, uint32_t* packed,
+                                  int threads) {
+    if (m < 0 || H <= 0 || W <= 0 || mode < 0 || mode > 2) return LF_E_ARG;
+    if (m == 0) return LF_OK;
+    if (!masks || !packed) return LF_E_ARG;
+    bool avx2 = false;
+#if defined(__x86_64__)
+    avx2 = __builtin_cpu_supports("avx2");
+#endif
+    const int64_t rows = m * H;
+    int nt = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+    if (nt < 1) nt = 1;
+    if (nt > 256) nt = 256;
+    if ((int64_t)nt > rows / 64 + 1) nt = (int)(rows / 64 + 1);            // not worth a thread below 64 rows
+    if (nt == 1) {
+        pack_rows(masks, mode, 0, rows, W, packed, avx2);
+        return LF_OK;
+    }
+    std::vector<std::thread> pool;
+    try {
+        for (int t = 0; t < nt; ++t) {
+            const int64_t a = rows * t / nt, b = rows * (t + 1) / nt;
+            pool.emplace_back(pack_rows, masks, mode, a, b, W, packed, avx2);
+        }
+    } catch (...) {
+        for (auto& th : pool) th.join();
+        return LF_E_UNSUPPORTED;                                            // could not start the threads
+    }
+    for (auto& th : pool) th.join();
+    return LF_OK;
+}

@@ -4,6 +4,8 @@
   ``np.fromfile(float32).reshape(-1, 4)``) read by a background thread into pinned,
   double-buffered host memory and copied to the GPU on a side stream while the previous
   batch is being processed;
+* ``pack_masks``: host-side binarise + bit-pack (``lf_pack_masks_host``, multi-threaded C++) for
+  sending masks to the device at one bit per pixel;
 * ``save_packed_masks`` / ``load_packed_masks``: instance masks as bit-packed words
   (``uint32 [M, H, ceil(W/32)]``, LSB = lowest x: the layout ``lf_erode_pack`` writes and
   ``lf_fuse_batch`` reads) with their confidence order in one ``.npz``: 1/8 byte per pixel;
@@ -159,6 +161,35 @@ def load_packed_masks(path, device=None):
     words = torch.from_numpy(np.ascontiguousarray(w).view(np.int32)).to(ctx.device)
     tb = torch.from_numpy(np.ascontiguousarray(bbox)).to(ctx.device) if bbox is not None else None
     return LF.PackedMasks(words, H, W, tb), conf
+
+
+def pack_masks(masks, float_threshold='ge_one', threads=0, out=None):
+    """Binarise + bit-pack masks on the host with ``lf_pack_masks_host`` (multi-threaded C++; a
+    transfer encoding: 1/8 of the uint8 bytes, 1/32 of the float32 bytes cross PCIe).  masks:
+    numpy or CPU tensor [M,H,W], uint8 / bool (non-zero = set) or float32 (``>= 1.0``, or
+    ``> 0.5`` with ``float_threshold='gt_half'``).  ``out``: optional uint32/int32 [M,H,ceil(W/32)]
+    destination (e.g. ``pinned_tensor.numpy()``).  Returns the packed array; erosion is not done
+    here -- hand the words to ``lidarfuse.PackedMasks(..., raw=True)``."""
+    m = masks.numpy() if hasattr(masks, 'numpy') and not isinstance(masks, np.ndarray) else np.asarray(masks)
+    if m.ndim != 3:
+        raise ValueError('masks must be [M,H,W]')
+    if m.dtype == np.bool_:
+        m = m.view(np.uint8)
+    if m.dtype == np.uint8:
+        mode = _abi.MODE_U8
+    elif m.dtype == np.float32:
+        mode = _abi.MODE_F32_GT_HALF if float_threshold == 'gt_half' else _abi.MODE_F32_GE1
+    else:
+        raise ValueError('masks must be uint8, bool or float32, got %s' % m.dtype)
+    m = np.ascontiguousarray(m)
+    M, H, W = m.shape
+    shape = (M, H, (W + 31) // 32)
+    if out is None:
+        out = np.empty(shape, dtype=np.uint32)
+    elif tuple(out.shape) != shape or out.dtype.itemsize != 4 or not out.flags['C_CONTIGUOUS']:
+        raise ValueError('out must be a C-contiguous 32-bit array of shape %s' % (shape,))
+    _abi.check(_abi.load().lf_pack_masks_host(m.ctypes.data, mode, M, H, W, out.ctypes.data, int(threads)))
+    return out
 
 
 def pack_masks_host(masks):

@@ -153,11 +153,17 @@ def structuring_element(shape, ksize):
 
 
 class PackedMasks:
-    """Bit-packed instance masks on the device: uint32 [M, H, ceil(W/32)]."""
+    """Bit-packed instance masks on the device: uint32 [M, H, ceil(W/32)].
 
-    def __init__(self, words, H, W, bbox=None):
+    ``raw=True``: the words are binarised masks that have NOT been eroded yet (packed on the
+    sending side by ``io.pack_masks`` / ``lf_pack_masks_host``); ``FrameBatch.run`` and
+    ``erode_pack`` then erode them on the device from the packed words (mode 3).  Otherwise
+    they are taken as the final masks the point pass reads."""
+
+    def __init__(self, words, H, W, bbox=None, raw=False):
         self.words, self.H, self.W = words, H, W
         self.bbox = bbox        # int32 [M,4] {2^20-x0, 2^20-y0, x1+1, y1+1} (zeros = empty) or None
+        self.raw = bool(raw)
 
     def __len__(self):
         return self.words.shape[0]
@@ -191,13 +197,20 @@ def erode_pack(masks, erosion_kernel_size=3, erosion_iterations=1, shape=MORPH_E
     ctx = get_ctx(device)
     if isinstance(masks, (list, tuple)):
         masks = np.stack(masks) if len(masks) else np.zeros((0, 1, 1), np.uint8)
-    t = _dev(masks, ctx)
-    if t.ndim != 3:
-        raise ValueError('masks must be [M,H,W]')
-    mode = _mask_mode(t, float_threshold)
-    if t.dtype == torch.bool:
-        t = t.view(torch.uint8)
-    M, H, W = t.shape
+    if isinstance(masks, PackedMasks):
+        # packed on the sending side: erode from the words (1/8 of the uint8 traffic)
+        t, mode = masks.words.contiguous(), _abi.MODE_PACKED
+        M, H, W = len(masks), masks.H, masks.W
+        if tuple(t.shape) != (M, H, (W + 31) // 32) or t.dtype not in (torch.int32, torch.uint32):
+            raise ValueError('PackedMasks.words must be 32-bit [M, H, ceil(W/32)]')
+    else:
+        t = _dev(masks, ctx)
+        if t.ndim != 3:
+            raise ValueError('masks must be [M,H,W]')
+        mode = _mask_mode(t, float_threshold)
+        if t.dtype == torch.bool:
+            t = t.view(torch.uint8)
+        M, H, W = t.shape
     wpr = (W + 31) // 32
     words = torch.empty((M, H, wpr), dtype=torch.int32, device=ctx.device)
     iters = int(erosion_iterations) if erosion_kernel_size else 0
@@ -258,6 +271,8 @@ def resize_masks(masks, size, device=None):
 def _as_packed(masks, camera, ctx, float_threshold='ge_one'):
     if isinstance(masks, PackedMasks):
         pm = masks
+        if pm.raw:
+            pm = PackedMasks(pm.words, pm.H, pm.W)       # used as they are: no erosion asked for here
         if len(pm) and (pm.H != camera.height or pm.W != camera.width):
             masks = pm.unpack(ctx)                       # 0/1 bytes at the masks' own resolution
         else:
@@ -567,11 +582,17 @@ class FrameBatch:
         self.best_cnt = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
         self.car_bits = torch.empty(self.points.shape[0], dtype=torch.int64, device=ctx.device) \
             if want_car_bits else None
-        if isinstance(self.masks, PackedMasks):
+        self._native = None
+        if isinstance(self.masks, PackedMasks) and self.masks.raw:
+            H, W = camera.height, camera.width
+            if n_m and (self.masks.H, self.masks.W) != (H, W):
+                raise ValueError('raw packed masks must be at camera resolution')
+            self.packed = PackedMasks(torch.empty((n_m, H, (W + 31) // 32), dtype=torch.int32,
+                                                  device=ctx.device), H, W)
+        elif isinstance(self.masks, PackedMasks):
             self.packed = self.masks
         else:
             H, W = camera.height, camera.width
-            self._native = None
             if self.masks is not None and n_m and tuple(self.masks.shape[1:]) != (H, W):
                 # masks below camera resolution (YOLO without retina_masks): eroded where they
                 # are, THEN resized, as cvs_erosion.py:96-106 / :153 do -- see run()
@@ -599,7 +620,8 @@ class FrameBatch:
         mark('begin')
         check(lib.lf_zero_counters(ctx.h, ptr(self.counters), self.counters.numel() * 4, st), ctx.h)
         mark('zero')
-        raw = not isinstance(self.masks, PackedMasks) and self.masks is not None and len(self.masks) > 0
+        pre = isinstance(self.masks, PackedMasks)          # masks arrived bit-packed
+        raw = self.masks is not None and len(self.masks) > 0 and (not pre or self.masks.raw)
         iters, se, mode, mt = 0, None, 0, None
         if raw and getattr(self, '_native', None) is not None:
             # erode at the masks' own resolution, resize like cv2.resize, pack without erosion
@@ -612,9 +634,12 @@ class FrameBatch:
         if raw:
             iters = int(erosion_iterations) if erosion_kernel_size else 0
             se = structuring_element(shape, erosion_kernel_size) if iters else None
-            mode = _mask_mode(self.masks, float_threshold)
-            mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
-        bbox = self.packed.bbox if isinstance(self.masks, PackedMasks) else self.mask_bbox
+            if pre:
+                mode, mt = _abi.MODE_PACKED, self.masks.words
+            else:
+                mode = _mask_mode(self.masks, float_threshold)
+                mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
+        bbox = self.packed.bbox if pre and not self.masks.raw else self.mask_bbox
         if persistent and self.car_bits is None:
             split = timed and self.F and self.max_n        # time the persistent kernel apart from K6
             check(lib.lf_process_batch(
@@ -667,6 +692,61 @@ class FrameBatch:
         with torch.cuda.graph(g):
             self.run(*args, **kwargs)
         return g
+
+    def upload(self, points=None, masks=None, threads=0, slices=16, float_threshold='ge_one'):
+        """Refill the batch from HOST buffers of the shapes it was built with, asynchronously on
+        the current stream (pinned CPU tensors copy without staging).  A batch built on
+        ``PackedMasks(raw=True)`` takes uint8 / bool / float32 host masks [sum M,H,W] and sends
+        them at one bit per pixel: ``lf_pack_masks_host`` packs slice i+1 into pinned staging
+        while slice i is on the wire; erosion still runs on the device.  A batch built on
+        full-resolution device masks copies them as they are."""
+        if points is not None:
+            src = points if isinstance(points, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(points))
+            self.points.copy_(src.view(self.points.shape), non_blocking=True)
+        if masks is None:
+            return
+        if isinstance(self.masks, PackedMasks):
+            if not self.masks.raw:
+                raise ValueError('this batch holds final packed masks; build it on PackedMasks(raw=True) to refill')
+            from . import io as IO
+            m = masks.numpy() if isinstance(masks, torch.Tensor) else np.asarray(masks)
+            words = self.masks.words
+            if tuple(m.shape) != (len(self.masks), self.masks.H, self.masks.W):
+                raise ValueError('masks must be [%d, %d, %d]' % (len(self.masks), self.masks.H, self.masks.W))
+            if getattr(self, '_h_words', None) is None:
+                self._h_words = torch.empty(words.shape, dtype=words.dtype, pin_memory=True)
+                self._h_free = torch.cuda.Event()
+            else:
+                self._h_free.synchronize()              # the previous upload has left the staging buffer
+            hw = self._h_words.numpy()
+            n = len(m)
+            step = max(1, (n + slices - 1) // max(1, slices))
+            for a in range(0, n, step):
+                b = min(n, a + step)
+                IO.pack_masks(m[a:b], float_threshold=float_threshold, threads=threads, out=hw[a:b])
+                words[a:b].copy_(self._h_words[a:b], non_blocking=True)
+            self._h_free.record(torch.cuda.current_stream(self.ctx.device))
+        else:
+            if getattr(self, '_native', None) is not None:
+                raise ValueError('low-resolution masks: rebuild the batch instead')
+            src = masks if isinstance(masks, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(masks))
+            dst = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
+            if src.dtype == torch.bool:
+                src = src.view(torch.uint8)
+            if src.dtype != dst.dtype or tuple(src.shape) != tuple(dst.shape):
+                raise ValueError('masks must be %s %s' % (dst.dtype, tuple(dst.shape)))
+            dst.copy_(src, non_blocking=True)
+
+    def download(self, out=None):
+        """Counter block -> host, asynchronously on the current stream; ``out``: pinned int32 tensor
+        of ``self.counters.shape`` (allocated once when omitted).  Synchronise the stream before
+        reading it; ``results()`` is the blocking, decoded form."""
+        if out is None:
+            if getattr(self, '_h_out', None) is None:
+                self._h_out = torch.empty(self.counters.shape, dtype=self.counters.dtype, pin_memory=True)
+            out = self._h_out
+        out.copy_(self.counters, non_blocking=True)
+        return out
 
     def results(self):
         """Host copies: dict of numpy arrays (one D2H of the counter block)."""

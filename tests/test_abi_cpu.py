@@ -150,3 +150,27 @@ def test_argument_checks_need_no_device(lib):
         len('frame,car_id,matched_bbox_id,total_points,points_inside_bbox,points_outside_bbox,'
             'inside_percentage,outside_percentage,is_matched,timestamp\n')
     assert b'argument' in lib.lf_strerror(_abi.LF_E_ARG).lower() or lib.lf_strerror(_abi.LF_E_ARG)
+
+
+def test_host_mask_packer_matches_numpy():
+    """lf_pack_masks_host (plain C++, no device): every binarisation rule, ragged widths, threads."""
+    from lidar_object_detection_b200 import io as IO
+    rng = np.random.default_rng(5)
+    for W in (1408, 1000, 37, 64, 31):
+        m = (rng.random((7, 29, W)) < 0.3).astype(np.uint8) * rng.integers(1, 256, (7, 29, W), dtype=np.uint8)
+        want = IO.pack_masks_host(m)
+        for threads in (1, 3, 0):
+            assert np.array_equal(IO.pack_masks(m, threads=threads), want), (W, threads)
+        assert np.array_equal(IO.pack_masks(m.astype(bool)), want)
+        f = (rng.random((7, 29, W)) * 1.3).astype(np.float32)
+        f[0, 0, :6] = [np.nan, -0.0, 1.0, 0.5, np.inf, -np.inf]
+        with np.errstate(invalid='ignore'):
+            assert np.array_equal(IO.pack_masks(f), IO.pack_masks_host(f >= 1.0)), W
+            assert np.array_equal(IO.pack_masks(f, 'gt_half'), IO.pack_masks_host(f > 0.5)), W
+    out = np.full((7, 29, 1), 0xFFFFFFFF, np.uint32)
+    assert IO.pack_masks(m, out=out) is out and np.array_equal(out, want)      # pad bits come out zero
+    assert IO.pack_masks(np.zeros((0, 4, 4), np.uint8)).shape == (0, 4, 1)
+    with pytest.raises(ValueError):
+        IO.pack_masks(np.zeros((2, 4, 4), np.int16))
+    with pytest.raises(ValueError):
+        IO.pack_masks(m, out=np.zeros((7, 29, 2), np.uint32))

@@ -94,7 +94,7 @@ def test_projection_special_values(LF, calib, oracle_calib):
 
 # ------------------------------------------------------------------ A5
 
-@pytest.mark.parametrize('W,H', [(1408, 376), (1000, 123), (33, 17), (64, 8)])
+@pytest.mark.parametrize('W,H', [(1408, 376), (1000, 123), (33, 17), (64, 8), (128, 40), (32, 20), (16, 9)])
 def test_erosion_matches_cv2(LF, W, H):
     rng = np.random.default_rng(W * 1000 + H)
     masks = MP.random_blob_masks(rng, 5, H, W, n_blobs=4, max_r=max(4, min(H, W) // 3))
@@ -585,3 +585,84 @@ def test_cuda_graph_replay_of_the_whole_step(LF, calib):
         assert np.array_equal(ref[k], got[k]), k
     want = P.process_frame(pts, raw, masks.astype(np.float32), cam, TVC, TVR)
     assert np.array_equal(got['total'], want['total'])
+
+
+# ------------------------------------------------------------------ packed masks in (SURVEY 8(d) secondary accounting)
+
+@pytest.mark.parametrize('W,H', [(1408, 376), (128, 40), (1000, 123), (33, 17), (64, 8), (96, 300), (32, 20)])
+def test_erosion_from_packed_words_matches_cv2(LF, W, H):
+    """Masks packed on the sending side (lf_pack_masks_host) and eroded on the device from the words
+    (lf_erode_pack mode 3): bulk-copy path (whole quads per row), generic path (any W), pad bits."""
+    import torch
+    from lidar_object_detection_b200 import io as IO
+    rng = np.random.default_rng(W * 77 + H)
+    masks = MP.random_blob_masks(rng, 6, H, W, n_blobs=4, max_r=max(4, min(H, W) // 3))
+    masks[3] = 1
+    masks[4, :, :] = 0
+    masks[4, H // 4:, W // 5:] = 1
+    masks[5] = 0
+    words = IO.pack_masks(masks * rng.integers(1, 256, masks.shape, dtype=np.uint8))
+    assert np.array_equal(words, IO.pack_masks_host(masks))
+    raw = LF.PackedMasks(torch.from_numpy(words.view(np.int32)).cuda(), H, W, raw=True)
+    for shape, cvshape in [(LF.MORPH_ELLIPSE, cv2.MORPH_ELLIPSE), (LF.MORPH_RECT, cv2.MORPH_RECT),
+                           (LF.MORPH_CROSS, cv2.MORPH_CROSS)]:
+        for k, it in ((1, 1), (3, 1), (3, 3), (5, 1), (5, 2), (7, 1), (9, 1), (15, 1)):
+            se = cv2.getStructuringElement(cvshape, (k, k))
+            want = np.stack([cv2.erode(m * 255, se, iterations=it) == 255 for m in masks])
+            pm = LF.erode_pack(raw, k, it, shape)
+            assert np.array_equal(pm.unpack().cpu().numpy().astype(bool), want), (W, H, shape, k, it)
+            ref = LF.erode_pack(masks, k, it, shape)
+            assert torch.equal(pm.words, ref.words) and torch.equal(pm.bbox, ref.bbox), (W, H, shape, k, it)
+    # pack only (iterations 0): a copy with the pad bits cleared
+    assert torch.equal(LF.erode_pack(raw, 0, 0).words, LF.erode_pack(masks, 0, 0).words)
+    # a run-time element that is no row span (generic element path)
+    se = np.array([[1, 0, 1], [0, 1, 0], [1, 0, 1]], np.uint8)
+    want = np.stack([cv2.erode(m * 255, se, iterations=1) == 255 for m in masks])
+    assert np.array_equal(LF.erode_pack(raw, 3, 1, se=se).unpack().cpu().numpy().astype(bool), want)
+    # in place is refused (strips read their neighbours' rows)
+    ctx = LF.get_ctx(0)
+    from lidar_object_detection_b200 import _abi
+    se3 = LF.structuring_element(LF.MORPH_ELLIPSE, 3)
+    rc = ctx.lib.lf_erode_pack(ctx.h, _abi.ptr(raw.words), 3, len(raw), H, W, se3.ctypes.data, 3, 1,
+                               _abi.ptr(raw.words), None, ctx.stream)
+    assert rc == _abi.LF_E_ARG
+
+
+def test_batch_from_packed_masks_equals_batch_from_uint8_masks(LF, calib):
+    """The whole step with masks that crossed PCIe bit-packed: identical counters and decisions."""
+    import torch
+    from lidar_object_detection_b200 import io as IO
+    cam, TVC, TVR = calib
+    frames = [100, 250, 2449]
+    pts, npts, masks, nm, corners, nb = [], [], [], [], [], []
+    for fr in frames:
+        p = load_frame(fr)
+        m = (standin(fr, cam)[0] != 0).astype(np.uint8)
+        boxes = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(load_boxes(fr), cam), TVC)
+        c = np.array([b['corners_velo'] for b in boxes], dtype=np.float64).reshape(-1, 8, 3)
+        pts.append(p); npts.append(len(p)); masks.append(m); nm.append(len(m)); corners.append(c); nb.append(len(c))
+    pts, masks, corners = np.concatenate(pts), np.concatenate(masks), np.concatenate(corners)
+    a = LF.FrameBatch(pts, npts, masks, nm, corners, nb, cam, TVR)
+    a.run(3, 1, 50, 10, True)
+    ra = a.results()
+    words = torch.from_numpy(IO.pack_masks(masks).view(np.int32)).cuda()
+    for persistent in (False, True):
+        b = LF.FrameBatch(pts, npts, LF.PackedMasks(words, cam.height, cam.width, raw=True), nm, corners, nb, cam, TVR)
+        b.run(3, 1, 50, 10, True, persistent=persistent)
+        rb = b.results()
+        for k in ra:
+            assert np.array_equal(ra[k], rb[k]), (k, persistent)
+        assert torch.equal(a.packed.words, b.packed.words)
+    g = b.capture(5, 1, 50, 10, True)                      # 5x5 from the packed words, as a graph
+    g.replay()
+    a.run(5, 1, 50, 10, True)
+    ra, rb = a.results(), b.results()
+    for k in ra:
+        assert np.array_equal(ra[k], rb[k]), k
+    # packed masks that are NOT raw are final: used as they are
+    c = LF.FrameBatch(pts, npts, LF.PackedMasks(a.packed.words.clone(), cam.height, cam.width, a.mask_bbox.clone()),
+                      nm, corners, nb, cam, TVR)
+    c.run(3, 1, 50, 10, True)
+    rc = c.results()
+    for k in ra:
+        assert np.array_equal(ra[k], rc[k]), k
