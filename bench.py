@@ -306,14 +306,20 @@ def run_gpu(args):
     # ---- secondary accounting (SURVEY 8(d) "packed-masks-in"): the masks cross PCIe and enter HBM at one
     # bit per pixel (lf_pack_masks_host on the sending side), erosion runs on the device from the words
     packed_in = None
-    if world == 1 and not args.no_packed and not args.persistent:
+    if not args.no_packed and not args.persistent:
         from lidar_object_detection_b200 import io as IO, lidarfuse as LF
         words = LF.erode_pack(batch.masks, 0, 0, device=local).words
         pb = LF.FrameBatch(batch.points, [n_pts] * frames, LF.PackedMasks(words, H_IMG, W_IMG, raw=True), [NCARS] * frames,
                            batch.boxes, sb.n_boxes, cam, TVR, device=local)
+
+        def pstep(mark=None):
+            pb.run(KSIZE, 1, 50, 10, True, mark=mark)
+            if exch is not None:
+                exch.exchange_batch(pb)
+
         for _ in range(3):
-            pb.run(KSIZE, 1, 50, 10, True)
-        torch.cuda.synchronize(dev)
+            pstep()
+        sync_all()
         same = all(torch.equal(a, b) for a, b in ((pb.total, batch.total), (pb.inside, batch.inside),
                                                   (pb.best_idx, batch.best_idx), (pb.packed.words, batch.packed.words)))
         if not same:
@@ -323,15 +329,19 @@ def run_gpu(args):
         p0.record(stream)
         for _ in range(K_steps):
             lst = []
-            pb.run(KSIZE, 1, 50, 10, True, mark=make_mark(lst))
+            pstep(make_mark(lst))
             pm.append(dict(lst))
         p1.record(stream)
-        torch.cuda.synchronize(dev)
+        sync_all()
         pms = p0.elapsed_time(p1) / K_steps
+        if world > 1:
+            t = torch.tensor([pms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            pms = float(t.item())
         wpr = (W_IMG + 31) // 32
         pbytes = sum(16 * n_pts + NCARS * H_IMG * wpr * 4 + 192 * b + 8 * NCARS * (b + 3) for b in sb.n_boxes)
         er_ms = sum(d['zero'].elapsed_time(d['erode_pack']) for d in pm) / len(pm)
-        packed_in = {'value': frames * n_pts / (pms * 1e-3), 'unit': 'points/s', 'ms_per_step': pms,
+        packed_in = {'value': world * frames * n_pts / (pms * 1e-3), 'unit': 'points/s', 'ms_per_step': pms,
                      'kernel_ms': {'erode_pack': er_ms,
                                    'fuse': sum(d['erode_pack'].elapsed_time(d['fuse']) for d in pm) / len(pm)},
                      'algorithmic_bytes_per_step': pbytes, 'achieved_gbs': pbytes / (pms * 1e-3) / 1e9,
@@ -341,25 +351,31 @@ def run_gpu(args):
             hm = h_masks.numpy()
             h_words = torch.empty(words.shape, dtype=words.dtype, pin_memory=True)
             hw = h_words.numpy()
-            threads = os.cpu_count() or 1
+            threads = max(1, (os.cpu_count() or 1) // world)       # the ranks share the host's cores
 
             def e2e_packed_step():
                 pb.upload(h_pts, h_masks, threads=threads)         # packs a slice while the previous one is on the wire
-                pb.run(KSIZE, 1, 50, 10, True)
+                pstep()
                 pb.download(h_out)
                 stream.synchronize()
 
             e2e_packed_step()
             if not torch.equal(h_out, batch.counters.cpu()):
                 raise SystemExit('PARITY FAILURE: host-packed end-to-end step differs')
+            sync_all()
             tp0 = time.perf_counter()
             for _ in range(n_e2e):
                 e2e_packed_step()
+            sync_all()
             dtp = (time.perf_counter() - tp0) / n_e2e
+            if world > 1:
+                t = torch.tensor([dtp], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dtp = float(t.item())
             tq0 = time.perf_counter()
             IO.pack_masks(hm, threads=threads, out=hw)
             tq = time.perf_counter() - tq0
-            packed_in['e2e'] = {'value': frames * n_pts / dtp, 'unit': 'points/s', 'ms_per_step': dtp * 1e3,
+            packed_in['e2e'] = {'value': world * frames * n_pts / dtp, 'unit': 'points/s', 'ms_per_step': dtp * 1e3,
                                 'h2d_bytes_per_step': int(h_pts.numel() * 4 + words.numel() * 4),
                                 'd2h_bytes_per_step': int(h_out.numel() * 4), 'host_pack_threads': threads,
                                 'host_pack_gbs_alone': hm.nbytes / tq / 1e9,
@@ -367,6 +383,13 @@ def run_gpu(args):
                                        'overlapped with their H2D / run / download; pinned uint8 masks in, counters out'}
         t_end = time.time()
         del pb
+        # the end-to-end headline is the faster of the two host-to-host calls; the other stays beside it
+        if e2e is not None and 'e2e' in packed_in and packed_in['e2e']['value'] > e2e['value']:
+            plain = e2e
+            e2e = dict(packed_in['e2e'], variant='masks bit-packed on the host for the transfer (erosion on the device)',
+                       plain_transfer=plain)
+        elif e2e is not None:
+            e2e['variant'] = 'masks sent as uint8 arrays'
 
     clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
     if rank == 0:
