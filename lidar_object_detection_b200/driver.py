@@ -82,3 +82,60 @@ def process_frames(source, detections, camera, TrVeloToCam, TrVeloToRect, master
         if st and master_csv_path:                   # cvs_erosion.py:375-376
             LF.append_to_master_csv(st, k['frame'], master_csv_path, timestamp)
     return out
+
+
+def process_sweeps_streamed(paths, frame_inputs, camera, TrVeloToRect, frames_per_batch=64, erosion_kernel_size=3,
+                            erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True, device=None,
+                            frame_ids=None):
+    """Real-data loop for sequences that do not fit one batch: the ``.bin`` sweeps ``paths`` are read
+    by ``io.SweepStreamer`` (reader thread -> pinned staging -> copy stream) while the previous
+    batch is on the GPU; ``frame_inputs(i) -> (masks [M,H,W] uint8/float32 numpy or CUDA tensor,
+    corners_velo [B,8,3] float64)`` supplies what the detector and the box loader produced for
+    sweep i.  Returns the table rows ``(frame, car_id, matched_bbox_id, total, inside)`` of every
+    car with at least one point, as ``append_to_master_csv`` writes them (cvs_erosion.py:232-265).
+    One ``results()`` read-back per batch."""
+    import torch
+    from . import io as IO
+    ctx = LF.get_ctx(device)
+    frame_ids = list(range(len(paths))) if frame_ids is None else list(frame_ids)
+    rows = []
+    i0 = 0
+    pending = None
+
+    def drain(p):
+        batch, ids = p
+        res = batch.results()
+        for f, fid in enumerate(ids):
+            m0, m1 = batch.h_mask_off[f], batch.h_mask_off[f + 1]
+            has_boxes = batch.h_box_off[f + 1] > batch.h_box_off[f]
+            for c in range(m0, m1):
+                t = int(res['total'][c])
+                if t == 0 or not has_boxes:                # no points -> no row; no boxes -> no statistics
+                    continue
+                bi, bc = int(res['best_idx'][c]), int(res['best_cnt'][c])
+                matched = bi >= 0 and bc >= min_points
+                rows.append((fid, c - m0, bi if matched else -1, t, bc if matched else 0))
+
+    for points, counts, _ in IO.SweepStreamer(paths, frames_per_batch, device=ctx.device.index):
+        n = len(counts)
+        masks, nm, corners, nb = [], [], [], []
+        for i in range(i0, i0 + n):
+            m, c = frame_inputs(i)
+            m = m if isinstance(m, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(m))
+            masks.append(m.to(ctx.device, non_blocking=True))
+            nm.append(len(m))
+            c = np.asarray(c, np.float64).reshape(-1, 8, 3)
+            corners.append(c)
+            nb.append(len(c))
+        mt = torch.cat(masks) if masks else torch.zeros((0, camera.height, camera.width), dtype=torch.uint8,
+                                                        device=ctx.device)
+        batch = LF.FrameBatch(points, counts, mt, nm, np.concatenate(corners) if corners else np.zeros((0, 8, 3)), nb,
+                              camera, TrVeloToRect, device=ctx.device.index)
+        batch.run(erosion_kernel_size, erosion_iterations, max_depth, min_points, use_oriented)
+        if pending is not None:
+            drain(pending)                                 # read batch i-1 back while batch i runs
+        pending = (batch, frame_ids[i0:i0 + n])
+        i0 += n
+    if pending is not None:
+        drain(pending)
+    return rows

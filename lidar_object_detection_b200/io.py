@@ -35,21 +35,31 @@ def sweep_points(path):
     return size // 16
 
 
-def read_sweeps_into(paths, out):
+def read_sweeps_into(paths, out, threads=1):
     """Read the sweeps ``paths`` back to back into ``out`` (float32 [>= sum N, 4], e.g. a
-    view of a pinned tensor).  Returns the per-sweep point counts."""
-    counts, o = [], 0
+    view of a pinned tensor).  Returns the per-sweep point counts.  ``threads`` > 1 reads
+    the files concurrently (``readinto`` releases the GIL; one thread copies ~8 GB/s out of
+    the page cache)."""
+    counts = [sweep_points(p) for p in paths]
     flat = out.reshape(-1)
-    for p in paths:
-        n = sweep_points(p)
-        if (o + n) * 4 > flat.shape[0]:
-            raise ValueError('staging buffer too small')
-        with open(p, 'rb') as fh:
+    if sum(counts) * 4 > flat.shape[0]:
+        raise ValueError('staging buffer too small')
+    starts = np.concatenate([[0], np.cumsum(counts)[:-1]]).astype(np.int64) if counts else []
+
+    def one(i):
+        o, n = int(starts[i]), counts[i]
+        with open(paths[i], 'rb') as fh:
             got = fh.readinto(memoryview(flat[o * 4:(o + n) * 4]).cast('B'))
         if got != n * 16:
-            raise IOError('%s: short read' % p)
-        counts.append(n)
-        o += n
+            raise IOError('%s: short read' % paths[i])
+
+    if threads > 1 and len(paths) > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(int(threads), len(paths))) as ex:
+            list(ex.map(one, range(len(paths))))
+    else:
+        for i in range(len(paths)):
+            one(i)
     return counts
 
 
@@ -63,13 +73,14 @@ class SweepStreamer:
     Two pinned staging buffers and two device buffers: while batch i is being consumed,
     batch i+1 is read from disk by a worker thread and copied on a side stream."""
 
-    def __init__(self, paths, frames_per_batch=64, device=None, max_points_per_frame=None):
+    def __init__(self, paths, frames_per_batch=64, device=None, max_points_per_frame=None, reader_threads=4):
         import torch
         if not torch.cuda.is_available():
             raise _abi.LidarFuseError('SweepStreamer needs a CUDA device (no CPU fallback)')
         self.torch = torch
         self.paths = list(paths)
         self.fpb = int(frames_per_batch)
+        self.reader_threads = int(reader_threads)
         self.device = torch.device('cuda', torch.cuda.current_device() if device is None else device)
         counts = [sweep_points(p) for p in self.paths]
         self.counts = counts
@@ -85,7 +96,7 @@ class SweepStreamer:
     def _stage(self, b, slot, result):
         try:
             paths = self.paths[b * self.fpb:(b + 1) * self.fpb]
-            result['counts'] = read_sweeps_into(paths, self.host[slot].numpy())
+            result['counts'] = read_sweeps_into(paths, self.host[slot].numpy(), self.reader_threads)
             result['paths'] = paths
         except Exception as e:                                        # surfaced in the consumer thread
             result['error'] = e

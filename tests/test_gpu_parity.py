@@ -666,3 +666,86 @@ def test_batch_from_packed_masks_equals_batch_from_uint8_masks(LF, calib):
     rc = c.results()
     for k in ra:
         assert np.array_equal(ra[k], rc[k]), k
+
+
+def test_erosion_shape_sweep_with_canaries(LF):
+    """Bounds check of our own (no sanitizer on this pool): every mask format over a sweep of image
+    shapes -- one-word rows, one-quad rows, strips of 1..97 rows, ragged last words -- through the C ABI
+    into output buffers fenced by canary words; results against cv2, canaries untouched."""
+    import torch
+    from lidar_object_detection_b200 import _abi, io as IO
+    ctx = LF.get_ctx(0)
+    rng = np.random.default_rng(99)
+    CAN = 0x5A5A5A5A
+    widths = [1, 2, 31, 32, 33, 63, 64, 65, 96, 127, 128, 129, 160, 256, 257, 512, 1408]
+    heights = [1, 2, 3, 15, 16, 17, 33, 95, 96, 97, 193]
+    n_cases = 0
+    for W in widths:
+        for H in heights:
+            if W * H > 80000 and (W, H) != (1408, 97):
+                continue
+            M = 3
+            masks = (rng.random((M, H, W)) < 0.85).astype(np.uint8)
+            masks[1] = 1
+            masks[2, : H // 2] = 0
+            wpr = (W + 31) // 32
+            words_in = torch.from_numpy(IO.pack_masks_host(masks).view(np.int32)).cuda()
+            srcs = {0: torch.from_numpy(masks).cuda(), 1: torch.from_numpy(masks.astype(np.float32)).cuda(),
+                    2: torch.from_numpy(masks.astype(np.float32) * 0.75).cuda(), 3: words_in}
+            for k, it, shape, cvshape in ((3, 1, LF.MORPH_ELLIPSE, cv2.MORPH_ELLIPSE), (7, 2, LF.MORPH_ELLIPSE, cv2.MORPH_ELLIPSE),
+                                          (5, 1, LF.MORPH_RECT, cv2.MORPH_RECT)):
+                se = LF.structuring_element(shape, k)
+                want = np.stack([cv2.erode(m * 255, cv2.getStructuringElement(cvshape, (k, k)), iterations=it) == 255
+                                 for m in masks])
+                want_words = IO.pack_masks_host(want)
+                for mode, src in srcs.items():
+                    n = M * H * wpr
+                    buf = torch.full((n + 64,), CAN, dtype=torch.int32, device='cuda')
+                    bb = torch.full((4 * M + 16,), 0, dtype=torch.int32, device='cuda')
+                    bb[:8] = CAN
+                    bb[8 + 4 * M:] = CAN
+                    rc = ctx.lib.lf_erode_pack(ctx.h, _abi.ptr(src), mode, M, H, W, se.ctypes.data, k, it,
+                                               buf.data_ptr() + 32 * 4, bb.data_ptr() + 8 * 4, ctx.stream)
+                    assert rc == 0, (W, H, k, it, mode, rc)
+                    got = buf.cpu().numpy()
+                    assert (got[:32] == CAN).all() and (got[32 + n:] == CAN).all(), ('canary', W, H, k, it, mode)
+                    assert np.array_equal(got[32:32 + n].view(np.uint32).reshape(M, H, wpr), want_words), (W, H, k, it, mode)
+                    gb = bb.cpu().numpy()
+                    assert (gb[:8] == CAN).all() and (gb[8 + 4 * M:] == CAN).all(), ('bbox canary', W, H, k, it, mode)
+                    for c in range(M):                                  # bounding box of the eroded mask
+                        ys, xs = np.nonzero(want[c])
+                        rec = gb[8 + 4 * c:12 + 4 * c]
+                        if len(ys) == 0:
+                            assert (rec == 0).all(), (W, H, k, it, mode, c)
+                        else:
+                            assert tuple(rec) == ((1 << 20) - xs.min(), (1 << 20) - ys.min(), xs.max() + 1, ys.max() + 1), \
+                                (W, H, k, it, mode, c)
+                    n_cases += 1
+    assert n_cases > 1500
+
+
+def test_streamed_sweeps_give_the_rows_of_the_single_batch(LF, calib, golden, tmp_path):
+    """Real-data loop (I/O row): .bin sweeps -> SweepStreamer (reader thread, pinned staging, copy
+    stream) -> one FrameBatch per 7 sweeps, read back one batch behind.  Rows identical with the whole
+    sequence in ONE batch and with the reference's CSV (same counts, same decisions)."""
+    import csv
+    from lidar_object_detection_b200 import driver
+    cam, TVC, TVR = calib
+    frames = [f for f in golden['_meta']['frames'] if load_boxes(f)]
+    paths, inputs = [], []
+    for fr in frames:
+        p = str(tmp_path / ('%010d.bin' % fr))
+        load_frame(fr).astype(np.float32).tofile(p)
+        paths.append(p)
+        m, b, c = standin(fr, cam)                                   # confidence-descending already
+        boxes = LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(load_boxes(fr), cam), TVC)
+        inputs.append(((m != 0).astype(np.uint8), np.array([bx['corners_velo'] for bx in boxes]).reshape(-1, 8, 3)))
+    rows = driver.process_sweeps_streamed(paths, lambda i: inputs[i], cam, TVR, frames_per_batch=7, frame_ids=frames)
+    # the reference's CSV for the same detections (written by the unmodified cvs_erosion.process_frames)
+    want = []
+    with open(os.path.join(GOLDEN, 'master_car_statistics_erosion3.csv')) as fh:
+        for r in csv.DictReader(fh):
+            want.append((int(r['frame']), int(r['car_id']), int(r['matched_bbox_id']), int(r['total_points']),
+                         int(r['points_inside_bbox'])))
+    assert sorted(rows) == sorted(want)
+    assert [r[0] for r in rows] == sorted(r[0] for r in rows)        # batches come back in order
