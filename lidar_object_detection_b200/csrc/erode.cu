@@ -226,6 +226,23 @@ lf_erode_fast_kernel(const __grid_constant__ ErodeParams P, const uint8_t* __res
     erode_fast_item<SE, ER_STAGES, MODE>(P, masks, packed, bbox, blockIdx.x, smem, full_bar, cbase);
 }
 
+// masks that arrive bit-packed (mode 3, whole quads per row): one CTA = (mask, strip), rows copied
+// straight into the guarded layout
+template <class SE>
+__global__ void __launch_bounds__(ER_THREADS, 8)
+lf_erode_packed_kernel(const __grid_constant__ ErodeParams P, const uint32_t* __restrict__ words,
+                       uint32_t* __restrict__ packed, int32_t* __restrict__ bbox) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    uint32_t cbase = 0;
+    erode_packed_item<SE>(P, words, packed, bbox, blockIdx.x, smem, &bar, cbase);
+}
+
 template <class SE, int MODE>
 cudaError_t launch_fast_mode(const ErodeParams& P, const uint8_t* masks, uint32_t* packed, int32_t* bbox,
                              unsigned grid, size_t smem, cudaStream_t s) {
@@ -241,7 +258,16 @@ cudaError_t launch_fast(const ErodeParams& P, int mode, const uint8_t* masks, ui
                         unsigned grid, size_t smem, cudaStream_t s) {
     if (mode == 0) return launch_fast_mode<SE, 0>(P, masks, packed, bbox, grid, smem, s);
     if (mode == 1) return launch_fast_mode<SE, 1>(P, masks, packed, bbox, grid, smem, s);
-    if (mode == 3) return launch_fast_mode<SE, 3>(P, masks, packed, bbox, grid, smem, s);
+    if (mode == 3) {
+        cudaError_t e = cudaFuncSetAttribute(lf_erode_packed_kernel<SE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem);
+        if (e != cudaSuccess) return e;
+        // latency-bound (load -> erode -> store per CTA): as many resident CTAs as the SM takes
+        e = cudaFuncSetAttribute(lf_erode_packed_kernel<SE>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (e != cudaSuccess) return e;
+        lf_erode_packed_kernel<SE><<<grid, ER_THREADS, smem, s>>>(P, (const uint32_t*)masks, packed, bbox);
+        return cudaGetLastError();
+    }
     return launch_fast_mode<SE, 2>(P, masks, packed, bbox, grid, smem, s);
 }
 
@@ -381,8 +407,12 @@ int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int
         else if (se_matches<SeRect7>(P)) spec = 7;
         else if (se_matches<SeCross7>(P)) spec = 8;
     }
-    if (spec >= 0) P.buf_words = (buf_rows + 2 * P.r) * (P.wpr + 1) + 1;
-    const size_t smem = (size_t)P.buf_words * 4 * (iterations > 0 ? 2 : 1) + (fastp ? stages * ER_CHUNK : 0);
+    // guarded layout of the compile-time-element kernels: row stride wpr + pad, k/2 guard rows each side;
+    // packed words in (mode 3) are copied there row by row (pad 4 keeps rows 16-byte aligned), no staging
+    const int pad = mode == 3 ? 4 : 1;
+    if (spec >= 0) P.buf_words = (buf_rows + 2 * P.r) * (P.wpr + pad) + pad;
+    const size_t smem = (size_t)P.buf_words * 4 * (iterations > 0 ? 2 : 1) +
+                        (fastp && mode != 3 ? stages * ER_CHUNK : 0);
     if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
     *spec_out = spec; *fast_out = fastp ? 1 : 0; *smem_out = smem;
     return LF_OK;
@@ -401,7 +431,9 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
     ErodeParams P;
     int spec, fast;
     size_t smem;
-    const int rc = lf_erode_plan(ctx, masks, mode, m, H, W, se, k, iterations, ER_MAX_ROWS, ER_STAGES, &P, &spec, &fast, &smem);
+    const int rc = lf_erode_plan(ctx, masks, mode, m, H, W, se, k, iterations,
+                                 mode == 3 ? ER_MAX_ROWS_PACKED : ER_MAX_ROWS, ER_STAGES, &P,
+                                 &spec, &fast, &smem);
     if (rc != LF_OK) return rc;
     const unsigned grid = (unsigned)(m * P.strips);
     cudaStream_t s = (cudaStream_t)stream;

@@ -11,6 +11,7 @@ constexpr int ER_STAGES_BATCH = 4;    // persistent batch kernel: more bytes in 
 constexpr int ER_CHUNK = 8192;          // bytes per stage: 256 threads x 32 px
 constexpr int ER_MAX_ROWS = 96;         // strip height bound (smem: 2 x (96+2*halo) x wpr x 4)
 constexpr int ER_MAX_ROWS_BATCH = 96;
+constexpr int ER_MAX_ROWS_PACKED = 64;  // masks that arrive bit-packed (mode 3): 26 KB per CTA, 8 CTAs per SM
 
 struct ErodeParams {
     int H, W, wpr;
@@ -149,8 +150,100 @@ __device__ __forceinline__ uint32_t pack8f(const uint4 a, const uint4 b) {
     return r;
 }
 
-// MODE 0: uint8 masks (non-zero = set), 1 byte per pixel; MODE 1 / 2: float32 masks, 4 bytes per pixel;
-// MODE 3: masks that arrive bit-packed already (uint32 [M][H][wpr], LSB = lowest x), 1/8 byte per pixel.
+// One erosion pass over `items` words of the guarded layout (row stride S = wpr + PAD words, PAD guard
+// words of ones between rows, word (row 0, wx 0) at `data0`).  Returns the OR of the centre words the
+// thread saw.
+template <class SE, int PAD>
+__device__ __forceinline__ uint32_t erode_pass_fast(const ErodeParams& P, const uint32_t* cur, uint32_t* nxt, int items,
+                                                    int S, int data0, int tid) {
+    constexpr int K = SE::k, RAD = K / 2;
+    uint32_t seen = 0;
+    for (int it = tid; it < items; it += ER_THREADS) {
+        const int idx = it + PAD * mdiv(it, P.wpr_magic) + data0;
+        const uint32_t ctr = cur[idx];
+        seen |= ctr;
+        if (ctr == 0u) {                                   // the anchor is part of every element here
+            nxt[idx] = 0u;
+            continue;
+        }
+        uint32_t acc = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < K; ++i) {
+            const int h = SE::hw(i);
+            if (h < 0) continue;
+            const uint32_t* rp = cur + idx + (i - RAD) * S;
+            const uint32_t c = rp[0];
+            acc &= c;
+            if (h > 0) {
+                const uint32_t l = rp[-1], r = rp[1];
+#pragma unroll
+                for (int d = 1; d <= h; ++d) acc &= __funnelshift_r(c, r, d) & __funnelshift_l(l, c, d);
+            }
+        }
+        nxt[idx] = acc;
+    }
+    return seen;
+}
+
+// Rows [r0, r1) of the result from the guarded layout to global memory + the mask's bounding box.
+template <int PAD>
+__device__ __forceinline__ void store_rows_fast(const ErodeParams& P, const uint32_t* cur, uint32_t* __restrict__ dstw,
+                                                int32_t* __restrict__ bbox_rec, int r0, int r1, int first, int S,
+                                                int tid) {
+    // `first` = word index of (row r0, wx 0) in `cur`
+    BBoxAcc acc;
+    if ((P.wpr & 3) == 0) {
+        // four words per thread: one 128-bit store, one bounding-box test per 128 pixels
+        const int qpr = P.wpr >> 2;                        // quads per row
+        const unsigned qmagic = (unsigned)((0x100000000ULL + qpr - 1) / qpr);
+        const int nq = (r1 - r0) * qpr;
+        for (int q = tid; q < nq; q += ER_THREADS) {
+            const int lr = mdiv(q, qmagic);
+            const int wq = q - lr * qpr;
+            const uint32_t* sp = cur + lr * S + 4 * wq + first;
+            const uint4 v = PAD == 4 ? *(const uint4*)sp : make_uint4(sp[0], sp[1], sp[2], sp[3]);
+            *(uint4*)(dstw + 4 * q) = v;
+            if (v.x | v.y | v.z | v.w) {
+                acc.add(v.x, r0 + lr, 4 * wq); acc.add(v.y, r0 + lr, 4 * wq + 1);
+                acc.add(v.z, r0 + lr, 4 * wq + 2); acc.add(v.w, r0 + lr, 4 * wq + 3);
+            }
+        }
+    } else {
+        const int out_items = (r1 - r0) * P.wpr;
+        for (int it = tid; it < out_items; it += ER_THREADS) {
+            const int lr = mdiv(it, P.wpr_magic);
+            const uint32_t w = cur[it + PAD * lr + first];
+            dstw[it] = w;
+            acc.add(w, r0 + lr, it - lr * P.wpr);
+        }
+    }
+    if (bbox_rec) acc.flush(bbox_rec);
+}
+
+__device__ __forceinline__ void store_zero_rows(const ErodeParams& P, uint32_t* __restrict__ dstw, int out_items, int tid) {
+    if ((P.wpr & 3) == 0) {
+        for (int q = tid; q < (out_items >> 2); q += ER_THREADS) *(uint4*)(dstw + 4 * q) = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+        for (int it = tid; it < out_items; it += ER_THREADS) dstw[it] = 0u;
+    }
+}
+
+// ones in every guard position of the layout: RAD rows above and below the window, the PAD words
+// before every row (= right neighbours of the previous row) and after the last one
+template <int PAD>
+__device__ __forceinline__ void fill_guards(uint32_t* bufA, uint32_t* bufB, int nrows, int RAD, int S, int tid) {
+    const int top = RAD * S, all = (nrows + 2 * RAD) * S + PAD;
+    for (int i = tid; i < top; i += ER_THREADS) {
+        bufA[i] = 0xFFFFFFFFu; bufB[i] = 0xFFFFFFFFu;
+        bufA[all - 1 - i] = 0xFFFFFFFFu; bufB[all - 1 - i] = 0xFFFFFFFFu;
+    }
+    for (int g = tid; g < (nrows + 1) * PAD; g += ER_THREADS) {
+        const int r = g / PAD, j = g - r * PAD;
+        bufA[(r + RAD) * S + j] = 0xFFFFFFFFu; bufB[(r + RAD) * S + j] = 0xFFFFFFFFu;
+    }
+}
+
+// MODE 0: uint8 masks (non-zero = set), 1 byte per pixel; MODE 1 / 2: float32 masks, 4 bytes per pixel.
 template <class SE, int NST, int MODE = 0>
 __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint8_t* __restrict__ masks,
                                                 uint32_t* __restrict__ packed, int32_t* __restrict__ bbox,
@@ -160,14 +253,15 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
     uint32_t* bufA = (uint32_t*)(smem + NST * ER_CHUNK);
     uint32_t* bufB = bufA + P.buf_words;
 
-    const int64_t mask = item / P.strips;
-    const int strip = (int)(item - mask * P.strips);
+    const unsigned mask32 = (unsigned)item / (unsigned)P.strips;          // item < 2^31 (lf_erode_plan)
+    const int64_t mask = mask32;
+    const int strip = (int)((unsigned)item - mask32 * (unsigned)P.strips);
     int r0, r1, ga, gb;
     strip_rows(P, strip, r0, r1, ga, gb);
-    const int row_bytes = MODE == 0 ? P.W : (MODE == 3 ? 4 * P.wpr : 4 * P.W);
+    const int row_bytes = MODE == 0 ? P.W : 4 * P.W;
     const uint8_t* src = masks + (mask * P.H + ga) * (int64_t)row_bytes;
     const int nrows = gb - ga;
-    const int L = nrows * row_bytes;                       // bytes in the run (a multiple of 16)
+    const int L = nrows * row_bytes;                       // bytes in the run (a multiple of 32)
     const int nch = (L + ER_CHUNK - 1) / ER_CHUNK;
     const int S = P.wpr + 1;                               // row stride in words
     const int tid = threadIdx.x;
@@ -181,17 +275,7 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
             bulk_g2s(smem + si * ER_CHUNK, src + (int64_t)i * ER_CHUNK, bytes, &full_bar[si]);
         }
     }
-    // guards: RAD rows above and below the window, word 0 of every row, one trailing word
-    if (P.iterations > 0) {
-        const int top = RAD * S, all = (nrows + 2 * RAD) * S + 1;
-        for (int i = tid; i < top; i += ER_THREADS) {
-            bufA[i] = 0xFFFFFFFFu; bufB[i] = 0xFFFFFFFFu;
-            bufA[all - 1 - i] = 0xFFFFFFFFu; bufB[all - 1 - i] = 0xFFFFFFFFu;
-        }
-        for (int r = tid; r <= nrows; r += ER_THREADS) {
-            bufA[(r + RAD) * S] = 0xFFFFFFFFu; bufB[(r + RAD) * S] = 0xFFFFFFFFu;
-        }
-    }
+    if (P.iterations > 0) fill_guards<1>(bufA, bufB, nrows, RAD, S, tid);
     const int data0 = RAD * S + 1;                         // word index of (row 0, wx 0)
     uint32_t nz = 0;                                       // OR of every word this thread produced
 
@@ -225,18 +309,6 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
             // flat word w -> row w / wpr; with the guard column the smem index is w + row + data0
             if (p0) { const uint32_t w = pack32(a0, a1); nz |= w; bufA[w0 + mdiv(w0, P.wpr_magic) + data0] = w; }
             if (p1) { const uint32_t w = pack32(b0, b1); nz |= w; bufA[w1 + mdiv(w1, P.wpr_magic) + data0] = w; }
-        } else if (MODE == 3) {
-            // packed words in: the thread's 32 bytes are 8 words, moved to the guarded layout as they are
-            // (the run ends on a 16-byte boundary, so the last group may hold four words only)
-            const uint32_t va[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const uint32_t vb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            const int nw = L >> 2;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int x0 = 8 * w0 + j, x1 = 8 * w1 + j;
-                if (p0 && x0 < nw) { nz |= va[j]; bufA[x0 + mdiv(x0, P.wpr_magic) + data0] = va[j]; }
-                if (p1 && x1 < nw) { nz |= vb[j]; bufA[x1 + mdiv(x1, P.wpr_magic) + data0] = vb[j]; }
-            }
         } else {
             // float32: the thread's 32 bytes are 8 pixels = one byte of a packed word (w0 / w1 count
             // 8-pixel groups here); little-endian bytes are in bit order, so a byte store does it
@@ -256,75 +328,78 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
     }
 
     uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
-    const int out_items = (r1 - r0) * P.wpr;
     cbase += (uint32_t)nch;
     // Instance masks are mostly background: a window without a set pixel erodes to nothing, so the
     // strip is written as zeros straight away (the barrier doubles as the one after the fill).
     if (!er_sync_or(nz != 0u)) {
-        if ((P.wpr & 3) == 0) {
-            for (int q = tid; q < (out_items >> 2); q += ER_THREADS) *(uint4*)(dstw + 4 * q) = make_uint4(0u, 0u, 0u, 0u);
-        } else {
-            for (int it = tid; it < out_items; it += ER_THREADS) dstw[it] = 0u;
-        }
+        store_zero_rows(P, dstw, (r1 - r0) * P.wpr, tid);
         return;
     }
     uint32_t* cur = bufA;
     uint32_t* nxt = bufB;
-    const int items = nrows * P.wpr;
     for (int itn = 0; itn < P.iterations; ++itn) {
         if (itn) er_sync();
-        for (int it = tid; it < items; it += ER_THREADS) {
-            const int idx = it + mdiv(it, P.wpr_magic) + data0;
-            if (cur[idx] == 0u) {                          // the anchor is part of every element here
-                nxt[idx] = 0u;
-                continue;
-            }
-            uint32_t acc = 0xFFFFFFFFu;
-#pragma unroll
-            for (int i = 0; i < K; ++i) {
-                const int h = SE::hw(i);
-                if (h < 0) continue;
-                const uint32_t* rp = cur + idx + (i - RAD) * S;
-                const uint32_t c = rp[0];
-                acc &= c;
-                if (h > 0) {
-                    const uint32_t l = rp[-1], r = rp[1];
-#pragma unroll
-                    for (int d = 1; d <= h; ++d) acc &= __funnelshift_r(c, r, d) & __funnelshift_l(l, c, d);
-                }
-            }
-            nxt[idx] = acc;
-        }
+        erode_pass_fast<SE, 1>(P, cur, nxt, nrows * P.wpr, S, data0, tid);
         uint32_t* t = cur; cur = nxt; nxt = t;
     }
     if (P.iterations > 0) er_sync();
-    const int skip = (r0 - ga) * S;
-    BBoxAcc acc;
-    if ((P.wpr & 3) == 0) {
-        // four words per thread: one 128-bit store, one bounding-box test per 128 pixels
-        const int qpr = P.wpr >> 2;                        // quads per row
-        const unsigned qmagic = (unsigned)((0x100000000ULL + qpr - 1) / qpr);
-        const int nq = (r1 - r0) * qpr;
-        for (int q = tid; q < nq; q += ER_THREADS) {
-            const int lr = mdiv(q, qmagic);
-            const int wq = q - lr * qpr;
-            const uint32_t* sp = cur + lr * S + 4 * wq + data0 + skip;
-            const uint4 v = make_uint4(sp[0], sp[1], sp[2], sp[3]);
-            *(uint4*)(dstw + 4 * q) = v;
-            if (v.x | v.y | v.z | v.w) {
-                acc.add(v.x, r0 + lr, 4 * wq); acc.add(v.y, r0 + lr, 4 * wq + 1);
-                acc.add(v.z, r0 + lr, 4 * wq + 2); acc.add(v.w, r0 + lr, 4 * wq + 3);
-            }
+    store_rows_fast<1>(P, cur, dstw, bbox ? bbox + 4 * mask : nullptr, r0, r1, data0 + (r0 - ga) * S, S, tid);
+}
+
+// Masks that arrive bit-packed already (mode 3: uint32 [M][H][wpr], LSB = lowest x; whole quads per
+// row).  No staging and no fill pass: one bulk copy per row drops the words straight into the guarded
+// layout (row stride wpr + 4 words keeps every row 16-byte aligned), the first erosion pass notices
+// an all-zero window on the way.  `smem` = the two buffers; `bar` = one mbarrier (count 1) whose
+// phase runs on from item to item (`cbase` counts items).
+template <class SE>
+__device__ __forceinline__ void erode_packed_item(const ErodeParams& P, const uint32_t* __restrict__ words,
+                                                  uint32_t* __restrict__ packed, int32_t* __restrict__ bbox,
+                                                  int64_t item, uint8_t* smem, uint64_t* bar, uint32_t& cbase) {
+    constexpr int K = SE::k, RAD = K / 2, PAD = 4;
+    uint32_t* bufA = (uint32_t*)smem;
+    uint32_t* bufB = bufA + P.buf_words;
+    const unsigned mask32 = (unsigned)item / (unsigned)P.strips;
+    const int64_t mask = mask32;
+    const int strip = (int)((unsigned)item - mask32 * (unsigned)P.strips);
+    int r0, r1, ga, gb;
+    strip_rows(P, strip, r0, r1, ga, gb);
+    const int nrows = gb - ga;
+    const int S = P.wpr + PAD;
+    const int data0 = RAD * S + PAD;
+    const int tid = threadIdx.x;
+    const uint32_t* src = words + (mask * P.H + ga) * (int64_t)P.wpr;
+    const uint32_t row_bytes = 4u * (uint32_t)P.wpr;
+
+    if (tid < 32) {                                        // warp 0 issues the row copies
+        if (tid == 0) {
+            fence_proxy_async_smem();                      // the previous item read these buffers
+            mbar_expect_tx(bar, row_bytes * (uint32_t)nrows);
         }
-    } else {
-        for (int it = tid; it < out_items; it += ER_THREADS) {
-            const int lr = mdiv(it, P.wpr_magic);
-            const uint32_t w = cur[it + lr + data0 + skip];
-            dstw[it] = w;
-            acc.add(w, r0 + lr, it - lr * P.wpr);
+        __syncwarp();
+        for (int r = tid; r < nrows; r += 32)
+            bulk_g2s(bufA + data0 + r * S, src + (int64_t)r * P.wpr, row_bytes, bar);
+    }
+    if (P.iterations > 0) fill_guards<PAD>(bufA, bufB, nrows, RAD, S, tid);
+    uint32_t* dstw = packed + (mask * (int64_t)P.H + r0) * P.wpr;
+    mbar_wait(bar, cbase & 1u);
+    cbase += 1u;
+    uint32_t* cur = bufA;
+    uint32_t* nxt = bufB;
+    if (P.iterations > 0) {
+        er_sync();                                         // guards written
+        uint32_t seen = 0;
+        for (int itn = 0; itn < P.iterations; ++itn) {
+            if (itn) er_sync();
+            const uint32_t sn = erode_pass_fast<SE, PAD>(P, cur, nxt, nrows * P.wpr, S, data0, tid);
+            if (itn == 0) seen = sn;
+            uint32_t* t = cur; cur = nxt; nxt = t;
+        }
+        if (!er_sync_or(seen != 0u)) {                     // nothing set anywhere in the window
+            store_zero_rows(P, dstw, (r1 - r0) * P.wpr, tid);
+            return;
         }
     }
-    if (bbox) acc.flush(bbox + 4 * mask);
+    store_rows_fast<PAD>(P, cur, dstw, bbox ? bbox + 4 * mask : nullptr, r0, r1, data0 + (r0 - ga) * S, S, tid);
 }
 
 typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)

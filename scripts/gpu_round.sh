@@ -13,6 +13,6 @@ timeout 600 python bench.py --persistent --no-cpu-baseline > gpurun_out/bench_pe
 timeout 600 python bench_next.py > gpurun_out/bench_next.jsonl 2>> gpurun_out/bench.err; echo "next rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-parity > gpurun_out/ncu_l.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'lf_erode_fast_kernel|lf_fuse_kernel' -s 4 -c 2 -o gpurun_out/full -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-parity --no-packed > gpurun_out/ncu_f.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:'lf_erode_fast_kernel.*, 3>' -s 1 -c 1 -o gpurun_out/full_packed -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-parity > gpurun_out/ncu_p.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'lf_erode_packed_kernel' -s 1 -c 1 -o gpurun_out/full_packed -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-parity > gpurun_out/ncu_p.log 2>&1
 timeout 300 python scripts/latency_cfg12.py > gpurun_out/latency_cfg12.json 2>> gpurun_out/bench.err; echo "latency rc=$?"
 ls -la gpurun_out
