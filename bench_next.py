@@ -116,7 +116,7 @@ def main():
     cols = torch.rand((16, 3), dtype=torch.float64, device=dev)
     rgb = torch.empty((n, 3), dtype=torch.float64, device=dev)
     bg = np.array([0.5, 0.5, 0.5])
-    timed(lambda: check(ctx.lib.lf_point_colors(ctx.h, ptr(bits), n, ptr(cols), 16, bg.ctypes.data, ptr(rgb), None, st),
+    timed(lambda: check(ctx.lib.lf_point_colors(ctx.h, ptr(bits), n, ptr(cols), 16, bg.ctypes.data, ptr(rgb), None, 0, st),
                         ctx.h), n * (8 + 24), 'lf_point_colors', '%d points, 16 masks, f64 RGB out' % n)
     del bits, rgb
     from lidar_object_detection_b200 import colour as C
@@ -133,6 +133,9 @@ def main():
             check(ctx.lib.lf_depth_overlay(ctx.h, ptr(dm[i]), ptr(mx[i:]), ptr(img[i]), ptr(lut), 256, H, W,
                                            ptr(out[i]), st), ctx.h)
     timed(overlay, nf * H * W * (8 + 3 + 3), 'lf_depth_overlay', '%d launches of one %dx%d frame each' % (nf, W, H))
+    timed(lambda: check(ctx.lib.lf_depth_overlay_batch(ctx.h, ptr(dm), ptr(mx), ptr(img), H * W * 3, ptr(lut), 256, nf, H, W,
+                                                       ptr(out), st), ctx.h),
+          nf * H * W * (8 + 3 + 3), 'lf_depth_overlay_batch', '%d frames of %dx%d in one launch' % (nf, W, H))
     # rank 4: real sweeps from disk through SweepStreamer + one FrameBatch per 64 sweeps (page-cache reads)
     import glob
     import tempfile

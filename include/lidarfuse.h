@@ -263,10 +263,14 @@ int lf_match_matrices(lf_ctx* ctx, const double* dets /*DEVICE [sum D][4]*/, con
 /* Per-point RGB of the V4 / V5 coloured clouds (V4:290-307; V5:524-550): colors_rgb[c]
  * (f64 [m][3], already BGR->RGB and / 255) of the last mask whose bit is set in
  * car_bits[i] (from lf_mask_gather / lf_fuse_batch), bg_rgb (HOST [3]) otherwise.
- * assigned (optional) = the scripts' bg_assigned flag. */
+ * assigned (optional) = the scripts' bg_assigned flag.
+ * policy: 0 = the LAST mask containing the point wins (V4 / V5 / vis.py:175-205 build one cloud
+ * per mask and draw them in mask order); 1 = the FIRST one wins (the per-point loop with
+ * `break` of Same_color.py:112-127). */
 int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits /*DEVICE [n]*/, int64_t n,
                     const double* colors_rgb /*DEVICE [m][3]*/, int m, const double bg_rgb[3] /*HOST*/,
-                    double* rgb /*DEVICE [n][3]*/, uint8_t* assigned /*DEVICE [n] or NULL*/, void* stream);
+                    double* rgb /*DEVICE [n][3]*/, uint8_t* assigned /*DEVICE [n] or NULL*/, int policy,
+                    void* stream);
 
 /* Depth map overlay of seg_with_pointcloud.py:173-180: where depth_map > 0 the pixel is
  * lut[int(depth / *depth_max * lut_n)] (matplotlib Colormap.__call__), elsewhere
@@ -275,6 +279,14 @@ int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits /*DEVICE [n]*/, int64_
 int lf_depth_overlay(lf_ctx* ctx, const double* depth_map /*DEVICE [H][W]*/, const double* depth_max /*DEVICE [1]*/,
                      const uint8_t* image_rgb /*DEVICE [H][W][3]*/, const double* lut_rgb /*DEVICE [lut_n][3]*/,
                      int lut_n, int H, int W, uint8_t* out_bgr /*DEVICE [H][W][3]*/, void* stream);
+
+/* The same for n depth maps in one launch (the loop over cars of seg_with_pointcloud.py:173-180,
+ * or over frames): depth_maps [n][H][W], depth_max [n]; image_stride = bytes between the images
+ * of consecutive maps, 0 = every map is laid over the same image. */
+int lf_depth_overlay_batch(lf_ctx* ctx, const double* depth_maps /*DEVICE [n][H][W]*/,
+                           const double* depth_max /*DEVICE [n]*/, const uint8_t* image_rgb /*DEVICE*/,
+                           int64_t image_stride, const double* lut_rgb /*DEVICE [lut_n][3]*/, int lut_n, int n,
+                           int H, int W, uint8_t* out_bgr /*DEVICE [n][H][W][3]*/, void* stream);
 
 /* ---- next rows: I/O formats ----------------------------------------- */
 

@@ -56,8 +56,9 @@ SIGNATURES = {
     'lf_resize_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _vp]),
     'lf_project_boxes': (C.c_int, [_vp, _vp, _i64, _f64, _f64, _i32, _vp, _vp, _vp, _vp, _vp]),
     'lf_match_matrices': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _f64, _f64, _f64, _vp, _vp, _vp]),
-    'lf_point_colors': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _vp, _vp]),
+    'lf_point_colors': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _vp, _i32, _vp]),
     'lf_depth_overlay': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    'lf_depth_overlay_batch': (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     'lf_format_csv_rows': (C.c_int64, [_vp, _vp, _vp, _vp, _vp, _i64, C.c_char_p, _i32, _vp, _i64]),
     'lf_synth_points': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _u64, _vp, _vp]),
     'lf_synth_masks': (C.c_int, [_vp, _vp, _i32, _i32, _vp, _f64, _vp, _vp]),

@@ -8,18 +8,19 @@
 
 namespace {
 
-// colour of the LAST mask that contains the point: the reference builds one point cloud per
-// mask in mask order and draws them in that order, so at equal depth the later one is on top.
+// colour of the LAST mask that contains the point: V4 / V5 / vis.py build one point cloud per
+// mask in mask order and draw them in that order, so at equal depth the later one is on top;
+// first_wins: the per-point loop of Same_color.py:112-127 stops at the first mask that matches.
 __global__ void __launch_bounds__(256)
 lf_point_colors_kernel(const unsigned long long* __restrict__ bits, int64_t n, const double* __restrict__ colors,
                        int m, double bg0, double bg1, double bg2, double* __restrict__ rgb,
-                       uint8_t* __restrict__ assigned) {
+                       uint8_t* __restrict__ assigned, int first_wins) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         unsigned long long b = bits[i];
         if (m < 64) b &= (1ULL << m) - 1ULL;
         double r = bg0, g = bg1, bl = bg2;
         if (b) {
-            const int c = 63 - __clzll((long long)b);
+            const int c = first_wins ? __ffsll((long long)b) - 1 : 63 - __clzll((long long)b);
             r = colors[3 * c]; g = colors[3 * c + 1]; bl = colors[3 * c + 2];
         }
         rgb[3 * i] = r; rgb[3 * i + 1] = g; rgb[3 * i + 2] = bl;
@@ -32,9 +33,13 @@ __device__ __forceinline__ uint8_t to_u8(double x) { return (uint8_t)(int)__dmul
 
 __global__ void __launch_bounds__(256)
 lf_depth_overlay_kernel(const double* __restrict__ depth, const double* __restrict__ dmax_p,
-                        const uint8_t* __restrict__ image_rgb, const double* __restrict__ lut, int lut_n, int64_t npix,
-                        uint8_t* __restrict__ out_bgr) {
-    const double dmax = *dmax_p;
+                        const uint8_t* __restrict__ image_rgb, int64_t image_stride, const double* __restrict__ lut,
+                        int lut_n, int64_t npix, uint8_t* __restrict__ out_bgr) {
+    // blockIdx.y = map index
+    depth += (int64_t)blockIdx.y * npix;
+    image_rgb += (int64_t)blockIdx.y * image_stride;
+    out_bgr += (int64_t)blockIdx.y * npix * 3;
+    const double dmax = dmax_p[blockIdx.y];
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (int64_t)gridDim.x * blockDim.x) {
         const double d = depth[i];
         double r, g, b;
@@ -58,8 +63,8 @@ lf_depth_overlay_kernel(const double* __restrict__ depth, const double* __restri
 }  // namespace
 
 extern "C" int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits, int64_t n, const double* colors_rgb, int m,
-                               const double bg_rgb[3], double* rgb, uint8_t* assigned, void* stream) {
-    if (!ctx || n < 0 || m < 0 || m > LF_MAX_CARS) return LF_E_ARG;
+                               const double bg_rgb[3], double* rgb, uint8_t* assigned, int policy, void* stream) {
+    if (!ctx || n < 0 || m < 0 || m > LF_MAX_CARS || policy < 0 || policy > 1) return LF_E_ARG;
     if (n == 0) return LF_OK;
     if (!car_bits || !rgb || !bg_rgb || (m > 0 && !colors_rgb)) return LF_E_ARG;
     LF_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -67,7 +72,24 @@ extern "C" int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits, int64_t n,
     const int64_t cap = (int64_t)ctx->sm_count * 16;
     if (blocks > cap) blocks = cap;
     lf_point_colors_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
-        (const unsigned long long*)car_bits, n, colors_rgb, m, bg_rgb[0], bg_rgb[1], bg_rgb[2], rgb, assigned);
+        (const unsigned long long*)car_bits, n, colors_rgb, m, bg_rgb[0], bg_rgb[1], bg_rgb[2], rgb, assigned, policy);
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}
+
+extern "C" int lf_depth_overlay_batch(lf_ctx* ctx, const double* depth_maps, const double* depth_max,
+                                      const uint8_t* image_rgb, int64_t image_stride, const double* lut_rgb,
+                                      int lut_n, int n, int H, int W, uint8_t* out_bgr, void* stream) {
+    if (!ctx || H <= 0 || W <= 0 || lut_n <= 0 || n < 0 || n > 65535 || image_stride < 0) return LF_E_ARG;
+    if (n == 0) return LF_OK;
+    if (!depth_maps || !depth_max || !image_rgb || !lut_rgb || !out_bgr) return LF_E_ARG;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t npix = (int64_t)H * W;
+    int64_t blocks = (npix + 255) / 256;
+    const int64_t cap = ((int64_t)ctx->sm_count * 16 + n - 1) / n;
+    if (blocks > cap) blocks = cap < 1 ? 1 : cap;
+    lf_depth_overlay_kernel<<<dim3((unsigned)blocks, (unsigned)n), 256, 0, (cudaStream_t)stream>>>(
+        depth_maps, depth_max, image_rgb, image_stride, lut_rgb, lut_n, npix, out_bgr);
     LF_CUDA(ctx, cudaGetLastError());
     return LF_OK;
 }
@@ -75,15 +97,5 @@ extern "C" int lf_point_colors(lf_ctx* ctx, const uint64_t* car_bits, int64_t n,
 extern "C" int lf_depth_overlay(lf_ctx* ctx, const double* depth_map, const double* depth_max,
                                 const uint8_t* image_rgb, const double* lut_rgb, int lut_n, int H, int W,
                                 uint8_t* out_bgr, void* stream) {
-    if (!ctx || H <= 0 || W <= 0 || lut_n <= 0) return LF_E_ARG;
-    if (!depth_map || !depth_max || !image_rgb || !lut_rgb || !out_bgr) return LF_E_ARG;
-    LF_CUDA(ctx, cudaSetDevice(ctx->device));
-    const int64_t npix = (int64_t)H * W;
-    int64_t blocks = (npix + 255) / 256;
-    const int64_t cap = (int64_t)ctx->sm_count * 16;
-    if (blocks > cap) blocks = cap;
-    lf_depth_overlay_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(depth_map, depth_max, image_rgb,
-                                                                              lut_rgb, lut_n, npix, out_bgr);
-    LF_CUDA(ctx, cudaGetLastError());
-    return LF_OK;
+    return lf_depth_overlay_batch(ctx, depth_map, depth_max, image_rgb, 0, lut_rgb, lut_n, 1, H, W, out_bgr, stream);
 }

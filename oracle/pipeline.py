@@ -509,6 +509,46 @@ def colored_cloud_reference(points_valid, u_valid, v_valid, masks, colors, camer
     return clouds, bg_assigned
 
 
+def same_color_reference(points, u, v, depth, masks, mask_colors, camera, max_depth=30):
+    """The per-point loop of Same_color.py:106-132 (inline in projectVeloToImage, so restated):
+    for every valid point in index order the FIRST mask with ``mask[y, x] > 0.5`` gives the colour
+    ``mask_colors[i] / 255`` (stored order, no BGR swap); points no mask claims are background.
+    -> (colored_points [n,3], colored_colors [n,3], full_points [k,3]) as the script builds them."""
+    valid = (u >= 0) & (u < camera.width) & (v >= 0) & (v < camera.height) & (depth > 0) & (depth < max_depth)
+    colored_points, colored_colors, full_points = [], [], []
+    for idx in np.where(valid)[0]:
+        x, y = u[idx], v[idx]
+        pt = points[idx, :3]
+        matched = False
+        for i, mask in enumerate(masks):
+            if y < mask.shape[0] and x < mask.shape[1] and mask[y, x] > 0.5:
+                colored_points.append(pt)
+                colored_colors.append(np.array(mask_colors[i]) / 255.0)
+                matched = True
+                break
+        if not matched:
+            full_points.append(pt)
+    return (np.array(colored_points).reshape(-1, 3), np.array(colored_colors).reshape(-1, 3),
+            np.array(full_points).reshape(-1, 3))
+
+
+def vis_cloud_reference(points_valid, u_valid, v_valid, masks, mask_colors, camera):
+    """vis.py:175-205 (inline, restated): per mask the indices with ``mask[vv, uu] > 0.5`` found by
+    a Python loop over the valid points, colour ``[c[2], c[1], c[0]] / 255``; ``bg_assigned``.
+    -> ([(indices, rgb)] per mask with points, bg_assigned)."""
+    clouds = []
+    bg_assigned = np.zeros(len(points_valid), dtype=bool)
+    for mask, color in zip(masks, mask_colors):
+        normalized_color = np.array([color[2], color[1], color[0]], dtype=float) / 255.0
+        idxs = [i for i, (uu, vv) in enumerate(zip(u_valid, v_valid))
+                if 0 <= uu < camera.width and 0 <= vv < camera.height and mask[vv, uu] > 0.5]
+        idxs = np.array(idxs, dtype=np.int64)
+        if len(idxs) > 0:
+            clouds.append((idxs, normalized_color))
+            bg_assigned[idxs] = True
+    return clouds, bg_assigned
+
+
 def jet_lut_restated(N=256):
     """matplotlib's 'jet' (``_cm._jet_data`` through ``colors._create_lookup_table``,
     gamma 1).  matplotlib is absent from this image: PARITY UNPINNED for these values."""

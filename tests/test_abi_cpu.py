@@ -144,7 +144,7 @@ def test_argument_checks_need_no_device(lib):
                                 *([None] * 9)) == _abi.LF_E_ARG
     assert lib.lf_resize_masks(None, None, 1, 4, 4, None, 8, 8, None) == _abi.LF_E_ARG
     assert lib.lf_project_boxes(None, None, 1, 0.1, 100.0, 4, None, None, None, None, None) == _abi.LF_E_ARG
-    assert lib.lf_point_colors(None, None, 1, None, 1, None, None, None, None) == _abi.LF_E_ARG
+    assert lib.lf_point_colors(None, None, 1, None, 1, None, None, None, 0, None) == _abi.LF_E_ARG
     assert lib.lf_format_csv_rows(None, None, None, None, None, -1, b't', 0, None, 0) == _abi.LF_E_ARG
     assert lib.lf_format_csv_rows(None, None, None, None, None, 0, b't', 1, None, 0) == \
         len('frame,car_id,matched_bbox_id,total_points,points_inside_bbox,points_outside_bbox,'

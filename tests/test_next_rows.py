@@ -239,6 +239,44 @@ def test_device_point_colours_match_the_v4_v5_loop():
 
 
 @pytest.mark.gpu
+def test_device_point_colours_match_the_same_color_and_vis_loops():
+    """Same_color.py:106-132 (first matching mask wins, colour in stored order) and vis.py:175-205
+    (one cloud per mask, BGR -> RGB, bg_assigned): the scripts' per-point Python loops, restated in
+    the oracle, against lf_point_colors with policy first / last."""
+    from conftest import load_frame, standin
+    from lidar_object_detection_b200 import colour as C, kitti360 as K, lidarfuse as LF
+    from oracle import pipeline as P
+    camera, TVC, TVR = K.calibration_chain(SAMPLE)
+    for fr in (100, 2098):
+        pts = load_frame(fr)
+        masks = standin(fr, camera)[0].astype(np.float32)
+        masks[1:] = np.maximum(masks[1:], masks[:-1] * (np.arange(masks.shape[2]) % 3 == 0))   # overlaps between masks
+        colors = [(int(i * 60) % 255, int(i * 120 + 7) % 255, int(i * 180 + 3) % 255) for i in range(len(masks))]
+        u, v, d = P.project_points(pts, TVR, camera)
+        cp, cc, fp = P.same_color_reference(pts, u, v, d, masks, colors, camera)
+        pv, rgb = C.colored_points(pts, TVR, masks, colors, camera, max_depth=30, policy='first', swap_bgr=False)
+        car = np.any(rgb != 0.5, axis=1)
+        bits = LF.mask_membership(*[a[P.filter_valid(u, v, d, camera, 30)] for a in (u, v)], masks, camera)
+        car = (bits.cpu().numpy() if hasattr(bits, 'cpu') else np.asarray(bits)) != 0   # a grey car colour would not show in rgb
+        assert np.array_equal(pv[car], cp) and np.array_equal(rgb[car], cc), fr
+        assert np.array_equal(pv[~car], fp) and np.all(rgb[~car] == 0.5)
+        assert len(cp) > 50
+        # vis.py: last cloud drawn wins, colours swapped to RGB
+        valid = P.filter_valid(u, v, d, camera, 30)
+        clouds, assigned = P.vis_cloud_reference(pts[valid, :3], u[valid], v[valid], masks, colors, camera)
+        expect = np.full((int(valid.sum()), 3), 0.5)
+        for idxs, col in clouds:
+            expect[idxs] = col
+        pv2, rgb2 = C.colored_points(pts, TVR, masks, colors, camera, max_depth=30)
+        assert np.array_equal(rgb2, expect) and np.array_equal(assigned, car)
+        # where masks overlap the two policies must differ
+        assert np.any(np.any(rgb2 != C.colored_points(pts, TVR, masks, colors, camera, max_depth=30, policy='first')[1],
+                             axis=1))
+    with pytest.raises(ValueError):
+        C.point_colors(np.zeros(3, np.int64), [(1, 2, 3)], policy='nearest')
+
+
+@pytest.mark.gpu
 def test_device_depth_overlay_matches_numpy(golden_arrays):
     from conftest import load_frame, standin
     from lidar_object_detection_b200 import colour as C, kitti360 as K, lidarfuse as LF
@@ -259,6 +297,22 @@ def test_device_depth_overlay_matches_numpy(golden_arrays):
         assert got.dtype == np.uint8 and np.array_equal(got, want)
         n += 1
     assert n >= 3
+    # all cars in one launch (shared image), and a batch with one image per map; an empty map gives the image
+    stack = np.stack([np.asarray(dm) for _, dm in maps] + [np.zeros_like(np.asarray(maps[0][1]))])
+    got = C.depth_overlays(stack, image)
+    for i, dm in enumerate(stack):
+        if dm.max() > 0:
+            assert np.array_equal(got[i], P.depth_overlay_reference(dm.copy(), image, P.jet_lut_restated())), i
+        else:
+            assert np.array_equal(got[i], image[:, :, ::-1])          # np.uint8(x / 255 * 255) round trip, RGB -> BGR
+    images = np.stack([np.roll(image, 7 * i, axis=1) for i in range(len(stack))])
+    got = C.depth_overlays(stack, images)
+    for i, dm in enumerate(stack):
+        if dm.max() > 0:
+            assert np.array_equal(got[i], P.depth_overlay_reference(dm.copy(), images[i], P.jet_lut_restated())), i
+    assert C.depth_overlays(stack[:0], image).shape == (0,) + image.shape
+    with pytest.raises(ValueError):
+        C.depth_overlays(stack, image[:-1])
 
 
 # ------------------------------------------------------------------ rank 4 (I/O formats)
