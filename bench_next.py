@@ -68,6 +68,16 @@ def main():
         timed(lambda: check(ctx.lib.lf_resize_masks(ctx.h, ptr(src), m, h, w, ptr(dst), H, W, st), ctx.h),
               m * (h * w + H * W), 'lf_resize_masks', '%d masks, %s' % (m, label))
         del src, dst
+    # the same resize from packed words to packed words (what the batch path does for low-resolution masks)
+    for (h, w), label in (((192, 704), '192x704 -> 376x1408'), ((752, 2816), '752x2816 -> 376x1408 (2x reduction)')):
+        m = M if h < H else M // 8
+        srcw = torch.zeros((m, h, (w + 31) // 32), dtype=torch.int32, device=dev)
+        srcw[:, h // 4:h // 2, 3:9] = -1                     # one blob per mask, like an instance mask
+        dstw = torch.empty((m, H, (W + 31) // 32), dtype=torch.int32, device=dev)
+        bbr = torch.zeros((m, 4), dtype=torch.int32, device=dev)
+        timed(lambda: check(ctx.lib.lf_resize_pack(ctx.h, ptr(srcw), m, h, w, ptr(dstw), ptr(bbr), H, W, st), ctx.h),
+              (srcw.numel() + dstw.numel()) * 4, 'lf_resize_pack', '%d packed masks, %s' % (m, label))
+        del srcw, dstw
     # the reference's own mask format: float32 0.0 / 1.0 masks through lf_erode_pack (bulk-copy fast path)
     mf = 2048
     f32 = torch.zeros((mf, H, W), dtype=torch.float32, device=dev)

@@ -218,6 +218,14 @@ int lf_depth_maps(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, do
 int lf_resize_masks(lf_ctx* ctx, const uint8_t* src /*DEVICE*/, int64_t m, int h, int w, uint8_t* dst /*DEVICE*/,
                     int H, int W, void* stream);
 
+/* The same resize for masks that are bit-packed already (0/1 images, e.g. the result of
+ * lf_erode_pack at the masks' own resolution): src uint32 [m][h][ceil(w/32)] ->
+ * dst uint32 [m][H][ceil(W/32)] with dst bit = (cv2.resize(src01, (W, H)) != 0), i.e. exactly what
+ * the gather reads after cvs_erosion.py:153-154; bbox (optional, zeroed by the caller) as
+ * lf_erode_pack writes it.  1/8 of the bytes of lf_resize_masks and no work for empty regions. */
+int lf_resize_pack(lf_ctx* ctx, const uint32_t* src /*DEVICE*/, int64_t m, int h, int w, uint32_t* dst /*DEVICE*/,
+                   int32_t* bbox /*DEVICE [m][4] or NULL*/, int H, int W, void* stream);
+
 /* ---- next rows: box projection and 2D matching matrices ---------- */
 
 #define LF_VIEW_VALID           0   /* secondtest.py:350 'valid' */

@@ -13,6 +13,7 @@
 // Every float / double step is spelled with round-to-nearest intrinsics so that nothing is
 // contracted into an fma the CPU code does not have.
 #include "common.cuh"
+#include "erode_body.cuh"
 
 namespace {
 
@@ -158,6 +159,165 @@ lf_resize_half_kernel(const uint8_t* __restrict__ src, int64_t m, int H, int W, 
     }
 }
 
+
+// ---------------------------------------------------------------------------
+// Bit-packed masks in, bit-packed "resized != 0" out (what the gather reads after
+// cv2.resize(mask.astype(np.uint8), (W, H)) ... > 0.5, cvs_erosion.py:153-154).  For a 0/1 image
+// the row value a = S0*c0 + S1*c1 takes one of four values per column, so the column table holds
+// (a >> 4) for the three non-zero patterns; an output pixel is set iff
+//     ((b0 * At) >> 16) + ((b1 * Ab) >> 16) >= 2        (the "+ 2 >> 2" of the uint8 formula).
+// One thread = one output word.  Instance masks are mostly background: when the source span of the
+// word is empty in both rows the word is zero without looking at a single tap.
+constexpr int RP_ROWS = 64;                               // output rows per work item (one image)
+
+__global__ void __launch_bounds__(256)
+lf_resize_pack_kernel(const uint32_t* __restrict__ src, int64_t m, int h, int w, int wpr_s, uint32_t* __restrict__ dst,
+                      int32_t* __restrict__ bbox, int H, int W, int wpr_d, double scale_x, double scale_y) {
+    extern __shared__ int2 rp_taps[];                       // per output column {s0, d | A(s0 only) << 1 | A(s1 only) << 9 | A(both) << 17}
+    __shared__ int4 s_row[RP_ROWS];                         // per output row of the item {s0, s1, b0, b1}
+    for (int dx = threadIdx.x; dx < W; dx += blockDim.x) {
+        const Tap t = tap(dx, scale_x, w, true);
+        rp_taps[dx] = make_int2(t.s0, (int)((unsigned)(t.s1 - t.s0) | ((unsigned)(t.c0 >> 4) << 1) |
+                                            ((unsigned)(t.c1 >> 4) << 9) | ((unsigned)((t.c0 + t.c1) >> 4) << 17)));
+    }
+    const unsigned blocks_per_img = (unsigned)((H + RP_ROWS - 1) / RP_ROWS);
+    const unsigned items = (unsigned)m * blocks_per_img;    // < 2^31 (lf_resize_pack)
+    for (unsigned it = blockIdx.x; it < items; it += gridDim.x) {
+        const unsigned img32 = it / blocks_per_img;
+        const int64_t img = img32;
+        const int y0 = (int)(it - img32 * blocks_per_img) * RP_ROWS;
+        const int ny = min(RP_ROWS, H - y0);
+        __syncthreads();                                    // taps ready / previous item's rows consumed
+        if (threadIdx.x < ny) {
+            const Tap ty = tap(y0 + threadIdx.x, scale_y, h, false);
+            s_row[threadIdx.x] = make_int4(ty.s0, ty.s1, ty.c0, ty.c1);
+        }
+        __syncthreads();
+        BBoxAcc acc;
+        const uint32_t* ibase = src + img * h * (int64_t)wpr_s;
+        uint32_t* obase = dst + (img * H + y0) * (int64_t)wpr_d;
+        const int lane = threadIdx.x & 31;
+        // thread = (word column, row group): everything that depends on the column only -- the span of
+        // source columns, its first / last word and their masks -- is computed once per item, the row
+        // loop then costs the loads, two ANDs / ORs and the store.  Loops are warp-uniform (ballots).
+        const int cols = min(wpr_d, (int)blockDim.x), rgroups = (int)blockDim.x / cols;
+        const int my_col = (int)threadIdx.x % cols, my_rg = (int)threadIdx.x / cols;
+        for (int wx0 = 0; wx0 < wpr_d; wx0 += cols) {
+            const int wx = wx0 + my_col;
+            const bool col_ok = wx < wpr_d && my_rg < rgroups;
+            int dx0 = 0, npx = 0, sa = 0, sb = 0, wa = 0, wb = 0;
+            uint32_t keep_a = 0, keep_b = 0;
+            if (col_ok) {
+                dx0 = 32 * wx;
+                npx = min(32, W - dx0);
+                const int2 tf = rp_taps[dx0], tl = rp_taps[dx0 + npx - 1];
+                sa = tf.x; sb = tl.x + (tl.y & 1);            // source columns the word can touch (taps are monotonic)
+                wa = sa >> 5; wb = sb >> 5;
+                keep_a = 0xFFFFFFFFu << (sa & 31);
+                keep_b = 0xFFFFFFFFu >> (31 - (sb & 31));
+                if (wa == wb) { keep_a &= keep_b; keep_b = 0u; }
+            }
+            const uint32_t ones = npx == 32 ? 0xFFFFFFFFu : (1u << npx) - 1u;
+            for (int rb = 0; rb < ny; rb += rgroups) {
+                const int ry = rb + my_rg;
+                const bool active = col_ok && ry < ny;
+                int off0 = 0, off1 = 0, b0 = 0, b1 = 0;
+                uint32_t out = 0;
+                bool mixed = false;
+                if (active) {
+                    const int4 rw = s_row[ry];
+                    off0 = rw.x * wpr_s; off1 = rw.y * wpr_s; b0 = rw.z; b1 = rw.w;
+                    uint32_t any, all;
+                    {
+                        const uint32_t v0 = __ldg(ibase + off0 + wa), v1 = __ldg(ibase + off1 + wa);
+                        any = (v0 | v1) & keep_a;
+                        all = (v0 & v1) | ~keep_a;
+                    }
+                    if (wb > wa) {
+                        const uint32_t v0 = __ldg(ibase + off0 + wb), v1 = __ldg(ibase + off1 + wb);
+                        any |= (v0 | v1) & keep_b;
+                        all &= (v0 & v1) | ~keep_b;
+                        for (int q = wa + 1; q < wb; ++q) {   // shrinking by more than 2: whole words in between
+                            const uint32_t u0 = __ldg(ibase + off0 + q), u1 = __ldg(ibase + off1 + q);
+                            any |= u0 | u1;
+                            all &= u0 & u1;
+                        }
+                    }
+                    // nothing set in the span: 0.  Everything set: every pixel has At = Ab = (c0 + c1) >> 4 >= 127
+                    // and b0 + b1 >= 2047, so floor(b0 * At / 65536) + floor(b1 * Ab / 65536) >= 3 - 1 = 2: all ones.
+                    if (any == 0u) out = 0u;
+                    else if (all == 0xFFFFFFFFu) out = ones;
+                    else mixed = true;
+                }
+                // words with an edge inside: the warp does them together, one pixel per lane
+                unsigned mm = __ballot_sync(0xFFFFFFFFu, mixed);
+                while (mm) {
+                    const int k = __ffs((int)mm) - 1;
+                    mm &= mm - 1;
+                    const int k0 = __shfl_sync(0xFFFFFFFFu, off0, k), k1 = __shfl_sync(0xFFFFFFFFu, off1, k);
+                    const int kb0 = __shfl_sync(0xFFFFFFFFu, b0, k), kb1 = __shfl_sync(0xFFFFFFFFu, b1, k);
+                    const int kdx = __shfl_sync(0xFFFFFFFFu, dx0, k), kn = __shfl_sync(0xFFFFFFFFu, npx, k);
+                    bool bit = false;
+                    if (lane < kn) {
+                        const int2 t = rp_taps[kdx + lane];
+                        const int s0 = t.x, s1 = t.x + (t.y & 1);
+                        const unsigned pt = ((__ldg(ibase + k0 + (s0 >> 5)) >> (s0 & 31)) & 1u) |
+                                            (((__ldg(ibase + k0 + (s1 >> 5)) >> (s1 & 31)) & 1u) << 1);
+                        const unsigned pb = ((__ldg(ibase + k1 + (s0 >> 5)) >> (s0 & 31)) & 1u) |
+                                            (((__ldg(ibase + k1 + (s1 >> 5)) >> (s1 & 31)) & 1u) << 1);
+                        const int At = pt ? ((unsigned)t.y >> (8 * pt - 7)) & 0xFF : 0;
+                        const int Ab = pb ? ((unsigned)t.y >> (8 * pb - 7)) & 0xFF : 0;
+                        bit = (((kb0 * At) >> 16) + ((kb1 * Ab) >> 16)) >= 2;
+                    }
+                    const unsigned w = __ballot_sync(0xFFFFFFFFu, bit);
+                    if (lane == k) out = w;
+                }
+                if (active) {
+                    obase[ry * wpr_d + wx] = out;
+                    acc.add(out, y0 + ry, wx);
+                }
+            }
+        }
+        if (bbox) acc.flush(bbox + 4 * img);
+    }
+}
+
+// keep the even bits of x (bit 2j -> bit j)
+__device__ __forceinline__ uint32_t even_bits(unsigned long long x) {
+    x &= 0x5555555555555555ULL;
+    x = (x | (x >> 1)) & 0x3333333333333333ULL;
+    x = (x | (x >> 2)) & 0x0F0F0F0F0F0F0F0FULL;
+    x = (x | (x >> 4)) & 0x00FF00FF00FF00FFULL;
+    x = (x | (x >> 8)) & 0x0000FFFF0000FFFFULL;
+    x = (x | (x >> 16)) & 0x00000000FFFFFFFFULL;
+    return (uint32_t)x;
+}
+
+// exact 2x reduction: OpenCV's INTER_AREA substitute, (sum of 2x2 + 2) >> 2 != 0 <=> at least two of the four set
+__global__ void __launch_bounds__(256)
+lf_resize_pack_half_kernel(const uint32_t* __restrict__ src, int64_t m, int wpr_s, uint32_t* __restrict__ dst,
+                           int32_t* __restrict__ bbox, int H, int W, int wpr_d) {
+    const int64_t rows = m * (int64_t)H;
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int64_t img = row / H;
+        const int dy = (int)(row - img * H);
+        const uint32_t* r0 = src + (img * 2 * H + 2 * dy) * (int64_t)wpr_s;
+        const uint32_t* r1 = r0 + wpr_s;
+        BBoxAcc acc;
+        for (int wx = threadIdx.x; wx < wpr_d; wx += blockDim.x) {
+            const int q = 2 * wx;
+            const unsigned long long a = (unsigned long long)__ldg(r0 + q) | ((q + 1 < wpr_s ? (unsigned long long)__ldg(r0 + q + 1) : 0ULL) << 32);
+            const unsigned long long b = (unsigned long long)__ldg(r1 + q) | ((q + 1 < wpr_s ? (unsigned long long)__ldg(r1 + q + 1) : 0ULL) << 32);
+            const unsigned long long a1 = a >> 1, b1 = b >> 1;
+            uint32_t out = even_bits((a & a1) | (b & b1) | ((a | a1) & (b | b1)));
+            if (32 * wx + 32 > W) out &= (1u << (W & 31)) - 1u;
+            dst[row * wpr_d + wx] = out;
+            acc.add(out, dy, wx);
+        }
+        if (bbox) acc.flush(bbox + 4 * img);
+    }
+}
+
 }  // namespace
 
 extern "C" int lf_resize_masks(lf_ctx* ctx, const uint8_t* src, int64_t m, int h, int w, uint8_t* dst, int H, int W,
@@ -200,6 +360,36 @@ extern "C" int lf_resize_masks(lf_ctx* ctx, const uint8_t* src, int64_t m, int h
                                               (int)smem));
             lf_resize_linear_kernel<<<(unsigned)blocks, 256, smem, st>>>(src, m, h, w, dst, H, W, scale_x, scale_y);
         }
+    }
+    LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}
+
+extern "C" int lf_resize_pack(lf_ctx* ctx, const uint32_t* src, int64_t m, int h, int w, uint32_t* dst, int32_t* bbox,
+                              int H, int W, void* stream) {
+    if (!ctx || m < 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0) return LF_E_ARG;
+    if (m == 0) return LF_OK;
+    if (!src || !dst || (const void*)src == (const void*)dst) return LF_E_ARG;
+    if ((int64_t)h * w >= ((int64_t)1 << 31) || (int64_t)H * W >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int wpr_s = (w + 31) / 32, wpr_d = (W + 31) / 32;
+    if (w == 2 * W && h == 2 * H) {
+        int64_t blocks = m * H;
+        const int64_t cap = (int64_t)ctx->sm_count * 16;
+        if (blocks > cap) blocks = cap;
+        lf_resize_pack_half_kernel<<<(unsigned)blocks, wpr_d >= 128 ? 256 : 64, 0, st>>>(src, m, wpr_s, dst, bbox, H, W, wpr_d);
+    } else {
+        const double scale_x = 1.0 / ((double)W / (double)w), scale_y = 1.0 / ((double)H / (double)h);
+        const size_t smem = (size_t)W * sizeof(int2);
+        if (smem > 96 * 1024 || (int64_t)RP_ROWS * wpr_d >= 65536) return LF_E_UNSUPPORTED;
+        if (m * ((H + RP_ROWS - 1) / RP_ROWS) >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
+        int64_t blocks = m * ((H + RP_ROWS - 1) / RP_ROWS);
+        const int64_t cap = (int64_t)ctx->sm_count * 8;
+        if (blocks > cap) blocks = cap;
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_resize_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        lf_resize_pack_kernel<<<(unsigned)blocks, 256, smem, st>>>(src, m, h, w, wpr_s, dst, bbox, H, W, wpr_d, scale_x,
+                                                                  scale_y);
     }
     LF_CUDA(ctx, cudaGetLastError());
     return LF_OK;

@@ -268,15 +268,28 @@ def resize_masks(masks, size, device=None):
     return out.cpu().numpy() if was_np else out
 
 
+def resize_pack(pm, size, device=None, out=None, bbox=None):
+    """``PackedMasks`` at any resolution -> ``PackedMasks`` at ``size`` (camera or (W, H)) whose bits are
+    ``cv2.resize(mask01, (W, H)) != 0``: the resize of cvs_erosion.py:153 followed by its ``> 0.5``,
+    straight from packed words to packed words (``lf_resize_pack``).  ``out`` / ``bbox``: optional
+    preallocated destination words [M,H,ceil(W/32)] and zeroed bbox records [M,4]."""
+    ctx = get_ctx(device)
+    W, H = (size.width, size.height) if hasattr(size, 'width') else (int(size[0]), int(size[1]))
+    M = len(pm)
+    words = out if out is not None else torch.empty((M, H, (W + 31) // 32), dtype=torch.int32, device=ctx.device)
+    bb = bbox if bbox is not None else torch.zeros((M, 4), dtype=torch.int32, device=ctx.device)
+    check(ctx.lib.lf_resize_pack(ctx.h, ptr(pm.words), M, pm.H, pm.W, ptr(words), ptr(bb), H, W, ctx.stream), ctx.h)
+    return PackedMasks(words, H, W, bb)
+
+
 def _as_packed(masks, camera, ctx, float_threshold='ge_one'):
     if isinstance(masks, PackedMasks):
         pm = masks
         if pm.raw:
             pm = PackedMasks(pm.words, pm.H, pm.W)       # used as they are: no erosion asked for here
         if len(pm) and (pm.H != camera.height or pm.W != camera.width):
-            masks = pm.unpack(ctx)                       # 0/1 bytes at the masks' own resolution
-        else:
-            return pm
+            return resize_pack(pm, camera, device=ctx.device)
+        return pm
     if isinstance(masks, (list, tuple)):
         masks = np.stack(masks) if len(masks) else np.zeros((0, camera.height, camera.width), np.uint8)
     shape = tuple(masks.shape[1:]) if len(masks) else (camera.height, camera.width)
@@ -597,7 +610,8 @@ class FrameBatch:
                 # masks below camera resolution (YOLO without retina_masks): eroded where they
                 # are, THEN resized, as cvs_erosion.py:96-106 / :153 do -- see run()
                 self._native = self.masks
-                self.masks = torch.empty((n_m, H, W), dtype=torch.uint8, device=ctx.device)
+                h, w = self.masks.shape[1:]
+                self._native_words = torch.empty((n_m, h, (w + 31) // 32), dtype=torch.int32, device=ctx.device)
             self.packed = PackedMasks(torch.empty((n_m, H, (W + 31) // 32), dtype=torch.int32,
                                                   device=ctx.device), H, W)
         self.launches_per_run = 0
@@ -624,13 +638,19 @@ class FrameBatch:
         raw = self.masks is not None and len(self.masks) > 0 and (not pre or self.masks.raw)
         iters, se, mode, mt = 0, None, 0, None
         if raw and getattr(self, '_native', None) is not None:
-            # erode at the masks' own resolution, resize like cv2.resize, pack without erosion
-            # (two extra launches and temporaries: this path is not CUDA-graph capturable)
-            pm = erode_pack(self._native, erosion_kernel_size, erosion_iterations, shape,
-                            float_threshold=float_threshold, device=ctx.device)
-            check(lib.lf_resize_masks(ctx.h, ptr(pm.unpack(ctx)), len(pm), pm.H, pm.W, ptr(self.masks),
-                                      self.camera.height, self.camera.width, st), ctx.h)
-            erosion_kernel_size, erosion_iterations = 0, 0
+            # erode at the masks' own resolution (packed), then cv2.resize + "> 0.5" from packed words
+            # to packed words: two launches, no temporaries
+            nat = self._native.view(torch.uint8) if self._native.dtype == torch.bool else self._native
+            n_it = int(erosion_iterations) if erosion_kernel_size else 0
+            se_n = structuring_element(shape, erosion_kernel_size) if n_it else None
+            h, w = nat.shape[1:]
+            check(lib.lf_erode_pack(ctx.h, ptr(nat), _mask_mode(nat, float_threshold), len(nat), h, w,
+                                    se_n.ctypes.data if n_it else None, se_n.shape[0] if n_it else 1, n_it,
+                                    ptr(self._native_words), None, st), ctx.h)
+            check(lib.lf_resize_pack(ctx.h, ptr(self._native_words), len(nat), h, w, ptr(self.packed.words),
+                                     ptr(self.mask_bbox), self.camera.height, self.camera.width, st), ctx.h)
+            launches += 2
+            raw = False
         if raw:
             iters = int(erosion_iterations) if erosion_kernel_size else 0
             se = structuring_element(shape, erosion_kernel_size) if iters else None
@@ -640,7 +660,7 @@ class FrameBatch:
                 mode = _mask_mode(self.masks, float_threshold)
                 mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
         bbox = self.packed.bbox if pre and not self.masks.raw else self.mask_bbox
-        if persistent and self.car_bits is None:
+        if persistent and self.car_bits is None and getattr(self, '_native', None) is None:
             split = timed and self.F and self.max_n        # time the persistent kernel apart from K6
             check(lib.lf_process_batch(
                 ctx.h, ptr(self.points), ptr(self.pt_off), ptr(mt) if raw else None, mode, len(mt) if raw else 0,
@@ -684,8 +704,6 @@ class FrameBatch:
         caller's stream without allocating or synchronising, so the whole step is capturable;
         worth it for small batches (cfg1: one frame), where launch latency is the step."""
         kwargs.pop('mark', None)
-        if getattr(self, '_native', None) is not None:
-            raise ValueError('low-resolution masks take temporaries in run(): not capturable')
         self.run(*args, **kwargs)                      # warm-up: function attributes, lazy module load
         torch.cuda.synchronize(self.ctx.device)
         g = torch.cuda.CUDAGraph()

@@ -167,6 +167,42 @@ def test_device_resize_is_bit_exact_with_cv2(src):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize('src', [(376, 1408), (192, 704), (752, 2816), (96, 320), (160, 608), (50, 77), (1000, 3000),
+                                 (17, 33), (1, 1)])
+def test_packed_resize_is_bit_exact_with_cv2(src):
+    """lf_resize_pack: packed 0/1 masks -> packed ``cv2.resize(mask01, (W, H)) != 0`` (the resize of
+    cvs_erosion.py:153 and its ``> 0.5``), every branch: identity, the 2x2-average substitution at
+    exactly 2x, enlarging (64-bit window), shrinking by more than 2 (multi-word spans), ragged last
+    words; bounding boxes as lf_erode_pack writes them."""
+    import cv2
+    import torch
+    from lidar_object_detection_b200 import io as IO, lidarfuse as LF
+    rng = np.random.default_rng(src[0] * 31 + src[1])
+    h, w = src
+    imgs = [(rng.random((h, w)) < 0.5).astype(np.uint8), (rng.random((h, w)) < 0.02).astype(np.uint8),
+            np.zeros((h, w), np.uint8), np.ones((h, w), np.uint8), np.zeros((h, w), np.uint8)]
+    cv2.circle(imgs[2], (w // 2, h // 2), max(1, min(h, w) // 3), 1, -1)
+    imgs[4][h // 3:h // 3 + max(1, h // 5), w // 4:w // 4 + max(1, w // 7)] = 1
+    stack = np.stack(imgs)
+    pm = LF.PackedMasks(torch.from_numpy(IO.pack_masks(stack).view(np.int32)).cuda(), h, w)
+    for (W, H) in [(1408, 376), (1000, 123), (33, 17), (w, h), (max(1, w // 2), max(1, h // 2))]:
+        out = LF.resize_pack(pm, (W, H))
+        got = out.unpack().cpu().numpy()
+        bb = out.bbox.cpu().numpy()
+        for i in range(len(imgs)):
+            want = cv2.resize(imgs[i], (W, H)) != 0
+            assert np.array_equal(got[i] != 0, want), (src, (W, H), i)
+            ys, xs = np.nonzero(want)
+            if len(ys) == 0:
+                assert (bb[i] == 0).all()
+            else:
+                assert tuple(bb[i]) == ((1 << 20) - xs.min(), (1 << 20) - ys.min(), xs.max() + 1, ys.max() + 1)
+        # same answer as the uint8 resize followed by the pack
+        ref = LF.erode_pack(LF.resize_masks(torch.from_numpy(stack).cuda(), (W, H)), 0, 0)
+        assert torch.equal(out.words, ref.words)
+
+
+@pytest.mark.gpu
 def test_low_resolution_masks_follow_the_reference_order(cam):
     """Masks below camera resolution: the reference erodes them where they are
     (cvs_erosion.py:96-106) and resizes inside extract_car_points_by_mask (:153).  The
