@@ -67,6 +67,29 @@ void pack_row_f32(const float* src, int W, uint32_t* dst) {
     }
 }
 
+#if defined(__x86_64__)
+template <int MODE>
+__attribute__((target("avx2"))) void pack_row_f32_avx2(const float* src, int W, uint32_t* dst) {
+    const int full = W >> 5;
+    const __m256 thr = _mm256_set1_ps(MODE == 1 ? 1.0f : 0.5f);
+    for (int w = 0; w < full; ++w) {
+        uint32_t acc = 0;
+        for (int g = 0; g < 4; ++g) {
+            const __m256 v = _mm256_loadu_ps(src + 32 * w + 8 * g);
+            // ordered compares: NaN is false, as in the scalar rule
+            const __m256 c = MODE == 1 ? _mm256_cmp_ps(v, thr, _CMP_GE_OQ) : _mm256_cmp_ps(v, thr, _CMP_GT_OQ);
+            acc |= (uint32_t)_mm256_movemask_ps(c) << (8 * g);
+        }
+        dst[w] = acc;
+    }
+    if (W & 31) {
+        uint32_t acc = 0;
+        for (int x = 32 * full; x < W; ++x) acc |= (uint32_t)(MODE == 1 ? (src[x] >= 1.0f) : (src[x] > 0.5f)) << (x & 31);
+        dst[full] = acc;
+    }
+}
+#endif
+
 void pack_rows(const void* masks, int mode, int64_t row0, int64_t row1, int W, uint32_t* packed, bool avx2) {
     const int wpr = (W + 31) >> 5;
     for (int64_t r = row0; r < row1; ++r) {
@@ -77,10 +100,17 @@ void pack_rows(const void* masks, int mode, int64_t row0, int64_t row1, int W, u
             if (avx2) { pack_row_u8_avx2(src, W, dst); continue; }
 #endif
             pack_row_u8(src, W, dst);
-        } else if (mode == 1) {
-            pack_row_f32<1>((const float*)masks + r * W, W, dst);
         } else {
-            pack_row_f32<2>((const float*)masks + r * W, W, dst);
+            const float* src = (const float*)masks + r * W;
+#if defined(__x86_64__)
+            if (avx2) {
+                if (mode == 1) pack_row_f32_avx2<1>(src, W, dst);
+                else pack_row_f32_avx2<2>(src, W, dst);
+                continue;
+            }
+#endif
+            if (mode == 1) pack_row_f32<1>(src, W, dst);
+            else pack_row_f32<2>(src, W, dst);
         }
     }
 }
