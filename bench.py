@@ -487,10 +487,17 @@ def main():
                          'the stand-alone erode / fuse launches')
     args = ap.parse_args()
     set_workload(args.workload, args.frames)
+    # stdout carries the ONE JSON line and nothing else: whatever libraries print while the job runs
+    # (NCCL's version banner goes to stdout when NCCL_DEBUG is set) is sent to stderr at the fd level.
+    sys.stdout.flush()
+    keep = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(keep, 'w')
     if args.impl == 'reference':
         run_reference(args)
     else:
         run_gpu(args)
+    sys.stdout.flush()
 
 
 if __name__ == '__main__':

@@ -116,6 +116,11 @@ int lf_erode_pack(lf_ctx* ctx, const void* masks /*DEVICE [m][H][W], mode 3: [m]
 int lf_pack_masks_host(const void* masks /*HOST [m][H][W]*/, int mode, int64_t m, int H, int W,
                        uint32_t* packed /*HOST [m][H][wpr]*/, int threads);
 
+/* Instruction set lf_pack_masks_host uses: 0 = scalar, 1 = AVX2, 2 = AVX-512BW (detected at
+ * run time).  cap >= 0 lowers the ceiling first (the tests run every path); cap < 0 only
+ * queries.  Returns the level in use. */
+int lf_host_simd(int cap);
+
 /* packed -> uint8 0/1 images (the eroded masks the reference keeps as float32,
  * cvs_erosion.py:103). */
 int lf_unpack_masks(lf_ctx* ctx, const uint32_t* packed /*DEVICE*/, int64_t m, int H, int W,

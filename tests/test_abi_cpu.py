@@ -153,10 +153,22 @@ def test_argument_checks_need_no_device(lib):
 
 
 def test_host_mask_packer_matches_numpy():
-    """lf_pack_masks_host (plain C++, no device): every binarisation rule, ragged widths, threads."""
-    from lidar_object_detection_b200 import io as IO
+    """lf_pack_masks_host (plain C++, no device): every binarisation rule, ragged widths, threads,
+    and every instruction-set path the host offers (scalar, AVX2, AVX-512BW)."""
+    from lidar_object_detection_b200 import _abi, io as IO
+    lib = _abi.load()
+    top = lib.lf_host_simd(2)
+    try:
+        for cap in range(top, -1, -1):
+            assert lib.lf_host_simd(cap) == cap
+            _check_host_packer(IO)
+    finally:
+        lib.lf_host_simd(2)
+
+
+def _check_host_packer(IO):
     rng = np.random.default_rng(5)
-    for W in (1408, 1000, 37, 64, 31):
+    for W in (1408, 1000, 37, 64, 96, 160, 31):
         m = (rng.random((7, 29, W)) < 0.3).astype(np.uint8) * rng.integers(1, 256, (7, 29, W), dtype=np.uint8)
         want = IO.pack_masks_host(m)
         for threads in (1, 3, 0):
