@@ -20,9 +20,68 @@ if ROOT not in sys.path:
 CALIB_ROOT = os.path.join(ROOT, 'tests', 'golden', 'kitti360_sample')
 
 
+def surface_kernels(args, timed, ctx, cam, TVC, TVR, LF, S, check, ptr, torch, np):
+    """The stand-alone kernels behind the reference's one-call-at-a-time function surface (A3 / A4
+    projection + gate, A6 gather, A8 containment, A10 depth maps) on 256 synthetic frames = 33.5 M points
+    (537 MB, larger than L2)."""
+    from lidar_object_detection_b200 import _abi
+    H, W, st, dev = cam.height, cam.width, ctx.stream, ctx.device
+    F = 256
+    sb = S.SyntheticBatch(F, cam, TVC, TVR, ncars=16, device=0)
+    sb.batch.run(3, 0, 50, 10, True)                        # packs the (un-eroded) masks
+    torch.cuda.synchronize()
+    pts, n = sb.points, sb.points.shape[0]
+    u = torch.empty(n, dtype=torch.int64, device=dev)
+    v = torch.empty(n, dtype=torch.int64, device=dev)
+    d = torch.empty(n, dtype=torch.float64, device=dev)
+    pix = torch.empty(n, dtype=torch.int32, device=dev)
+    timed(lambda: check(ctx.lib.lf_project(ctx.h, ptr(pts), n, 50.0, ptr(u), ptr(v), ptr(d), ptr(pix), st), ctx.h),
+          n * (16 + 28), 'lf_project (u, v int64 + depth f64 + gated pixel out)', '%d points' % n)
+    timed(lambda: check(ctx.lib.lf_project(ctx.h, ptr(pts), n, 50.0, None, None, None, ptr(pix), st), ctx.h),
+          n * (16 + 4), 'lf_project (gated pixel index only)', '%d points' % n)
+    words = sb.batch.packed.words
+    bits = torch.empty(n, dtype=torch.int64, device=dev)
+    timed(lambda: check(ctx.lib.lf_mask_gather(ctx.h, ptr(words), 16, H, W, ptr(u), ptr(v), n, ptr(bits), st), ctx.h),
+          n * (16 + 8), 'lf_mask_gather', '%d pixel pairs (int64 u, v) x 16 packed masks -> 64-bit membership' % n)
+    inb = torch.empty(n, dtype=torch.uint8, device=dev)
+    boxes = sb.batch.boxes
+    timed(lambda: check(ctx.lib.lf_points_in_box(ctx.h, ptr(pts), 0, n, 4, ptr(boxes), 1, ptr(inb), st), ctx.h),
+          n * (16 + 1), 'lf_points_in_box (oriented)', '%d float32 points x 1 box -> uint8 flags' % n)
+    sid = (torch.arange(n, device=dev, dtype=torch.int32) & 15)
+    B = int(sb.n_boxes[0])
+    cnt = torch.zeros(16 * max(B, 1), dtype=torch.int32, device=dev)
+    timed(lambda: check(ctx.lib.lf_count_in_boxes(ctx.h, ptr(pts), 0, n, 4, ptr(sid), ptr(boxes), B, 1, ptr(cnt), st),
+                        ctx.h), n * (16 + 4), 'lf_count_in_boxes (oriented)', '%d points x %d boxes, 16 point sets' % (n, B))
+    del u, v, d, pix, bits, inb, sid
+    # A10 depth maps: one frame per call (the reference's loop) and the batch entry point
+    npix = H * W
+    scr = torch.empty(npix, dtype=torch.int64, device=dev)
+    per = torch.empty((16, H, W), dtype=torch.float64, device=dev)
+    n1 = sb.n
+    for pol, name in ((_abi.POLICY_LAST, 'last'), (_abi.POLICY_NEAREST, 'nearest')):
+        timed(lambda: check(ctx.lib.lf_depth_maps(ctx.h, ptr(pts), n1, 30.0, pol, ptr(words), 16, ptr(scr), None, ptr(per),
+                                                  st), ctx.h),
+              n1 * 16 + npix * 8 * 17, 'lf_depth_maps (%s)' % name, 'one frame, %d points, 16 per-car f64 maps' % n1)
+    FB = 64
+    scrb = torch.empty((FB, npix), dtype=torch.int64, device=dev)
+    perb = torch.empty((FB * 16, H, W), dtype=torch.float64, device=dev)
+    fullb = torch.empty((FB, H, W), dtype=torch.float64, device=dev)
+    for pol, name in ((_abi.POLICY_LAST, 'last'), (_abi.POLICY_NEAREST, 'nearest')):
+        timed(lambda: check(ctx.lib.lf_depth_maps_batch(ctx.h, ptr(pts), ptr(sb.batch.pt_off), FB, n1, 30.0, pol, ptr(words),
+                                                        ptr(sb.batch.mask_off), ptr(scrb), ptr(fullb), ptr(perb), st), ctx.h),
+              FB * (n1 * 16 + npix * 8 * (1 + 1 + 1 + 16)), 'lf_depth_maps_batch (%s)' % name,
+              '%d frames in one call: key image cleared + read, frame map + 16 per-car f64 maps each' % FB)
+        timed(lambda: check(ctx.lib.lf_depth_maps_batch(ctx.h, ptr(pts), ptr(sb.batch.pt_off), FB, n1, 30.0, pol, None,
+                                                        None, ptr(scrb), ptr(fullb), None, st), ctx.h),
+              FB * (n1 * 16 + npix * 8 * 3), 'lf_depth_maps_batch (%s, frame maps only)' % name, '%d frames' % FB)
+    del sb, scrb, perb, fullb
+    torch.cuda.empty_cache()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--reps', type=int, default=20)
+    ap.add_argument('--only', default='', help="'surface' = only the stand-alone 8(a) kernels and the depth maps")
     args = ap.parse_args()
     import numpy as np
     import torch
@@ -58,6 +117,9 @@ def main():
         print(json.dumps({'kernel': name, 'ms': med, 'ms_min': ms[0], 'algorithmic_bytes': int(nbytes),
                           'achieved_gbs': gbs, 'peak_gbs': peak, 'frac': gbs / peak, 'note': note}))
 
+    surface_kernels(args, timed, ctx, cam, TVC, TVR, LF, S, check, ptr, torch, np)
+    if args.only == 'surface':
+        return
     # rank 1: resize 16384 half-resolution masks to camera resolution (bilinear), and 2x area
     M = 1024 * 16
     g = torch.Generator(device=dev).manual_seed(1)

@@ -213,6 +213,19 @@ int lf_depth_maps(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, do
                   uint64_t* scratch /*DEVICE*/, double* full /*DEVICE or NULL*/,
                   double* per_car /*DEVICE or NULL*/, void* stream);
 
+/* A10 for a batch of frames: the loop of seg_with_pointcloud.py:153-170 over F frames in
+ * three launches (key images cleared, one atomic per gated point, resolve).  Frames are
+ * CSR-concatenated as in lf_fuse_batch: pt_off DEVICE int64 [F+1], mask_off DEVICE int32
+ * [F+1] (masks of frame f = packed[mask_off[f] .. mask_off[f+1])).  scratch: DEVICE uint64
+ * [F][H*W].  full: optional DEVICE f64 [F][H][W]; per_car: optional DEVICE f64 [sum M][H][W].
+ * Keys of policy `last` are point indices inside the frame, so the result of every frame
+ * is the one lf_depth_maps gives for it alone.  Needs an even image width. */
+int lf_depth_maps_batch(lf_ctx* ctx, const float* pts /*DEVICE [sum N][4]*/, const int64_t* pt_off /*DEVICE*/, int F,
+                        int64_t max_points_per_frame, double max_depth, int policy,
+                        const uint32_t* packed /*DEVICE [sum M][H][wpr] or NULL*/, const int32_t* mask_off /*DEVICE or NULL*/,
+                        uint64_t* scratch /*DEVICE*/, double* full /*DEVICE or NULL*/, double* per_car /*DEVICE or NULL*/,
+                        void* stream);
+
 /* ---- next rows: mask resize to camera resolution ------------------ */
 
 /* cv2.resize(mask.astype(np.uint8), (W, H)) with the default INTER_LINEAR

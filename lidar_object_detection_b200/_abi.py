@@ -54,6 +54,7 @@ SIGNATURES = {
     'lf_car_stats': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     'lf_zero_counters': (C.c_int, [_vp, _vp, _i64, _vp]),
     'lf_depth_maps': (C.c_int, [_vp, _vp, _i64, _f64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    'lf_depth_maps_batch': (C.c_int, [_vp, _vp, _vp, _i32, _i64, _f64, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),
     'lf_resize_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _vp]),
     'lf_resize_pack': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _i32, _i32, _vp]),
     'lf_project_boxes': (C.c_int, [_vp, _vp, _i64, _f64, _f64, _i32, _vp, _vp, _vp, _vp, _vp]),

@@ -126,4 +126,30 @@ __device__ __forceinline__ bool lf_gate(const LfCam& c, double uq, double vq, do
            (depth > 0.0) && (depth < max_depth);
 }
 
+// fp32 look at a point before any fp64 work (SURVEY A4 gate, cvs_erosion.py:359):
+// false only for points that CERTAINLY fail the gate -- behind the camera, beyond
+// the range limit, or more than a pixel outside the image.  The margins (LfCam
+// tX/tY/tD, lf_set_camera) cover the fp32 evaluation error for points within the
+// radius gR; farther points, NaN and inf stay "maybe", so the exact fp64 path decides
+// everything that matters.  Branch-free on purpose.
+struct PreGate {
+    float c[12], hwx, hwy, tX, tY, ntD, dhi, gR;
+    __device__ __forceinline__ PreGate(const LfCam& cam, double max_depth) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) c[i] = cam.Pg[i];
+        hwx = cam.hwx; hwy = cam.hwy; tX = cam.tX; tY = cam.tY; ntD = -cam.tD; gR = cam.gR;
+        float dmax32 = (float)max_depth;
+        dmax32 += fabsf(dmax32) * 1e-6f;                   // the cast may round down
+        dhi = dmax32 + cam.tD;
+    }
+    __device__ __forceinline__ bool maybe(const float4 p) const {
+        const float d = fmaf(c[8], p.x, fmaf(c[9], p.y, fmaf(c[10], p.z, c[11])));
+        const float x = fmaf(c[0], p.x, fmaf(c[1], p.y, fmaf(c[2], p.z, c[3])));
+        const float y = fmaf(c[4], p.x, fmaf(c[5], p.y, fmaf(c[6], p.z, c[7])));
+        const float big = fmaxf(fmaxf(fabsf(p.x), fabsf(p.y)), fabsf(p.z));
+        const bool out = (d < ntD) | (d > dhi) | (fabsf(x) > fmaf(hwx, d, tX)) | (fabsf(y) > fmaf(hwy, d, tY));
+        return !out | !(big <= gR);
+    }
+};
+
 static inline int lf_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

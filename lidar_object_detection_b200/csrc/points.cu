@@ -9,6 +9,8 @@
 
 namespace {
 
+constexpr int LF_COUNT_SMEM_BOXES = 512;              // 96 KB of box records
+
 __device__ __forceinline__ bool lf_slab(double rx, double ry, double rz, const double* e, double ee) {
     double d = __dmul_rn(rx, e[0]);
     d = __fma_rn(ry, e[1], d);
@@ -65,13 +67,22 @@ __global__ void __launch_bounds__(256)
 lf_count_in_boxes_kernel(const T* __restrict__ xyz, int64_t n, int stride_elems,
                          const int32_t* __restrict__ set_id, const lf_box* __restrict__ boxes, int B,
                          int oriented, int32_t* __restrict__ inside) {
+    // boxes staged in shared memory when they fit (they do for every frame of the sample: <= 314)
+    extern __shared__ __align__(16) uint8_t s_raw[];
+    const bool staged = B <= LF_COUNT_SMEM_BOXES;
+    if (staged) {
+        const int nd = B * (int)(sizeof(lf_box) / 8);
+        for (int i = threadIdx.x; i < nd; i += blockDim.x) ((double*)s_raw)[i] = ((const double*)boxes)[i];
+        __syncthreads();
+    }
+    const lf_box* bxs = staged ? (const lf_box*)s_raw : boxes;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const T* p = xyz + i * stride_elems;
         const double X = (double)p[0], Y = (double)p[1], Z = (double)p[2];
         const int s = set_id[i];
         for (int b = 0; b < B; ++b) {
-            const lf_box& bx = boxes[b];
+            const lf_box& bx = bxs[b];
             // float32 early-out only when the coordinates are float32-exact
             if (sizeof(T) == 4 && ((float)X < bx.lo[0] || (float)X > bx.hi[0] || (float)Y < bx.lo[1] ||
                                    (float)Y > bx.hi[1] || (float)Z < bx.lo[2] || (float)Z > bx.hi[2]))
@@ -124,12 +135,18 @@ extern "C" int lf_count_in_boxes(lf_ctx* ctx, const void* xyz, int is_f64, int64
     if (n == 0 || B == 0) return LF_OK;
     if (!xyz || !set_id || !boxes || !inside) return LF_E_ARG;
     LF_CUDA(ctx, cudaSetDevice(ctx->device));
-    if (is_f64)
-        lf_count_in_boxes_kernel<double><<<grid_for(ctx, n), 256, 0, (cudaStream_t)stream>>>(
+    const size_t smem = B <= LF_COUNT_SMEM_BOXES ? (size_t)B * sizeof(lf_box) : 0;
+    if (is_f64) {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_count_in_boxes_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(LF_COUNT_SMEM_BOXES * sizeof(lf_box))));
+        lf_count_in_boxes_kernel<double><<<grid_for(ctx, n), 256, smem, (cudaStream_t)stream>>>(
             (const double*)xyz, n, stride_elems, set_id, boxes, B, use_oriented, inside);
-    else
-        lf_count_in_boxes_kernel<float><<<grid_for(ctx, n), 256, 0, (cudaStream_t)stream>>>(
+    } else {
+        LF_CUDA(ctx, cudaFuncSetAttribute(lf_count_in_boxes_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(LF_COUNT_SMEM_BOXES * sizeof(lf_box))));
+        lf_count_in_boxes_kernel<float><<<grid_for(ctx, n), 256, smem, (cudaStream_t)stream>>>(
             (const float*)xyz, n, stride_elems, set_id, boxes, B, use_oriented, inside);
+    }
     LF_CUDA(ctx, cudaGetLastError());
     return LF_OK;
 }

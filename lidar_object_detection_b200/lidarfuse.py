@@ -851,6 +851,47 @@ def per_car_depth_maps(points, TrVeloToRect, masks, camera, max_depth=30, policy
     return (maps, fl) if full else maps
 
 
+def per_car_depth_maps_batch(points, n_points, masks, n_masks, TrVeloToRect, camera, max_depth=30, policy='last',
+                             full=False, per_car=True, device=None):
+    """``per_car_depth_maps`` for F frames at once (``lf_depth_maps_batch``: three launches for the
+    whole batch instead of three per frame).  points: [sum N,4] (frames concatenated, ``n_points``
+    per frame); masks: [sum M,H,W] or ``PackedMasks`` (``n_masks`` per frame).  Returns a list with
+    one entry per frame, each the [(car_id, depthMap)] list ``per_car_depth_maps`` returns for that
+    frame alone (seg_with_pointcloud.py:153-170); with ``full=True`` also the [F,H,W] frame maps.
+    numpy in -> numpy out, tensors in -> views of one device buffer out."""
+    ctx = get_ctx(device)
+    ctx.set_camera(TrVeloToRect, camera.K, camera.width, camera.height)
+    was_np = _is_np(points)
+    pts = _points4(points, ctx)
+    n_points = [int(x) for x in n_points]
+    n_masks = [int(x) for x in n_masks]
+    F = len(n_points)
+    if len(n_masks) != F or sum(n_points) != pts.shape[0]:
+        raise ValueError('n_points / n_masks must describe the %d concatenated frames' % F)
+    pm = _as_packed(masks, camera, ctx, float_threshold='gt_half')
+    if sum(n_masks) != len(pm):
+        raise ValueError('n_masks must sum to the number of masks')
+    H, W = camera.height, camera.width
+    pt_off = torch.tensor(np.concatenate([[0], np.cumsum(n_points)]), dtype=torch.int64, device=ctx.device)
+    mask_off = torch.tensor(np.concatenate([[0], np.cumsum(n_masks)]), dtype=torch.int32, device=ctx.device)
+    scratch = torch.empty((F, H * W), dtype=torch.int64, device=ctx.device)
+    M = len(pm)
+    per = torch.empty((M, H, W), dtype=torch.float64, device=ctx.device) if (per_car and M) else None
+    fl = torch.empty((F, H, W), dtype=torch.float64, device=ctx.device) if full else None
+    pol = {'last': _abi.POLICY_LAST, 'nearest': _abi.POLICY_NEAREST}[policy]
+    check(ctx.lib.lf_depth_maps_batch(ctx.h, ptr(pts), ptr(pt_off), F, max(n_points) if F else 0, float(max_depth), pol,
+                                      ptr(pm.words) if M else None, ptr(mask_off), ptr(scratch), ptr(fl), ptr(per),
+                                      ctx.stream), ctx.h)
+    out, m0 = [], 0
+    host = per.cpu().numpy() if (was_np and per is not None) else per
+    for f in range(F):
+        out.append([(i + 1, host[m0 + i]) for i in range(n_masks[f])] if host is not None else [])
+        m0 += n_masks[f]
+    if full:
+        return out, (fl.cpu().numpy() if was_np else fl)
+    return out
+
+
 # --------------------------------------------------------------------------
 # A11  CSV (host; byte-compatible with the pandas writer of the reference)
 # --------------------------------------------------------------------------

@@ -92,6 +92,28 @@ def test_projection_special_values(LF, calib, oracle_calib):
     assert all(len(x) == 0 for x in e)
 
 
+def test_pixel_only_projection_equals_the_full_call(LF, calib):
+    """lf_project asked for the gated pixel alone lets the fp32 pre-gate answer for points that
+    certainly fail the gate: the pixel indices must be those of the full fp64 call, on real sweeps
+    (both range limits) and on special values."""
+    import torch
+    from lidar_object_detection_b200._abi import check, ptr
+    cam, TVC, TVR = calib
+    ctx = LF.get_ctx(0)
+    special = np.array([[np.nan, 0, 0, 0], [np.inf, 1, 1, 0], [1e30, -1e30, 5, 0], [0, 0, 0, 0], [3e38, 3e38, 3e38, 0],
+                        [10, 0.5, -0.5, 0.2], [-10, 0.5, -0.5, 0.2], [49.99, 1, 0, 0], [50.3, 1, 0, 0]], np.float32)
+    for fr in (100, 2449):
+        pts = np.concatenate([load_frame(fr), special])
+        for max_depth in (50.0, 30.0, 1e9):
+            _, _, _, want = LF.project_points(pts, TVR, cam, max_depth=max_depth, return_pix=True)
+            t = torch.from_numpy(pts).to(ctx.device)
+            pix = torch.full((len(pts),), 7, dtype=torch.int32, device=ctx.device)
+            check(ctx.lib.lf_project(ctx.h, ptr(t), len(pts), max_depth, None, None, None, ptr(pix), ctx.stream), ctx.h)
+            got = pix.cpu().numpy()
+            assert np.array_equal(got, np.asarray(want)), (fr, max_depth)
+            assert (got >= 0).sum() > 20000
+
+
 # ------------------------------------------------------------------ A5
 
 @pytest.mark.parametrize('W,H', [(1408, 376), (1000, 123), (33, 17), (64, 8), (128, 40), (32, 20), (16, 9)])
@@ -417,6 +439,47 @@ def test_depth_maps_match_reference_and_oracle(LF, calib, golden, golden_arrays)
             assert np.array_equal(dm > 0, maps[car - 1][1] > 0)
     assert checked >= 5
     assert LF.per_car_depth_maps(load_frame(100), TVR, np.zeros((0, cam.height, cam.width), np.float32), cam) == []
+
+
+@pytest.mark.parametrize('policy', ['last', 'nearest'])
+def test_depth_maps_batch_equals_per_frame_and_oracle(LF, calib, golden, policy):
+    """lf_depth_maps_batch over the 20 sample frames in one call (ragged: 0..12 masks per frame, an
+    empty frame in the middle) = the oracle's per-frame maps, bit for bit (seg_with_pointcloud.py:153-170)."""
+    cam, TVC, TVR = calib
+    frames = list(golden['_meta']['frames'])
+    pts, masks, n_pts, n_masks = [], [], [], []
+    for fr in frames:
+        pts.append(load_frame(fr)); masks.append(standin(fr, cam)[0])
+        n_pts.append(len(pts[-1])); n_masks.append(len(masks[-1]))
+    pts.insert(7, np.zeros((0, 4), np.float32)); masks.insert(7, np.zeros((0, cam.height, cam.width), np.float32))
+    n_pts.insert(7, 0); n_masks.insert(7, 0)
+    got, full = LF.per_car_depth_maps_batch(np.concatenate(pts), n_pts, np.concatenate(masks), n_masks, TVR, cam,
+                                            max_depth=30, policy=policy, full=True)
+    assert len(got) == len(n_pts) and full.shape == (len(n_pts), cam.height, cam.width)
+    cars = 0
+    for f in range(len(n_pts)):
+        u, v, d = P.project_points(pts[f], TVR, cam) if n_pts[f] else (np.zeros(0, np.int64),) * 2 + (np.zeros(0),)
+        want = P.per_car_depth_maps(u, v, d, masks[f], cam, max_depth=30, policy=policy)
+        assert [c for c, _ in got[f]] == [c for c, _ in want]
+        for (_, dm), (_, wdm) in zip(got[f], want):
+            assert dm.dtype == np.float64 and np.array_equal(dm, wdm)
+            cars += 1
+        valid = P.filter_valid(u, v, d, cam, 30)
+        ref_full = np.zeros((cam.height, cam.width))
+        if policy == 'last':
+            ref_full[v[valid], u[valid]] = d[valid]
+        else:
+            ref_full[:] = np.inf
+            np.minimum.at(ref_full, (v[valid], u[valid]), d[valid])
+            ref_full[np.isinf(ref_full)] = 0.0
+        assert np.array_equal(full[f], ref_full), f
+    assert cars == sum(n_masks) >= 100
+    # one frame through the batch entry point = the single-frame entry point
+    one = LF.per_car_depth_maps_batch(pts[0], [n_pts[0]], masks[0], [n_masks[0]], TVR, cam, policy=policy)[0]
+    ref = LF.per_car_depth_maps(pts[0], TVR, masks[0], cam, policy=policy)
+    assert all(np.array_equal(a[1], b[1]) for a, b in zip(one, ref)) and len(one) == len(ref)
+    assert LF.per_car_depth_maps_batch(np.zeros((0, 4), np.float32), [], np.zeros((0, cam.height, cam.width), np.uint8),
+                                       [], TVR, cam) == []
 
 
 # ------------------------------------------------------------------ synthetic batches (cfg3-shaped)
