@@ -191,8 +191,23 @@ def run_gpu(args):
     n_pts = sb.n
     exch = None
     if world > 1:
-        exch = D.CounterExchange(world * frames, NCARS, rank, world, dev)
-        exch.bind(batch.h_mask_off, sb.n_boxes)
+        nccl_exch = D.CounterExchange(world * frames, NCARS, rank, world, dev)
+        nccl_exch.bind(batch.h_mask_off, sb.n_boxes)
+        exch, exch_kind = nccl_exch, 'one NCCL all_reduce(SUM) over the zero-filled int64 table per batch'
+        if args.exchange == 'peer' and D.PeerCounterExchange.available():
+            try:
+                exch = D.PeerCounterExchange(world * frames, NCARS, rank, world, dev)
+                exch_kind = 'lf_publish_table: rows stored into every rank\'s table over NVLink peer memory + one ' \
+                            'signal-pad barrier per batch'
+            except Exception as e:                       # no peer access on this box: the NCCL exchange stays
+                sys.stderr.write('peer exchange unavailable (%r), using NCCL\n' % (e,))
+        if exch is not nccl_exch:                        # both exchanges must give the same table
+            batch.run(KSIZE, 1, 50, 10, True)
+            t1, a1 = nccl_exch.exchange_batch(batch)
+            t2, _ = exch.exchange_batch(batch)
+            torch.cuda.synchronize(dev)
+            if not (torch.equal(t1.to(torch.int32), t2) and torch.equal(a1, exch.agg)):
+                raise SystemExit('PARITY FAILURE: peer-store exchange differs from the NCCL all-reduce')
 
     def step(mark=None):
         batch.run(KSIZE, 1, 50, 10, True, mark=mark, persistent=args.persistent)
@@ -426,7 +441,8 @@ def run_gpu(args):
                                                                         NCARS, KSIZE, KSIZE),
                        'frames_per_gpu': frames, 'points_per_frame': n_pts, 'masks_per_frame': NCARS,
                        'l2_policy': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush' % (step_bytes / 1e9),
-                       'parallelism': 'frames sharded, dp%d' % world},
+                       'parallelism': 'frames sharded, dp%d' % world,
+                       'exchange': exch_kind if world > 1 else None},
             'gpu_launches': int(batch.launches_per_run - 1) * K_steps,
             'kernel_ms': kern_ms,
             'step_hbm': {'algorithmic_bytes_per_step': step_bytes, 'achieved_gbs': step_bytes / (ms_step * 1e-3) / 1e9,
@@ -482,6 +498,8 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
     ap.add_argument('--no-packed', action='store_true', help='skip the packed-masks-in secondary measurement')
+    ap.add_argument('--exchange', default='peer', choices=['peer', 'nccl'],
+                    help='N > 1: per-car table exchanged by stores into peer memory (default) or by the NCCL all-reduce')
     ap.add_argument('--persistent', action='store_true',
                     help='one persistent erode+fuse kernel (lf_process_batch with scheduler words) instead of '
                          'the stand-alone erode / fuse launches')

@@ -213,6 +213,22 @@ int lf_depth_maps(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, do
                   uint64_t* scratch /*DEVICE*/, double* full /*DEVICE or NULL*/,
                   double* per_car /*DEVICE or NULL*/, void* stream);
 
+/* 8(e)  the counter exchange between the ranks of one node, as stores into peer memory.
+ * Replaces the table all-reduce of distributed.CounterExchange (zero-filled table, sum over
+ * disjoint supports): each rank writes the rows of ITS frames -- {total_points, best_count,
+ * best_idx + 1, frame has boxes} as int32[4] per (frame, car slot), slots past a frame's
+ * last car zero -- at row0 + f into the table copy of EVERY rank, and its eight aggregates
+ * (lf_car_stats `agg`) into slot `rank` of every copy's int64 [world][8] block.
+ * peers: DEVICE array [world] of the ranks' buffer base addresses, all mapped into this
+ * process (torch symmetric memory `buffer_ptrs_dev`); the table lives table_off_bytes
+ * (16-aligned) and the aggregates agg_off_bytes into each buffer.  The caller orders the
+ * ranks afterwards (one signal-pad barrier) and double-buffers the table between batches. */
+int lf_publish_table(lf_ctx* ctx, const int32_t* total /*DEVICE*/, const int32_t* best_idx /*DEVICE*/,
+                     const int32_t* best_cnt /*DEVICE*/, const int32_t* mask_off /*DEVICE [F+1]*/,
+                     const int32_t* box_off /*DEVICE [F+1]*/, const int64_t* agg /*DEVICE [8] or NULL*/, int F,
+                     int max_cars, int64_t row0, void* const* peers /*DEVICE [world]*/, int world, int rank,
+                     int64_t table_off_bytes, int64_t agg_off_bytes, void* stream);
+
 /* A10 for a batch of frames: the loop of seg_with_pointcloud.py:153-170 over F frames in
  * three launches (key images cleared, one atomic per gated point, resolve).  Frames are
  * CSR-concatenated as in lf_fuse_batch: pt_off DEVICE int64 [F+1], mask_off DEVICE int32

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, '_lib', 'liblidarfuse.so')
+LIB_PATH = os.environ.get('LIDARFUSE_LIB') or os.path.join(HERE, '_lib', 'liblidarfuse.so')   # override: kernel experiments
 
 LF_OK, LF_E_ARG, LF_E_CUDA, LF_E_UNSUPPORTED, LF_E_NOCAMERA = 0, -1, -2, -3, -4
 POLICY_NEAREST, POLICY_LAST = 0, 1
@@ -42,6 +42,8 @@ SIGNATURES = {
     'lf_unpack_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     'lf_pack_masks_host': (C.c_int, [_vp, _i32, _i64, _i32, _i32, _vp, _i32]),
     'lf_host_simd': (C.c_int, [_i32]),
+    'lf_publish_table': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i64, _vp, _i32, _i32, _i64, _i64,
+                                   _vp]),
     'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
     'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp]),

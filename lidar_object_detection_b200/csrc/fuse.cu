@@ -13,7 +13,7 @@
 
 namespace {
 
-__global__ void __launch_bounds__(FUSE_THREADS, 5)
+__global__ void __launch_bounds__(FUSE_THREADS, LF_FUSE_CTAS)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];

@@ -10,10 +10,22 @@ namespace {
 constexpr int FUSE_CONSUMERS = 8;                         // consumer warps
 constexpr int FUSE_THREADS = 32 * FUSE_CONSUMERS;         // stand-alone kernel: every warp consumes
 constexpr int BATCH_THREADS = FUSE_THREADS + 32;          // persistent kernel: + one scheduler warp
-constexpr int FUSE_SUB = 1024;                            // points per stage = 16 KB
+#ifndef LF_FUSE_SUB
+#define LF_FUSE_SUB 1024
+#endif
+#ifndef LF_FUSE_STAGES
+#define LF_FUSE_STAGES 2
+#endif
+#ifndef LF_FUSE_SEG
+#define LF_FUSE_SEG 16384
+#endif
+#ifndef LF_FUSE_CTAS
+#define LF_FUSE_CTAS 5
+#endif
+constexpr int FUSE_SUB = LF_FUSE_SUB;                     // points per stage = 16 KB
 constexpr int FUSE_GROUPS = FUSE_SUB / 32;                // 32-point groups per stage, handed out dynamically
-constexpr int FUSE_STAGES = 2;                            // power of two: stage / parity by shifts
-constexpr int FUSE_SUBS_PER_SEG = 16;
+constexpr int FUSE_STAGES = LF_FUSE_STAGES;
+constexpr int FUSE_SUBS_PER_SEG = LF_FUSE_SEG / FUSE_SUB;
 constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 16384 points per CTA
 
 struct FuseArgs {

@@ -92,6 +92,72 @@ class CounterExchange:
         return self.table, self.agg
 
 
+class PeerCounterExchange:
+    """The same exchange without a reduction: ``lf_publish_table`` stores this rank's rows and
+    aggregates straight into every rank's copy of the table (NVLink peer stores into torch
+    symmetric memory), then ONE signal-pad barrier orders the ranks -- two launches per batch
+    instead of zero-fill + scatter + all-reduce.  Tables are int32 [F_global, max_cars, 4] and
+    double-buffered: the table ``exchange_batch`` returns stays valid until the call after next.
+    Needs one node with peer access (NVLink / NVSwitch); ``available()`` tells."""
+
+    @staticmethod
+    def available():
+        try:
+            import torch.distributed._symmetric_memory  # noqa: F401
+        except Exception:
+            return False
+        return torch.cuda.is_available() and dist.is_initialized()
+
+    def __init__(self, n_frames_global, max_cars, rank, world, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.rank, self.world, self.max_cars = rank, world, max_cars
+        self.lo, self.hi = shard_range(n_frames_global, rank, world)
+        self.n_frames = n_frames_global
+        self._tbytes = n_frames_global * max_cars * TABLE_COLS * 4
+        self._tbytes = (self._tbytes + 15) // 16 * 16
+        self._half = self._tbytes + world * 8 * 8                      # table + [world][8] int64 aggregates
+        self._half = (self._half + 15) // 16 * 16
+        self.buf = symm.empty(2 * self._half // 8, dtype=torch.int64, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self._peers = int(self.hdl.buffer_ptrs_dev)
+        self._step = 0
+        torch.cuda.synchronize(device)
+        self.hdl.barrier(channel=0)                                    # every copy is zeroed before the first store
+        self.table = self.agg_slots = None
+
+    def _views(self, half):
+        base = half * self._half // 8
+        t = self.buf[base:base + self._tbytes // 8].view(torch.int32)[:self.n_frames * self.max_cars * TABLE_COLS]
+        a = self.buf[base + self._tbytes // 8:base + self._tbytes // 8 + self.world * 8]
+        return t.view(self.n_frames, self.max_cars, TABLE_COLS), a.view(self.world, 8)
+
+    def exchange_batch(self, batch):
+        """Publish the counters of a lidarfuse.FrameBatch (after ``run``) to every rank; returns
+        (table, agg_slots): the full int32 table and the aggregates per rank, int64 [world, 8]
+        (``.agg`` sums them)."""
+        from ._abi import check, ptr
+        ctx = batch.ctx
+        half = self._step & 1
+        self._step += 1
+        off = half * self._half
+        check(ctx.lib.lf_publish_table(ctx.h, ptr(batch.total), ptr(batch.best_idx), ptr(batch.best_cnt),
+                                       ptr(batch.mask_off), ptr(batch.box_off), ptr(batch.agg), batch.F, self.max_cars,
+                                       self.lo, self._peers, self.world, self.rank, off, off + self._tbytes, ctx.stream),
+              ctx.h)
+        self.hdl.barrier(channel=0)
+        self.table, self.agg_slots = self._views(half)
+        return self.table, self.agg_slots
+
+    @property
+    def agg(self):
+        """The eight aggregates summed over the ranks (int64 [8]); ``agg_slots`` holds them per rank."""
+        return self.agg_slots.sum(dim=0)
+
+    def bind(self, mask_off, box_counts):
+        """Nothing to pre-compute (kept for interface parity with CounterExchange)."""
+
+
 def rows_from_table(table, frame_ids, min_points=10):
     """Global per-car rows (frame, car_id, matched_bbox_id, total, inside, outside)
     from the reduced table -- what rank 0 turns into CSV lines."""
