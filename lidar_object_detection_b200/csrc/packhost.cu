@@ -63,12 +63,19 @@ __attribute__((target("avx2"))) void pack_row_u8_avx2(const uint8_t* src, int W,
 #if defined(__x86_64__)
 __attribute__((target("avx512f,avx512bw"))) void pack_row_u8_avx512(const uint8_t* src, int W, uint32_t* dst) {
     const int full = W >> 6;
+    const bool nt = ((uintptr_t)dst & 7) == 0;
     for (int w = 0; w < full; ++w) {
         _mm_prefetch((const char*)(src + 64 * w + PF), _MM_HINT_T0);
         const __m512i v = _mm512_loadu_si512((const void*)(src + 64 * w));
         const uint64_t m = (uint64_t)_mm512_test_epi8_mask(v, v);            // bit i = byte i != 0
-        dst[2 * w] = (uint32_t)m;
-        dst[2 * w + 1] = (uint32_t)(m >> 32);
+        // streaming store: the words are read next by the DMA engine, not by this core, and a
+        // plain store would first pull the destination line in (read-for-ownership)
+        if (nt) {
+            _mm_stream_si64((long long*)(dst + 2 * w), (long long)m);
+        } else {
+            dst[2 * w] = (uint32_t)m;
+            dst[2 * w + 1] = (uint32_t)(m >> 32);
+        }
     }
     for (int x0 = 64 * full; x0 < W; x0 += 32) {
         uint32_t acc = 0;
@@ -169,6 +176,9 @@ void pack_rows(const void* masks, int mode, int64_t row0, int64_t row1, int W, u
             else pack_row_f32<2>(src, W, dst);
         }
     }
+#if defined(__x86_64__)
+    _mm_sfence();                                       // streaming stores of the AVX-512 path
+#endif
 }
 
 std::atomic<int> g_simd_cap{2};

@@ -109,6 +109,21 @@ def project_points(points, TrVeloToRect, camera, max_depth=50, return_pix=False,
     return out
 
 
+def gated_pixels(points, TrVeloToRect, camera, max_depth=50, device=None):
+    """Flat pixel index ``v*W + u`` (int32) of every point that passes the gate of cvs_erosion.py:359,
+    -1 for the others: projection + ``filter_valid`` in one pass when ``u, v, depth`` themselves are
+    not needed (the kernel then lets the fp32 pre-gate answer for points that certainly fail;
+    the indices are those of ``project_points(..., return_pix=True)``)."""
+    ctx = get_ctx(device)
+    ctx.set_camera(TrVeloToRect, camera.K, camera.width, camera.height)
+    was_np = _is_np(points)
+    pts = _points4(points, ctx)
+    n = pts.shape[0]
+    pix = torch.empty(n, dtype=torch.int32, device=ctx.device)
+    check(ctx.lib.lf_project(ctx.h, ptr(pts), n, float(max_depth), None, None, None, ptr(pix), ctx.stream), ctx.h)
+    return pix.cpu().numpy() if was_np else pix
+
+
 def filter_valid(u, v, depth, camera, max_depth=50, device=None):
     """Boolean gate of cvs_erosion.py:359 (max_depth 30 in V4:275, V5:508,
     seg_with_pointcloud.py:154-158) on already projected arrays."""

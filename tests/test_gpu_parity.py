@@ -111,6 +111,7 @@ def test_pixel_only_projection_equals_the_full_call(LF, calib):
             check(ctx.lib.lf_project(ctx.h, ptr(t), len(pts), max_depth, None, None, None, ptr(pix), ctx.stream), ctx.h)
             got = pix.cpu().numpy()
             assert np.array_equal(got, np.asarray(want)), (fr, max_depth)
+            assert np.array_equal(LF.gated_pixels(pts, TVR, cam, max_depth=max_depth), got)
             assert (got >= 0).sum() > 20000
 
 
