@@ -1,9 +1,10 @@
 // K1+K4+K5 fused pass over the points of a batch of frames, and K6 per-car decision.
 //
 // One CTA = (frame, segment of FUSE_SEG consecutive points).  The segment is
-// streamed through a 3-stage shared-memory ring by cp.async.bulk (TMA engine):
-// 16 KB sub-chunks of 1024 points, so every point costs exactly 16 B of HBM
-// traffic and two sub-chunks per CTA are always in flight with no register cost.
+// streamed through a 2-stage shared-memory ring by cp.async.bulk (TMA engine):
+// 24 KB sub-chunks of 1536 points, so every point costs exactly 16 B of HBM
+// traffic and the next sub-chunk is in flight while this one is consumed (4 CTAs/SM,
+// 64 registers; the geometry was swept on B200).
 // Per point: fp64 projection chain -> depth gate -> two divisions only for
 // points in front of the camera -> packed-mask gather (L2) -> oriented-box test
 // against the boxes a warp-level bounding-box cull leaves over.  Counters are
@@ -13,7 +14,11 @@
 
 namespace {
 
-__global__ void __launch_bounds__(FUSE_THREADS, LF_FUSE_CTAS)
+// Two geometries of the same kernel: <1536 points per stage, 4 CTAs/SM, 64 registers> when the
+// frame state (boxes + private counters) is small enough for four CTAs per SM, otherwise
+// <1024, 3> (cfg5: 64 masks x 64 boxes per frame = 30 KB of state per CTA).
+template <int SUB, int CTAS>
+__global__ void __launch_bounds__(FUSE_THREADS, CTAS)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
@@ -27,7 +32,31 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
     }
     __syncthreads();
     uint32_t fbase = 0;
-    fuse_item<FUSE_THREADS>(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, stage_cnt, fbase, FuseNoHook());
+    fuse_item<FUSE_THREADS, FuseNoHook, SUB>(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, stage_cnt, fbase, FuseNoHook());
+}
+
+constexpr int FUSE_SUB_WIDE = 1024, FUSE_SEG_WIDE = 16384, FUSE_CTAS_WIDE = 3;   // large per-frame state
+
+template <int SUB, int CTAS>
+cudaError_t launch_fuse(const lf_ctx* ctx, FuseArgs A, size_t state_bytes, int seg_subs, int F,
+                        int64_t max_points_per_frame, cudaStream_t stream) {
+    const size_t smem = (size_t)FUSE_STAGES * SUB * sizeof(float4) + state_bytes;
+    cudaError_t e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) return e;
+    // small batches: shorter segments, so that one frame still spreads over the machine
+    int subs = seg_subs;                                  // stages per segment
+    while (subs > 1 && (int64_t)F * ((max_points_per_frame + (int64_t)subs * SUB - 1) / ((int64_t)subs * SUB)) <
+                           (int64_t)4 * ctx->sm_count)
+        subs = (subs + 1) / 2;
+    const int seg = subs * SUB;
+    A.seg_points = seg;
+    const int64_t chunks = (max_points_per_frame + seg - 1) / seg;
+    if (chunks > 0x7FFFFFFF) return cudaErrorInvalidValue;
+    dim3 grid((unsigned)chunks, (unsigned)F);
+    lf_fuse_kernel<SUB, CTAS><<<grid, FUSE_THREADS, smem, stream>>>(ctx->cam, A);
+    return cudaGetLastError();
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -108,20 +137,17 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
     if (max_masks_per_frame > LF_MAX_CARS) return LF_E_UNSUPPORTED;   // callers split the masks of such frames
     A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
-    const size_t smem = (size_t)FUSE_STAGES * FUSE_SUB * sizeof(float4) + (size_t)A.smem_boxes * sizeof(lf_box) +
-                        4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4) + 16 * (size_t)A.smem_cars;
-    if (smem > 200 * 1024) return LF_E_UNSUPPORTED;
-    LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    LF_CUDA(ctx, cudaFuncSetAttribute(lf_fuse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    // small batches: shorter segments, so that one frame still spreads over the machine
-    int seg = FUSE_SEG;
-    while (seg > FUSE_SUB && (int64_t)F * ((max_points_per_frame + seg - 1) / seg) < (int64_t)4 * ctx->sm_count) seg >>= 1;
-    A.seg_points = seg;
-    const int64_t chunks = (max_points_per_frame + seg - 1) / seg;
-    if (chunks > 0x7FFFFFFF) return LF_E_UNSUPPORTED;
-    dim3 grid((unsigned)chunks, (unsigned)F);
-    lf_fuse_kernel<<<grid, FUSE_THREADS, smem, (cudaStream_t)stream>>>(ctx->cam, A);
-    LF_CUDA(ctx, cudaGetLastError());
+    const size_t state = (size_t)A.smem_boxes * sizeof(lf_box) +
+                         4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4) + 16 * (size_t)A.smem_cars;
+    if ((size_t)FUSE_STAGES * FUSE_SUB_WIDE * sizeof(float4) + state > 200 * 1024) return LF_E_UNSUPPORTED;
+    // four CTAs of the 1536-point geometry per SM need <= 56 KB each (1 KB per CTA is the system's)
+    const bool narrow = (size_t)FUSE_STAGES * FUSE_SUB * sizeof(float4) + state + 1024 <= (size_t)227 * 1024 / LF_FUSE_CTAS;
+    if (narrow)
+        LF_CUDA(ctx, (launch_fuse<FUSE_SUB, LF_FUSE_CTAS>(ctx, A, state, FUSE_SUBS_PER_SEG, F, max_points_per_frame,
+                                                           (cudaStream_t)stream)));
+    else
+        LF_CUDA(ctx, (launch_fuse<FUSE_SUB_WIDE, FUSE_CTAS_WIDE>(ctx, A, state, FUSE_SEG_WIDE / FUSE_SUB_WIDE, F,
+                                                                  max_points_per_frame, (cudaStream_t)stream)));
     return LF_OK;
 }
 

@@ -11,22 +11,24 @@ constexpr int FUSE_CONSUMERS = 8;                         // consumer warps
 constexpr int FUSE_THREADS = 32 * FUSE_CONSUMERS;         // stand-alone kernel: every warp consumes
 constexpr int BATCH_THREADS = FUSE_THREADS + 32;          // persistent kernel: + one scheduler warp
 #ifndef LF_FUSE_SUB
-#define LF_FUSE_SUB 1024
+#define LF_FUSE_SUB 1536
 #endif
 #ifndef LF_FUSE_STAGES
 #define LF_FUSE_STAGES 2
 #endif
 #ifndef LF_FUSE_SEG
-#define LF_FUSE_SEG 16384
+#define LF_FUSE_SEG 12288
 #endif
 #ifndef LF_FUSE_CTAS
-#define LF_FUSE_CTAS 5
+#define LF_FUSE_CTAS 4
 #endif
-constexpr int FUSE_SUB = LF_FUSE_SUB;                     // points per stage = 16 KB
+constexpr int FUSE_SUB = LF_FUSE_SUB;                     // points per stage = 24 KB (a multiple of 256: whole groups per warp)
 constexpr int FUSE_GROUPS = FUSE_SUB / 32;                // 32-point groups per stage, handed out dynamically
 constexpr int FUSE_STAGES = LF_FUSE_STAGES;
 constexpr int FUSE_SUBS_PER_SEG = LF_FUSE_SEG / FUSE_SUB;
-constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 16384 points per CTA
+constexpr int FUSE_SEG = FUSE_SUB * FUSE_SUBS_PER_SEG;    // 12288 points per CTA
+static_assert(FUSE_SUB % (32 * FUSE_CONSUMERS) == 0 && FUSE_SUB / (32 * FUSE_CONSUMERS) <= 32, "stage = whole groups per warp");
+static_assert(LF_FUSE_SEG % FUSE_SUB == 0, "segment = whole stages");
 
 struct FuseArgs {
     const float4* pts;
@@ -227,7 +229,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // there, overlapped with the item).
 struct FuseNoHook { __device__ __forceinline__ void operator()() const {} };
 
-template <int NT, class Hook>
+template <int NT, class Hook, int SUB = FUSE_SUB>
 __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, int f, int seg, uint8_t* smem,
                                           uint64_t* full_bar, int* stage_cnt, uint32_t& fbase, Hook hook) {
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
@@ -237,15 +239,15 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
         return;
     }
     const int npts = (int)min((int64_t)A.seg_points, p1 - seg0);
-    const int nsub = (npts + FUSE_SUB - 1) / FUSE_SUB;
+    const int nsub = (npts + SUB - 1) / SUB;
     const int ngroups = (npts + 31) / 32;
     const int m0 = A.mask_off[f];
     const int M = A.mask_off[f + 1] - m0;
     const int b0 = A.box_off[f];
     const int B = A.box_off[f + 1] - b0;
 
-    float4* stage = (float4*)smem;                                               // [FUSE_STAGES][FUSE_SUB]
-    int4* s_mbb = (int4*)(smem + FUSE_STAGES * FUSE_SUB * sizeof(float4));      // [smem_cars] {x0, y0, x1, y1}
+    float4* stage = (float4*)smem;                                               // [FUSE_STAGES][SUB]
+    int4* s_mbb = (int4*)(smem + FUSE_STAGES * SUB * sizeof(float4));      // [smem_cars] {x0, y0, x1, y1}
     lf_box* s_box = (lf_box*)(s_mbb + A.smem_cars);
     int32_t* s_inside = (int32_t*)((uint8_t*)s_box + (size_t)A.smem_boxes * sizeof(lf_box));
     int32_t* s_nin = s_inside + (size_t)A.smem_cars * A.smem_boxes;
@@ -258,9 +260,9 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
         fence_proxy_async_smem();                          // the previous item read these stages
         for (int i = 0; i < FUSE_STAGES && i < nsub; ++i) {
             const int s = (int)((fbase + i) % FUSE_STAGES);
-            const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
+            const uint32_t bytes = (uint32_t)min(SUB, npts - i * SUB) * 16u;
             mbar_expect_tx(&full_bar[s], bytes);
-            bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)i * FUSE_SUB, bytes, &full_bar[s]);
+            bulk_g2s(stage + s * SUB, src + (int64_t)i * SUB, bytes, &full_bar[s]);
         }
     }
     {   // while the first sub-chunks fly: stage the frame's boxes, clear the private counters
@@ -298,17 +300,17 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
             const uint32_t c = fbase + (uint32_t)sub;
             const int s = (int)(c % FUSE_STAGES);
             mbar_wait(&full_bar[s], (c / FUSE_STAGES) & 1u);
-            const float4* sp = stage + s * FUSE_SUB + warp * 32 + lane;
-            const int k0 = sub * FUSE_SUB + warp * 32 + lane;          // point index inside the segment
+            const float4* sp = stage + s * SUB + warp * 32 + lane;
+            const int k0 = sub * SUB + warp * 32 + lane;          // point index inside the segment
             unsigned mb = 0;
 #pragma unroll
-            for (int j = 0; j < FUSE_GROUPS / FUSE_CONSUMERS; ++j) {
+            for (int j = 0; j < (SUB / 32 / FUSE_CONSUMERS); ++j) {
                 const float4 p = sp[j * 32 * FUSE_CONSUMERS];
                 const bool live = k0 + j * 32 * FUSE_CONSUMERS < npts;
                 mb |= (unsigned)(live & pg.maybe(p)) << j;
             }
             unsigned todo = __reduce_or_sync(0xFFFFFFFFu, mb);
-            if (all_groups) todo = (1u << (FUSE_GROUPS / FUSE_CONSUMERS)) - 1u;
+            if (all_groups) todo = (1u << ((SUB / 32 / FUSE_CONSUMERS))) - 1u;
             while (todo) {
                 const int j = __ffs((int)todo) - 1;
                 todo &= todo - 1;
@@ -324,10 +326,10 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
                 atomicExch(&stage_cnt[s], 0);
                 const int i = sub + FUSE_STAGES;
                 if (i < nsub) {
-                    const uint32_t bytes = (uint32_t)min(FUSE_SUB, npts - i * FUSE_SUB) * 16u;
+                    const uint32_t bytes = (uint32_t)min(SUB, npts - i * SUB) * 16u;
                     fence_proxy_async_smem();
                     mbar_expect_tx(&full_bar[s], bytes);
-                    bulk_g2s(stage + s * FUSE_SUB, src + (int64_t)i * FUSE_SUB, bytes, &full_bar[s]);
+                    bulk_g2s(stage + s * SUB, src + (int64_t)i * SUB, bytes, &full_bar[s]);
                 }
             }
         }
