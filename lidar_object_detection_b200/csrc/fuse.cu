@@ -2,9 +2,9 @@
 //
 // One CTA = (frame, segment of FUSE_SEG consecutive points).  The segment is
 // streamed through a 2-stage shared-memory ring by cp.async.bulk (TMA engine):
-// 24 KB sub-chunks of 1536 points, so every point costs exactly 16 B of HBM
-// traffic and the next sub-chunk is in flight while this one is consumed (4 CTAs/SM,
-// 64 registers; the geometry was swept on B200).
+// 30 KB sub-chunks of 1920 points (16 KB / 1024 points in the wide geometry), so every
+// point costs exactly 16 B of HBM traffic and the next sub-chunk is in flight while this
+// one is consumed (the geometries were swept on B200).
 // Per point: fp64 projection chain -> depth gate -> two divisions only for
 // points in front of the camera -> packed-mask gather (L2) -> oriented-box test
 // against the boxes a warp-level bounding-box cull leaves over.  Counters are
@@ -14,11 +14,13 @@
 
 namespace {
 
-// Two geometries of the same kernel: <1536 points per stage, 4 CTAs/SM, 64 registers> when the
-// frame state (boxes + private counters) is small enough for four CTAs per SM, otherwise
-// <1024, 3> (cfg5: 64 masks x 64 boxes per frame = 30 KB of state per CTA).
-template <int SUB, int CTAS>
-__global__ void __launch_bounds__(FUSE_THREADS, CTAS)
+// Two geometries of the same kernel (swept on B200):
+//   narrow  12 warps, 2 x 1920-point stages (60 KB), 15 360-point segments, 3 CTAs/SM -- when the
+//           frame state (boxes + private counters) leaves room for three such CTAs per SM;
+//   wide     8 warps, 2 x 1024-point stages (32 KB), 16 384-point segments, 3 CTAs/SM -- large
+//           frame state (cfg5: 64 masks x 64 boxes per frame = 30 KB per CTA).
+template <int SUB, int WARPS, int CTAS>
+__global__ void __launch_bounds__(32 * WARPS, CTAS)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
@@ -32,18 +34,34 @@ lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseAr
     }
     __syncthreads();
     uint32_t fbase = 0;
-    fuse_item<FUSE_THREADS, FuseNoHook, SUB>(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, stage_cnt, fbase, FuseNoHook());
+    fuse_item<32 * WARPS, FuseNoHook, SUB, WARPS>(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, stage_cnt, fbase,
+                                                   FuseNoHook());
 }
 
-constexpr int FUSE_SUB_WIDE = 1024, FUSE_SEG_WIDE = 16384, FUSE_CTAS_WIDE = 3;   // large per-frame state
+#ifndef LF_NARROW_SUB
+#define LF_NARROW_SUB 1920
+#endif
+#ifndef LF_NARROW_WARPS
+#define LF_NARROW_WARPS 12
+#endif
+#ifndef LF_NARROW_SEG
+#define LF_NARROW_SEG 15360
+#endif
+#ifndef LF_NARROW_CTAS
+#define LF_NARROW_CTAS 3
+#endif
+constexpr int NARROW_SUB = LF_NARROW_SUB, NARROW_WARPS = LF_NARROW_WARPS, NARROW_SEG = LF_NARROW_SEG, NARROW_CTAS = LF_NARROW_CTAS;
+constexpr int WIDE_SUB = 1024, WIDE_WARPS = 8, WIDE_SEG = 16384, WIDE_CTAS = 3;
+static_assert(NARROW_SEG % NARROW_SUB == 0 && WIDE_SEG % WIDE_SUB == 0, "segment = whole stages");
 
-template <int SUB, int CTAS>
+template <int SUB, int WARPS, int CTAS>
 cudaError_t launch_fuse(const lf_ctx* ctx, FuseArgs A, size_t state_bytes, int seg_subs, int F,
                         int64_t max_points_per_frame, cudaStream_t stream) {
     const size_t smem = (size_t)FUSE_STAGES * SUB * sizeof(float4) + state_bytes;
-    cudaError_t e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, WARPS, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, WARPS, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (e != cudaSuccess) return e;
     // small batches: shorter segments, so that one frame still spreads over the machine
     int subs = seg_subs;                                  // stages per segment
@@ -55,7 +73,7 @@ cudaError_t launch_fuse(const lf_ctx* ctx, FuseArgs A, size_t state_bytes, int s
     const int64_t chunks = (max_points_per_frame + seg - 1) / seg;
     if (chunks > 0x7FFFFFFF) return cudaErrorInvalidValue;
     dim3 grid((unsigned)chunks, (unsigned)F);
-    lf_fuse_kernel<SUB, CTAS><<<grid, FUSE_THREADS, smem, stream>>>(ctx->cam, A);
+    lf_fuse_kernel<SUB, WARPS, CTAS><<<grid, 32 * WARPS, smem, stream>>>(ctx->cam, A);
     return cudaGetLastError();
 }
 
@@ -139,14 +157,16 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
     const size_t state = (size_t)A.smem_boxes * sizeof(lf_box) +
                          4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4) + 16 * (size_t)A.smem_cars;
-    if ((size_t)FUSE_STAGES * FUSE_SUB_WIDE * sizeof(float4) + state > 200 * 1024) return LF_E_UNSUPPORTED;
-    // four CTAs of the 1536-point geometry per SM need <= 56 KB each (1 KB per CTA is the system's)
-    const bool narrow = (size_t)FUSE_STAGES * FUSE_SUB * sizeof(float4) + state + 1024 <= (size_t)227 * 1024 / LF_FUSE_CTAS;
+    if ((size_t)FUSE_STAGES * WIDE_SUB * sizeof(float4) + state > 200 * 1024) return LF_E_UNSUPPORTED;
+    // NARROW_CTAS CTAs of the narrow geometry per SM (1 KB per CTA is the system's)
+    // ... and only when the batch fills the machine with them: a frame or two spread better over 1024-point CTAs
+    const bool narrow = (size_t)FUSE_STAGES * NARROW_SUB * sizeof(float4) + state + 1024 <= (size_t)227 * 1024 / NARROW_CTAS &&
+                        (int64_t)F * ((max_points_per_frame + NARROW_SUB - 1) / NARROW_SUB) >= (int64_t)2 * ctx->sm_count;
     if (narrow)
-        LF_CUDA(ctx, (launch_fuse<FUSE_SUB, LF_FUSE_CTAS>(ctx, A, state, FUSE_SUBS_PER_SEG, F, max_points_per_frame,
-                                                           (cudaStream_t)stream)));
+        LF_CUDA(ctx, (launch_fuse<NARROW_SUB, NARROW_WARPS, NARROW_CTAS>(ctx, A, state, NARROW_SEG / NARROW_SUB, F,
+                                                                        max_points_per_frame, (cudaStream_t)stream)));
     else
-        LF_CUDA(ctx, (launch_fuse<FUSE_SUB_WIDE, FUSE_CTAS_WIDE>(ctx, A, state, FUSE_SEG_WIDE / FUSE_SUB_WIDE, F,
+        LF_CUDA(ctx, (launch_fuse<WIDE_SUB, WIDE_WARPS, WIDE_CTAS>(ctx, A, state, WIDE_SEG / WIDE_SUB, F,
                                                                   max_points_per_frame, (cudaStream_t)stream)));
     return LF_OK;
 }

@@ -7,11 +7,14 @@
 namespace {
 
 
-constexpr int FUSE_CONSUMERS = 8;                         // consumer warps
+#ifndef LF_FUSE_WARPS
+#define LF_FUSE_WARPS 8
+#endif
+constexpr int FUSE_CONSUMERS = LF_FUSE_WARPS;             // consumer warps
 constexpr int FUSE_THREADS = 32 * FUSE_CONSUMERS;         // stand-alone kernel: every warp consumes
 constexpr int BATCH_THREADS = FUSE_THREADS + 32;          // persistent kernel: + one scheduler warp
 #ifndef LF_FUSE_SUB
-#define LF_FUSE_SUB 1536
+#define LF_FUSE_SUB 1536         /* persistent kernel (batch.cu); the stand-alone launch has its own geometries */
 #endif
 #ifndef LF_FUSE_STAGES
 #define LF_FUSE_STAGES 2
@@ -229,13 +232,14 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // there, overlapped with the item).
 struct FuseNoHook { __device__ __forceinline__ void operator()() const {} };
 
-template <int NT, class Hook, int SUB = FUSE_SUB>
+template <int NT, class Hook, int SUB = FUSE_SUB, int WARPS = FUSE_CONSUMERS>
 __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, int f, int seg, uint8_t* smem,
                                           uint64_t* full_bar, int* stage_cnt, uint32_t& fbase, Hook hook) {
+    static_assert(SUB % (32 * WARPS) == 0 && SUB / (32 * WARPS) <= 32, "stage = whole groups per warp");
     const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
     const int64_t seg0 = p0 + (int64_t)seg * A.seg_points;
     if (seg0 >= p1) {
-        if (threadIdx.x == 32 * FUSE_CONSUMERS) hook();
+        if (threadIdx.x == 32 * WARPS) hook();
         return;
     }
     const int npts = (int)min((int64_t)A.seg_points, p1 - seg0);
@@ -283,8 +287,8 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
     }
     __syncthreads();
 
-    if (warp >= FUSE_CONSUMERS) {
-        if (threadIdx.x == 32 * FUSE_CONSUMERS) hook();
+    if (warp >= WARPS) {
+        if (threadIdx.x == 32 * WARPS) hook();
     } else {
         const int plane32 = cam.H * cam.wpr;               // words per packed mask (< 2^25, see lf_set_camera)
         const uint32_t* mask_base = A.packed + (int64_t)m0 * plane32;
@@ -304,24 +308,24 @@ __device__ __forceinline__ void fuse_item(const LfCam& cam, const FuseArgs& A, i
             const int k0 = sub * SUB + warp * 32 + lane;          // point index inside the segment
             unsigned mb = 0;
 #pragma unroll
-            for (int j = 0; j < (SUB / 32 / FUSE_CONSUMERS); ++j) {
-                const float4 p = sp[j * 32 * FUSE_CONSUMERS];
-                const bool live = k0 + j * 32 * FUSE_CONSUMERS < npts;
+            for (int j = 0; j < (SUB / 32 / WARPS); ++j) {
+                const float4 p = sp[j * 32 * WARPS];
+                const bool live = k0 + j * 32 * WARPS < npts;
                 mb |= (unsigned)(live & pg.maybe(p)) << j;
             }
             unsigned todo = __reduce_or_sync(0xFFFFFFFFu, mb);
-            if (all_groups) todo = (1u << ((SUB / 32 / FUSE_CONSUMERS))) - 1u;
+            if (all_groups) todo = (1u << ((SUB / 32 / WARPS))) - 1u;
             while (todo) {
                 const int j = __ffs((int)todo) - 1;
                 todo &= todo - 1;
-                const int k = k0 + j * 32 * FUSE_CONSUMERS;
+                const int k = k0 + j * 32 * WARPS;
                 const bool live = k < npts;
-                const float4 p = sp[j * 32 * FUSE_CONSUMERS];
+                const float4 p = sp[j * 32 * WARPS];
                 fuse_warp_points(cam, A, p, live, (mb >> j) & 1u, seg0 + k, lane, M, B, s_mbb, mask_base, plane32, s_box,
                                  s_inside, s_nin, s_total, my_valid);
             }
             __syncwarp();
-            if (lane == 0 && atomicAdd(&stage_cnt[s], 1) == FUSE_CONSUMERS - 1) {
+            if (lane == 0 && atomicAdd(&stage_cnt[s], 1) == WARPS - 1) {
                 // last warp out of this stage: every warp's reads are done -> refill it
                 atomicExch(&stage_cnt[s], 0);
                 const int i = sub + FUSE_STAGES;
