@@ -194,7 +194,9 @@ def run_gpu(args):
         nccl_exch = D.CounterExchange(world * frames, NCARS, rank, world, dev)
         nccl_exch.bind(batch.h_mask_off, sb.n_boxes)
         exch, exch_kind = nccl_exch, 'one NCCL all_reduce(SUM) over the zero-filled int64 table per batch'
-        if args.exchange == 'peer' and D.PeerCounterExchange.available():
+        can = torch.tensor([int(args.exchange == 'peer' and D.PeerCounterExchange.available())], device=dev)
+        dist.all_reduce(can, op=dist.ReduceOp.MIN)       # every rank must be able to, or none uses it
+        if int(can.item()):
             try:
                 exch = D.PeerCounterExchange(world * frames, NCARS, rank, world, dev)
                 exch_kind = 'lf_publish_table: rows stored into every rank\'s table over NVLink peer memory + one ' \
