@@ -6,7 +6,7 @@ HDL-64-shaped frames (BASELINE.json metric).
 
 A step = one pass of the hot path over one batch per GPU: counter memset,
 erode+pack of the uint8 masks, the fused point pass and the per-car decision
-(4 launches; --persistent: erosion and the point pass as one persistent kernel),
+(4 launches),
 plus -- at N > 1 -- the single all-reduce of the per-car table.
 N = 1 runs BASELINE configs[2]: 1024 frames x 131072 points x 16 masks
 (1408x376) x 16 boxes, all resident in HBM (10.8 GB >> 126 MB L2, so no L2
@@ -212,7 +212,7 @@ def run_gpu(args):
                 raise SystemExit('PARITY FAILURE: peer-store exchange differs from the NCCL all-reduce')
 
     def step(mark=None):
-        batch.run(KSIZE, 1, 50, 10, True, mark=mark, persistent=args.persistent)
+        batch.run(KSIZE, 1, 50, 10, True, mark=mark)
         if exch is not None:
             exch.exchange_batch(batch)
 
@@ -280,8 +280,7 @@ def run_gpu(args):
     kern = {}
     for lst in marks:
         d = dict(lst)
-        pairs = (('zero', 'erode_pack'), ('erode_pack', 'fuse'), ('fuse', 'car_stats')) if not args.persistent else \
-            (('zero', 'batch'), ('batch', 'car_stats'))
+        pairs = (('zero', 'erode_pack'), ('erode_pack', 'fuse'), ('fuse', 'car_stats'))
         for a, b in pairs:
             kern.setdefault(b, []).append(d[a].elapsed_time(d[b]))
     kern_ms = {k: sum(v) / len(v) for k, v in kern.items()}
@@ -323,7 +322,7 @@ def run_gpu(args):
     # ---- secondary accounting (SURVEY 8(d) "packed-masks-in"): the masks cross PCIe and enter HBM at one
     # bit per pixel (lf_pack_masks_host on the sending side), erosion runs on the device from the words
     packed_in = None
-    if not args.no_packed and not args.persistent:
+    if not args.no_packed:
         from lidar_object_detection_b200 import io as IO, lidarfuse as LF
         words = LF.erode_pack(batch.masks, 0, 0, device=local).words
         pb = LF.FrameBatch(batch.points, [n_pts] * frames, LF.PackedMasks(words, H_IMG, W_IMG, raw=True), [NCARS] * frames,
@@ -419,13 +418,9 @@ def run_gpu(args):
             peak = 6650.0
         step_bytes = sum(algorithmic_bytes_per_frame(n_pts, NCARS, b) for b in sb.n_boxes)
         se_name = 'SeCross3' if KSIZE == 3 else 'SeEllipse%d' % KSIZE
-        if not args.persistent:  # dominant kernel: the erode launch, F*M*H*W bytes in
-            kname, kkey, tkey = 'lf_erode_fast_kernel<%s> (lf_erode_pack)' % se_name, 'erode_pack', 'lf_erode_fast_kernel'
-            mask_bytes = frames * NCARS * H_IMG * W_IMG
-        else:                   # the persistent kernel does erode + point pass: all algorithmic bytes of the step
-            kname, kkey, tkey = 'lf_batch_kernel<%s> (lf_process_batch: erode+pack and fused point pass)' % se_name, \
-                'batch', 'lf_batch_kernel'
-            mask_bytes = step_bytes
+        # dominant kernel: the erode launch, F*M*H*W bytes in
+        kname, kkey, tkey = 'lf_erode_fast_kernel<%s> (lf_erode_pack)' % se_name, 'erode_pack', 'lf_erode_fast_kernel'
+        mask_bytes = frames * NCARS * H_IMG * W_IMG
         ach = mask_bytes / (kern_ms[kkey] * 1e-3) / 1e9
         traffic = None
         try:
@@ -502,9 +497,6 @@ def main():
     ap.add_argument('--no-packed', action='store_true', help='skip the packed-masks-in secondary measurement')
     ap.add_argument('--exchange', default='peer', choices=['peer', 'nccl'],
                     help='N > 1: per-car table exchanged by stores into peer memory (default) or by the NCCL all-reduce')
-    ap.add_argument('--persistent', action='store_true',
-                    help='one persistent erode+fuse kernel (lf_process_batch with scheduler words) instead of '
-                         'the stand-alone erode / fuse launches')
     args = ap.parse_args()
     set_workload(args.workload, args.frames)
     # stdout carries the ONE JSON line and nothing else: whatever libraries print while the job runs

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define LF_VERSION 100
+#define LF_VERSION 200
 
 #define LF_OK            0
 #define LF_E_ARG        -1   /* bad argument (null pointer, negative size, unsupported shape) */
@@ -45,6 +45,11 @@ extern "C" {
 
 #define LF_MAX_SE 15         /* structuring elements up to 15x15 */
 #define LF_MAX_CARS 64       /* masks per frame handled in one pass of lf_fuse_batch */
+
+/* `use_oriented` of lf_fuse_batch / lf_process_batch is a flag word */
+#define LF_FUSE_ORIENTED 1   /* oriented slab test (cvs_erosion.py:114-145); clear = axis-aligned (V1:118-139) */
+#define LF_FUSE_EXACT    2   /* verification mode: no point is classified in fp32, every point that may pass the
+                                gate takes the float64 chain (same results by construction; the tests compare) */
 
 #define LF_POLICY_NEAREST 0  /* z-buffer: smallest depth per pixel (north-star) */
 #define LF_POLICY_LAST    1  /* last point in index order wins (seg_with_pointcloud.py:162-168) */
@@ -142,7 +147,9 @@ int lf_prepare_boxes(const double* corners_velo /*HOST [n][8][3]*/, int64_t n, l
  *   n_in_box[box]      gated points inside box b (extension metrics)
  *   n_valid[f]         points passing the gate
  *   car_bits           optional DEVICE uint64 [total points]: bit c = point in mask c of its frame
- *                      (0 for gated-out points); may be NULL                                       */
+ *                      (0 for gated-out points); may be NULL
+ * use_oriented: LF_FUSE_ORIENTED | LF_FUSE_EXACT flags (0 / 1 keep their old meaning).  Any F: batches
+ * beyond 65535 frames are issued as several launches.  Camera images up to 65535 x 65535.         */
 int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
                   const uint32_t* packed /*DEVICE*/,
                   const int32_t* mask_bbox /*DEVICE [sum M][4] from lf_erode_pack, 16-B aligned, or NULL*/,
@@ -155,14 +162,10 @@ int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_of
 
 /* The whole per-batch body of cvs_erosion.process_frames (:342-372) in one call:
  * lf_erode_pack + lf_fuse_batch + lf_car_stats with the same arguments and the same
- * results.  When `sched` is given (DEVICE int32 [F + 2], zeroed by the caller like the
- * counters), the masks are uint8 at camera resolution and the structuring element is one
- * of the compiled-in cv2 shapes (RECT / CROSS / ELLIPSE up to 7x7), erosion and the point
- * pass run as ONE persistent kernel whose CTAs claim "erode mask m" / "fuse segment s of
- * frame f" work items, a frame's points being released as soon as its last mask is
- * packed; otherwise the three stand-alone launches are issued.  masks == NULL: `packed`
- * and `mask_bbox` are inputs (already packed masks).  best_idx / best_cnt / agg as in
- * lf_car_stats (NULL best_idx skips the decision). */
+ * results (three launches on `stream`).  masks == NULL: `packed` and `mask_bbox` are
+ * inputs (already packed masks).  best_idx / best_cnt / agg as in lf_car_stats (NULL
+ * best_idx skips the decision).  `sched` is reserved and ignored (pass NULL): the
+ * persistent erode+fuse kernel it selected in version 100 was slower than the launches. */
 int lf_process_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
                      const void* masks /*DEVICE [n_masks][H][W] or NULL*/, int mask_mode, int64_t n_masks,
                      const int32_t* mask_off /*DEVICE [F+1]*/, const uint8_t* se /*HOST [k][k]*/, int k,

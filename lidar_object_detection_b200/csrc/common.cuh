@@ -19,6 +19,12 @@ struct LfCam {
     float hwx, hwy;        // (W+1)/2, (H+1)/2: half extents with a one-pixel margin
     float tX, tY, tD;      // bounds on the fp32 evaluation error for points within gR
     float gR;              // points beyond it skip the pre-gate (exact path decides)
+    // fused point pass (fuse_body.cuh): one magnitude-relative tolerance for every fp32 row,
+    //   tol(p) = kT * (|x|+|y|+|z|+1) >= 4 x the worst fp32 evaluation error of any row at p,
+    // evaluated as fmaf((|x|+|y|+|z|) * gS, kTs, kT) with gS = 2^108, kTs = kT * 2^-108 so that it
+    // overflows to +inf (= "never certain") for points beyond 2^20 m; cxm, cym = image centre
+    // ((W-1)/2, (H-1)/2) the rows 0 / 1 of Pg are shifted by.
+    float kT, kTs, gS, cxm, cym;
 };
 
 struct lf_ctx {

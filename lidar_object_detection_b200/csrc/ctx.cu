@@ -90,6 +90,19 @@ extern "C" int lf_set_camera(lf_ctx* ctx, const double TrVeloToRect[16], const d
     ctx->cam.tD = (float)(eps * fmax(pm[2], 1e-30) * mag * 1.0001);
     ctx->cam.tX = (float)(eps * (pm[0] + (W + 2.0) * pm[2]) * mag * 1.0001 + 1e-30);
     ctx->cam.tY = (float)(eps * (pm[1] + (H + 2.0) * pm[2]) * mag * 1.0001 + 1e-30);
+    // Fused point pass: |fp32 row - exact row| <= 4 * 2^-24 * max_j|P_rj| * mag(p), mag = |x|+|y|+|z|+1
+    // (one coefficient rounding + three fma roundings, no overflow below 2^20 m).  kT carries
+    // a further factor 4 and the largest amplification any test applies to the depth error
+    // ((W+2) resp. (H+2) times row 2), so one tolerance serves the depth gate, the one-pixel
+    // image margin and the half-pixel residual test of the rounded pixel.
+    double kT = eps * (fmax(pm[0], pm[1]) + (fmax(W, H) + 2.0) * fmax(pm[2], 1e-30)) * 1.0001 + 1e-30;
+    if (!(kT >= 7.62939453125e-06)) kT = 7.62939453125e-06;   // 2^-17: a larger tolerance is always safe
+    ctx->cam.kT = (float)kT;
+    if ((double)ctx->cam.kT < kT) ctx->cam.kT = nextafterf(ctx->cam.kT, INFINITY);
+    ctx->cam.gS = 3.2451855365842673e+32f;                 // 2^108
+    ctx->cam.kTs = ctx->cam.kT * 3.0814879110195774e-33f;  // kT * 2^-108 (exact scaling; kT >= 2^-18 keeps it normal)
+    ctx->cam.cxm = (float)cxm;
+    ctx->cam.cym = (float)cym;
     ctx->has_camera = 1;
     return LF_OK;
 }

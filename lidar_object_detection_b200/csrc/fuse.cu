@@ -1,80 +1,66 @@
 // K1+K4+K5 fused pass over the points of a batch of frames, and K6 per-car decision.
 //
-// One CTA = (frame, segment of FUSE_SEG consecutive points).  The segment is
-// streamed through a 2-stage shared-memory ring by cp.async.bulk (TMA engine):
-// 30 KB sub-chunks of 1920 points (16 KB / 1024 points in the wide geometry), so every
-// point costs exactly 16 B of HBM traffic and the next sub-chunk is in flight while this
-// one is consumed (the geometries were swept on B200).
-// Per point: fp64 projection chain -> depth gate -> two divisions only for
-// points in front of the camera -> packed-mask gather (L2) -> oriented-box test
-// against the boxes a warp-level bounding-box cull leaves over.  Counters are
-// privatised in shared memory and flushed with one global atomic per non-zero
-// counter per CTA.
+// One CTA = (frame, segment of consecutive points).  Every thread streams its points through
+// registers (PER independent 128-bit loads in flight, read exactly once: 16 B of HBM traffic
+// per point), classifies them in fp32, and only survivors -- compacted into per-warp
+// shared-memory queues -- reach the packed-mask gather (L2) and the float64 containment test
+// (fuse_body.cuh).  Counters are privatised in shared memory and flushed with one global
+// atomic per non-zero counter per CTA.
+#include <math.h>
 #include "fuse_body.cuh"
 
 namespace {
 
-// Two geometries of the same kernel (swept on B200):
-//   narrow  12 warps, 2 x 1920-point stages (60 KB), 15 360-point segments, 3 CTAs/SM -- when the
-//           frame state (boxes + private counters) leaves room for three such CTAs per SM;
-//   wide     8 warps, 2 x 1024-point stages (32 KB), 16 384-point segments, 3 CTAs/SM -- large
-//           frame state (cfg5: 64 masks x 64 boxes per frame = 30 KB per CTA).
-template <int SUB, int WARPS, int CTAS>
+#ifndef LF_FUSE_WARPS
+#define LF_FUSE_WARPS 8
+#endif
+#ifndef LF_FUSE_PER
+#define LF_FUSE_PER 8            /* loads in flight per thread; the small-queue geometry uses half */
+#endif
+#ifndef LF_FUSE_CTAS
+#define LF_FUSE_CTAS 4           /* launch bound (registers); shared memory decides how many really fit */
+#endif
+#ifndef LF_FUSE_SEG
+#define LF_FUSE_SEG 16384        /* points per CTA for batches that fill the machine */
+#endif
+
+template <int WARPS, int PER, bool BITS, int CTAS>
 __global__ void __launch_bounds__(32 * WARPS, CTAS)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
-    __shared__ int stage_cnt[FUSE_STAGES];
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < FUSE_STAGES; ++s) {
-            mbar_init(&full_bar[s], 1);
-            stage_cnt[s] = 0;
-        }
-        mbar_fence_init();
-    }
-    __syncthreads();
-    uint32_t fbase = 0;
-    fuse_item<32 * WARPS, FuseNoHook, SUB, WARPS>(cam, A, blockIdx.y, blockIdx.x, smem, full_bar, stage_cnt, fbase,
-                                                   FuseNoHook());
+    fuse_segment<WARPS, PER, BITS>(cam, A, blockIdx.y, blockIdx.x, smem);
 }
 
-#ifndef LF_NARROW_SUB
-#define LF_NARROW_SUB 1920
-#endif
-#ifndef LF_NARROW_WARPS
-#define LF_NARROW_WARPS 12
-#endif
-#ifndef LF_NARROW_SEG
-#define LF_NARROW_SEG 15360
-#endif
-#ifndef LF_NARROW_CTAS
-#define LF_NARROW_CTAS 3
-#endif
-constexpr int NARROW_SUB = LF_NARROW_SUB, NARROW_WARPS = LF_NARROW_WARPS, NARROW_SEG = LF_NARROW_SEG, NARROW_CTAS = LF_NARROW_CTAS;
-constexpr int WIDE_SUB = 1024, WIDE_WARPS = 8, WIDE_SEG = 16384, WIDE_CTAS = 3;
-static_assert(NARROW_SEG % NARROW_SUB == 0 && WIDE_SEG % WIDE_SUB == 0, "segment = whole stages");
-
-template <int SUB, int WARPS, int CTAS>
-cudaError_t launch_fuse(const lf_ctx* ctx, FuseArgs A, size_t state_bytes, int seg_subs, int F,
-                        int64_t max_points_per_frame, cudaStream_t stream) {
-    const size_t smem = (size_t)FUSE_STAGES * SUB * sizeof(float4) + state_bytes;
-    cudaError_t e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, WARPS, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
+template <int WARPS, int PER, bool BITS, int CTAS>
+cudaError_t launch_fuse(const lf_ctx* ctx, FuseArgs A, size_t state_bytes, int F, int64_t max_points_per_frame,
+                        cudaStream_t stream) {
+    using G = FuseGeom<WARPS, PER, BITS>;
+    const size_t smem = G::queue_bytes + state_bytes;
+    auto kern = lf_fuse_kernel<WARPS, PER, BITS, CTAS>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(lf_fuse_kernel<SUB, WARPS, CTAS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (e != cudaSuccess) return e;
-    // small batches: shorter segments, so that one frame still spreads over the machine
-    int subs = seg_subs;                                  // stages per segment
-    while (subs > 1 && (int64_t)F * ((max_points_per_frame + (int64_t)subs * SUB - 1) / ((int64_t)subs * SUB)) <
-                           (int64_t)4 * ctx->sm_count)
-        subs = (subs + 1) / 2;
-    const int seg = subs * SUB;
-    A.seg_points = seg;
+    // small batches: shorter segments (whole groups per warp), so that one frame still spreads over the machine
+    int64_t seg = LF_FUSE_SEG;
+    while (seg > G::NT && (int64_t)F * ((max_points_per_frame + seg - 1) / seg) < (int64_t)4 * ctx->sm_count)
+        seg = ((seg / 2 + G::NT - 1) / G::NT) * G::NT;
+    A.seg_points = (int)seg;
     const int64_t chunks = (max_points_per_frame + seg - 1) / seg;
     if (chunks > 0x7FFFFFFF) return cudaErrorInvalidValue;
     dim3 grid((unsigned)chunks, (unsigned)F);
-    lf_fuse_kernel<SUB, WARPS, CTAS><<<grid, 32 * WARPS, smem, stream>>>(ctx->cam, A);
+    kern<<<grid, G::NT, smem, stream>>>(ctx->cam, A);
     return cudaGetLastError();
+}
+
+template <bool BITS>
+cudaError_t launch_fuse_any(const lf_ctx* ctx, const FuseArgs& A, size_t state, int F, int64_t maxn, cudaStream_t st) {
+    // full queues (PER loads in flight per thread) when LF_FUSE_CTAS such CTAs fit one SM next to the
+    // frame state; else the half-size geometry (cfg5: 64 masks x 64 boxes = 32 KB of state per CTA)
+    using Gf = FuseGeom<LF_FUSE_WARPS, LF_FUSE_PER, BITS>;
+    if ((Gf::queue_bytes + state + 1024) * LF_FUSE_CTAS <= (size_t)227 * 1024)
+        return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER, BITS, LF_FUSE_CTAS>(ctx, A, state, F, maxn, st);
+    return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER / 2, BITS, LF_FUSE_CTAS>(ctx, A, state, F, maxn, st);
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -137,13 +123,14 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
         return LF_E_ARG;
     if (!ctx->has_camera) return LF_E_NOCAMERA;
     if (F == 0 || max_points_per_frame == 0) return LF_OK;
-    if (!pts || !pt_off || !mask_off || !box_off || !cnt_off || !total || !inside || !n_in_box || !n_valid)
-        return LF_E_ARG;
-    if (max_masks_per_frame > 0 && !packed) return LF_E_ARG;
-    if (max_boxes_per_frame > 0 && !boxes) return LF_E_ARG;
+    if (!pts || !pt_off || !mask_off || !box_off || !cnt_off || !n_valid) return LF_E_ARG;
+    if (max_masks_per_frame > 0 && (!packed || !total)) return LF_E_ARG;
+    if (max_boxes_per_frame > 0 && (!boxes || !n_in_box)) return LF_E_ARG;
+    if (max_masks_per_frame > 0 && max_boxes_per_frame > 0 && !inside) return LF_E_ARG;
     if (((uintptr_t)pts & 15) != 0 || ((uintptr_t)mask_bbox & 15) != 0) return LF_E_ARG;
     if ((int64_t)ctx->cam.H * ctx->cam.wpr * LF_MAX_CARS >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
-    if (F > 65535) return LF_E_UNSUPPORTED;      // gridDim.y; callers split larger batches
+    if (ctx->cam.W > 65535 || ctx->cam.H > 65535) return LF_E_UNSUPPORTED;   // queued pixels are 16 + 16 bits
+    if (max_masks_per_frame > LF_MAX_CARS) return LF_E_UNSUPPORTED;           // one 64-bit membership word per point
     LF_CUDA(ctx, cudaSetDevice(ctx->device));
 
     FuseArgs A;
@@ -151,23 +138,33 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     A.boxes = boxes; A.box_off = box_off; A.cnt_off = cnt_off;
     A.total = total; A.inside = inside; A.n_in_box = n_in_box; A.n_valid = n_valid;
     A.car_bits = (unsigned long long*)car_bits;
-    A.max_depth = max_depth; A.use_oriented = use_oriented;
+    A.max_depth = max_depth;
+    A.use_oriented = use_oriented & LF_FUSE_ORIENTED;
+    A.force_exact = (use_oriented & LF_FUSE_EXACT) != 0;
+    // float brackets of the range gate: dmax_hi >= max_depth > dmax_lo (NaN: nothing is ever certain)
+    float dh = (float)max_depth, dl = (float)max_depth;
+    if ((double)dh < max_depth) dh = nextafterf(dh, INFINITY);
+    if (!((double)dl < max_depth)) dl = nextafterf(dl, -INFINITY);
+    A.dmax_hi = dh; A.dmax_lo = dl;
     A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
-    if (max_masks_per_frame > LF_MAX_CARS) return LF_E_UNSUPPORTED;   // callers split the masks of such frames
     A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
-    const size_t state = (size_t)A.smem_boxes * sizeof(lf_box) +
-                         4 * ((size_t)A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 4) + 16 * (size_t)A.smem_cars;
-    if ((size_t)FUSE_STAGES * WIDE_SUB * sizeof(float4) + state > 200 * 1024) return LF_E_UNSUPPORTED;
-    // NARROW_CTAS CTAs of the narrow geometry per SM (1 KB per CTA is the system's)
-    // ... and only when the batch fills the machine with them: a frame or two spread better over 1024-point CTAs
-    const bool narrow = (size_t)FUSE_STAGES * NARROW_SUB * sizeof(float4) + state + 1024 <= (size_t)227 * 1024 / NARROW_CTAS &&
-                        (int64_t)F * ((max_points_per_frame + NARROW_SUB - 1) / NARROW_SUB) >= (int64_t)2 * ctx->sm_count;
-    if (narrow)
-        LF_CUDA(ctx, (launch_fuse<NARROW_SUB, NARROW_WARPS, NARROW_CTAS>(ctx, A, state, NARROW_SEG / NARROW_SUB, F,
-                                                                        max_points_per_frame, (cudaStream_t)stream)));
-    else
-        LF_CUDA(ctx, (launch_fuse<WIDE_SUB, WIDE_WARPS, WIDE_CTAS>(ctx, A, state, WIDE_SEG / WIDE_SUB, F,
-                                                                  max_points_per_frame, (cudaStream_t)stream)));
+    A.seg_points = 0;
+    const size_t state = fuse_state_bytes(A.smem_cars, A.smem_boxes);
+    cudaStream_t st = (cudaStream_t)stream;
+    // the frame state is per-CTA shared memory; the largest frame must leave room for the half-size queues
+    if (FuseGeom<LF_FUSE_WARPS, LF_FUSE_PER / 2, true>::queue_bytes + state + 1024 > (size_t)227 * 1024)
+        return LF_E_UNSUPPORTED;
+    // frames beyond gridDim.y = 65535 go out in further launches of the same kernel (the CSR arrays
+    // are simply entered at frame f0)
+    for (int f0 = 0; f0 < F; f0 += 65535) {
+        const int nf = F - f0 < 65535 ? F - f0 : 65535;
+        FuseArgs Af = A;
+        Af.pt_off += f0; Af.mask_off += f0; Af.box_off += f0; Af.cnt_off += f0; Af.n_valid += f0;
+        if (car_bits)
+            LF_CUDA(ctx, launch_fuse_any<true>(ctx, Af, state, nf, max_points_per_frame, st));
+        else
+            LF_CUDA(ctx, launch_fuse_any<false>(ctx, Af, state, nf, max_points_per_frame, st));
+    }
     return LF_OK;
 }
 
@@ -183,5 +180,40 @@ extern "C" int lf_car_stats(lf_ctx* ctx, const int32_t* total, const int32_t* in
         total, inside, mask_off, box_off, cnt_off, F, min_points, best_idx, best_cnt,
         (unsigned long long*)agg);
     LF_CUDA(ctx, cudaGetLastError());
+    return LF_OK;
+}
+
+// erode + fuse + decision in one ABI call (three stand-alone launches).  `sched` is reserved: the
+// persistent erode+fuse kernel it once selected was measured slower than the launches and is gone.
+extern "C" int lf_process_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const void* masks, int mask_mode,
+                                int64_t n_masks, const int32_t* mask_off, const uint8_t* se, int k, int iterations,
+                                uint32_t* packed, int32_t* mask_bbox, const lf_box* boxes, const int32_t* box_off,
+                                const int64_t* cnt_off, int F, int64_t max_points_per_frame, int max_masks_per_frame,
+                                int max_boxes_per_frame, double max_depth, int use_oriented, int min_points,
+                                int32_t* total, int32_t* inside, int32_t* n_in_box, int32_t* n_valid,
+                                int32_t* best_idx, int32_t* best_cnt, int64_t* agg, int32_t* sched, void* stream) {
+    (void)sched;
+    if (!ctx || F < 0 || n_masks < 0 || max_points_per_frame < 0 || max_masks_per_frame < 0 ||
+        max_boxes_per_frame < 0 || iterations < 0)
+        return LF_E_ARG;
+    if (!ctx->has_camera) return LF_E_NOCAMERA;
+    if (F == 0) return LF_OK;
+    int rc;
+    if (masks && n_masks > 0) {
+        rc = lf_erode_pack(ctx, masks, mask_mode, n_masks, ctx->cam.H, ctx->cam.W, se, k, iterations, packed, mask_bbox,
+                           stream);
+        if (rc != LF_OK) return rc;
+    }
+    if (max_points_per_frame > 0) {
+        rc = lf_fuse_batch(ctx, pts, pt_off, packed, mask_bbox, mask_off, boxes, box_off, cnt_off, F,
+                           max_points_per_frame, max_masks_per_frame, max_boxes_per_frame, max_depth, use_oriented,
+                           total, inside, n_in_box, n_valid, nullptr, stream);
+        if (rc != LF_OK) return rc;
+        if (best_idx && best_cnt) {
+            rc = lf_car_stats(ctx, total, inside, mask_off, box_off, cnt_off, F, min_points, best_idx, best_cnt, agg,
+                              stream);
+            if (rc != LF_OK) return rc;
+        }
+    }
     return LF_OK;
 }

@@ -558,8 +558,6 @@ class FrameBatch:
         n_boxes = np.asarray(n_boxes, np.int64)
         if not (len(n_masks) == len(n_boxes) == self.F):
             raise ValueError('per-frame count arrays must have equal length')
-        if self.F > 65535:
-            raise ValueError('at most 65535 frames per batch; split larger jobs')
         self.points = _points4(points, ctx) if not isinstance(points, torch.Tensor) or points.shape[-1] != 4 \
             or points.dtype != torch.float32 or not points.is_cuda else points.contiguous()
         if self.points.shape[0] != int(n_points.sum()):
@@ -591,11 +589,11 @@ class FrameBatch:
         self.max_m = int(n_masks.max()) if self.F else 0
         self.max_b = int(n_boxes.max()) if self.F else 0
         sm, sb, sc = int(n_masks.sum()), int(n_boxes.sum()), int(self.h_cnt_off[-1])
-        # one allocation for everything the step zeroes:
-        # mask bbox [sm,4] | total | n_in_box | n_valid | inside | sched [F+2] | agg(int64 x8)
+        # one allocation for everything the step zeroes and everything it hands back:
+        # mask bbox [sm,4] | total | n_in_box | n_valid | inside | best_idx | best_cnt | pad | agg(int64 x8)
         self._o = 4 * sm
-        self._ns = self._o + sm + sb + self.F + sc
-        self._nz = self._ns + self.F + 2
+        self._ob = self._o + sm + sb + self.F + sc        # best_idx, then best_cnt
+        self._nz = self._ob + 2 * sm
         self._nz += self._nz & 1
         self.counters = torch.zeros(self._nz + 16, dtype=torch.int32, device=ctx.device)
         o = self._o
@@ -604,10 +602,9 @@ class FrameBatch:
         self.n_in_box = self.counters[o + sm:o + sm + sb]
         self.n_valid = self.counters[o + sm + sb:o + sm + sb + self.F]
         self.inside = self.counters[o + sm + sb + self.F:o + sm + sb + self.F + sc]
-        self.sched = self.counters[self._ns:self._ns + self.F + 2]
+        self.best_idx = self.counters[self._ob:self._ob + sm]
+        self.best_cnt = self.counters[self._ob + sm:self._ob + 2 * sm]
         self.agg = self.counters[self._nz:].view(torch.int64)
-        self.best_idx = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
-        self.best_cnt = torch.empty(max(sm, 1), dtype=torch.int32, device=ctx.device)
         self.car_bits = torch.empty(self.points.shape[0], dtype=torch.int64, device=ctx.device) \
             if want_car_bits else None
         self._native = None
@@ -632,19 +629,18 @@ class FrameBatch:
         self.launches_per_run = 0
 
     def run(self, erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True,
-            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, persistent=False):
+            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, one_call=False, exact=False):
         """memset + erode/pack + fused point pass + per-car decision, all async
-        on the current stream.  Returns nothing; read ``results()``.
+        on the current stream.  Returns nothing; read ``results()`` / ``table()``.
 
-        ``persistent=True`` hands ``lf_process_batch`` its scheduler words, so that
-        erosion and the point pass run as ONE persistent kernel when the masks
-        allow it (measured slower than the two launches on B200, see DESIGN.md 5);
-        the default issues the stand-alone launches, ``mark(name)`` between them."""
+        ``one_call=True`` issues erode + point pass + decision through the single ABI entry
+        ``lf_process_batch`` instead of the three calls (``mark(name)`` between them);
+        ``exact=True`` is the verification mode of the point pass (``LF_FUSE_EXACT``: no point
+        is classified in fp32) -- same results, the tests compare the two."""
         ctx, lib = self.ctx, self.ctx.lib
         ctx.set_camera(self.TrVeloToRect, self.camera.K, self.camera.width, self.camera.height)
         st = ctx.stream
         launches = 1
-        timed = mark is not None
         mark = mark or (lambda name: None)
         mark('begin')
         check(lib.lf_zero_counters(ctx.h, ptr(self.counters), self.counters.numel() * 4, st), ctx.h)
@@ -675,23 +671,17 @@ class FrameBatch:
                 mode = _mask_mode(self.masks, float_threshold)
                 mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
         bbox = self.packed.bbox if pre and not self.masks.raw else self.mask_bbox
-        if persistent and self.car_bits is None and getattr(self, '_native', None) is None:
-            split = timed and self.F and self.max_n        # time the persistent kernel apart from K6
+        flags = (_abi.FUSE_ORIENTED if use_oriented else 0) | (_abi.FUSE_EXACT if exact else 0)
+        if one_call and self.car_bits is None and getattr(self, '_native', None) is None:
             check(lib.lf_process_batch(
                 ctx.h, ptr(self.points), ptr(self.pt_off), ptr(mt) if raw else None, mode, len(mt) if raw else 0,
                 ptr(self.mask_off), se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
                 ptr(self.packed.words), ptr(bbox), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
-                self.F, self.max_n, self.max_m, self.max_b, float(max_depth), int(use_oriented), int(min_points),
+                self.F, self.max_n, self.max_m, self.max_b, float(max_depth), flags, int(min_points),
                 ptr(self.total), ptr(self.inside), ptr(self.n_in_box), ptr(self.n_valid),
-                None if split else ptr(self.best_idx), None if split else ptr(self.best_cnt),
-                None if split else ptr(self.agg), ptr(self.sched), st), ctx.h)
-            mark('batch')
-            if split:
-                check(lib.lf_car_stats(ctx.h, ptr(self.total), ptr(self.inside), ptr(self.mask_off),
-                                       ptr(self.box_off), ptr(self.cnt_off), self.F, int(min_points),
-                                       ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), st), ctx.h)
+                ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), None, st), ctx.h)
             mark('car_stats')
-            self.launches_per_run = 3 if (self.F and self.max_n) else (2 if raw else 1)
+            self.launches_per_run = 1 + (1 if raw else 0) + (2 if (self.F and self.max_n) else 0)
             return
         if raw:
             check(lib.lf_erode_pack(ctx.h, ptr(mt), mode, len(mt), self.camera.height, self.camera.width,
@@ -703,7 +693,7 @@ class FrameBatch:
             check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
                                     ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
                                     self.F, self.max_n, self.max_m, self.max_b, float(max_depth),
-                                    int(use_oriented), ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
+                                    flags, ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
                                     ptr(self.n_valid), ptr(self.car_bits), st), ctx.h)
             mark('fuse')
             check(lib.lf_car_stats(ctx.h, ptr(self.total), ptr(self.inside), ptr(self.mask_off),
@@ -781,9 +771,10 @@ class FrameBatch:
         out.copy_(self.counters, non_blocking=True)
         return out
 
-    def results(self):
-        """Host copies: dict of numpy arrays (one D2H of the counter block)."""
-        c = self.counters.cpu().numpy()
+    def results(self, host=None):
+        """Host copies: dict of numpy arrays (one D2H of the counter block, or the block
+        ``download()`` already brought over)."""
+        c = self.counters.cpu().numpy() if host is None else (host.numpy() if isinstance(host, torch.Tensor) else host)
         sm, sb, sc = int(self.h_mask_off[-1]), int(self.h_box_off[-1]), int(self.h_cnt_off[-1])
         o = self._o
         total = c[o:o + sm].astype(np.int64); o += sm
@@ -792,7 +783,7 @@ class FrameBatch:
         inside = c[o:o + sc].astype(np.int64)
         agg = c[self._nz:].view(np.int64).copy()
         return {'total': total, 'n_in_box': n_in_box, 'n_valid': n_valid, 'inside': inside, 'agg': agg,
-                'best_idx': self.best_idx.cpu().numpy()[:sm], 'best_cnt': self.best_cnt.cpu().numpy()[:sm]}
+                'best_idx': c[self._ob:self._ob + sm].copy(), 'best_cnt': c[self._ob + sm:self._ob + 2 * sm].copy()}
 
     def frame_stats(self, res, f, min_points=10, colors=None, extended=False):
         """The list of per-car dicts of frame f, as calculate_car_point_statistics

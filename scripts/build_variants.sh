@@ -1,5 +1,5 @@
 # Kernel experiments: objects of every source once, then one library per set of -D flags for the
-# point-pass sources.  usage: bash scripts/build_variants.sh name1 "-DLF_FUSE_SUB=512 -DLF_FUSE_STAGES=4" name2 "..."
+# point-pass sources.  usage: bash scripts/build_variants.sh name1 "-DLF_FUSE_PER=4 -DLF_FUSE_CTAS=3" name2 "..."
 # Libraries land in build/variants/liblidarfuse_<name>.so; run with LIDARFUSE_LIB=<path>.
 set -e
 cd "$(dirname "$0")/.."
@@ -12,9 +12,8 @@ wait
 while [ $# -ge 2 ]; do
   name=$1; defs=$2; shift 2
   nvcc $FLAGS $defs -c $C/fuse.cu -o $O/fuse_$name.o &
-  nvcc $FLAGS $defs -c $C/batch.cu -o $O/batch_$name.o &
   wait
-  nvcc -shared -o $O/liblidarfuse_$name.so $O/fuse_$name.o $O/batch_$name.o $O/ctx.o $O/project.o $O/erode.o $O/boxes2d.o \
+  nvcc -shared -o $O/liblidarfuse_$name.so $O/fuse_$name.o $O/ctx.o $O/project.o $O/erode.o $O/boxes2d.o \
     $O/resize.o $O/colour.o $O/csvfmt.o $O/packhost.o $O/points.o $O/synth.o $O/publish.o
   echo built $name "($defs)"
 done

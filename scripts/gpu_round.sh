@@ -9,7 +9,6 @@ timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo 
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 timeout 600 python bench.py --impl reference --steps 50 --warmup 3 > gpurun_out/bench_reference.json 2>> gpurun_out/bench.err; echo "ref rc=$?"
 timeout 600 python bench.py --workload cfg5 --steps 20 > gpurun_out/bench_cfg5.json 2>> gpurun_out/bench.err; echo "cfg5 rc=$?"
-timeout 600 python bench.py --persistent --no-cpu-baseline > gpurun_out/bench_persistent.json 2>> gpurun_out/bench.err; echo "persistent rc=$?"
 timeout 900 python bench_next.py > gpurun_out/bench_next.jsonl 2>> gpurun_out/bench.err; echo "next rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/launches.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-parity > gpurun_out/ncu_l.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'lf_erode_fast_kernel|lf_fuse_kernel' -s 4 -c 2 -o gpurun_out/full -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-parity --no-packed > gpurun_out/ncu_f.log 2>&1

@@ -26,7 +26,7 @@ def test_every_header_symbol_is_exported(lib):
     assert names == set(_abi.SIGNATURES), names ^ set(_abi.SIGNATURES)
     for n in names:
         assert getattr(lib, n) is not None
-    assert lib.lf_version() == 100
+    assert lib.lf_version() == 200
     assert lib.lf_strerror(0) == b'ok' and b'argument' in lib.lf_strerror(-1)
 
 

@@ -321,13 +321,13 @@ def test_persistent_batch_kernel_equals_separate_launches(LF, calib, golden, var
     u8 = (np.concatenate(masks) != 0).astype(np.uint8)
     batch = LF.FrameBatch(np.concatenate(pts), [len(p) for p in pts], u8, [len(m) for m in masks], corners,
                           [len(b) for b in boxes], cam, TVR)
-    batch.run(min_points=10, persistent=False, **kw)
+    batch.run(min_points=10, one_call=False, **kw)
     sep = batch.results()
     sep_packed = batch.packed.words.cpu().numpy().copy()
     sep_bbox = batch.mask_bbox.cpu().numpy().copy()
     batch.packed.words.zero_()
     for rep in range(3):                       # the queue is re-armed by the counter memset
-        batch.run(min_points=10, persistent=True, **kw)
+        batch.run(min_points=10, one_call=True, **kw)
         got = batch.results()
         for k in sep:
             assert np.array_equal(sep[k], got[k]), (k, rep)
@@ -349,9 +349,9 @@ def test_persistent_batch_kernel_many_frames(LF, calib):
     from lidar_object_detection_b200 import synthetic as S
     cam, TVC, TVR = calib
     sb = S.SyntheticBatch(300, cam, TVC, TVR, ncars=16, seed=99)
-    sb.batch.run(3, 1, 50, 10, True, persistent=False)
+    sb.batch.run(3, 1, 50, 10, True, one_call=False)
     sep = sb.batch.results()
-    sb.batch.run(3, 1, 50, 10, True, persistent=True)
+    sb.batch.run(3, 1, 50, 10, True, one_call=True)
     got = sb.batch.results()
     for k in sep:
         assert np.array_equal(sep[k], got[k]), k
@@ -578,7 +578,7 @@ def test_dense_stress_shape_cfg5(LF, calib):
     assert np.array_equal(res['inside'][:b.h_cnt_off[1]].reshape(64, sb.n_boxes[0]), want['inside'])
     assert _norm_stats(b.frame_stats(res, 0)) == _norm_stats(want['stats'])
     assert res['total'].sum() > 10000
-    b.run(7, 1, 50, 10, True, persistent=True)
+    b.run(7, 1, 50, 10, True, one_call=True)
     got = b.results()
     for k in res:
         assert np.array_equal(res[k], got[k]), k
@@ -605,6 +605,113 @@ def test_mask_bounding_boxes(LF):
                     assert bb[m].tolist() == [(1 << 20) - xs.min(), (1 << 20) - ys.min(), xs.max() + 1, ys.max() + 1]
 
 
+def test_point_pass_fp32_classification_equals_the_exact_mode(LF, calib, golden):
+    """The point pass decides most points from an fp32 residual test (fuse_body.cuh, stage 3) and
+    sends the rest through the float64 chain; LF_FUSE_EXACT sends everything through it.  Both
+    must give identical counters and membership bits: on the ragged real batch, on a synthetic
+    batch, and on an adversarial frame whose points sit on pixel-rounding ties, on the image
+    border and on the range gate (those must all land in the exact path and agree with numpy)."""
+    from lidar_object_detection_b200 import synthetic as S
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames']
+    pts, masks, boxes, raws = _batch_inputs(frames, cam, TVC, LF)
+    corners = np.concatenate([np.array([b['corners_velo'] for b in bs], dtype=np.float64).reshape(-1, 8, 3)
+                              for bs in boxes])
+    batch = LF.FrameBatch(np.concatenate(pts), [len(p) for p in pts], np.concatenate(masks),
+                          [len(m) for m in masks], corners, [len(b) for b in boxes], cam, TVR, want_car_bits=True)
+    for md in (50, 30):
+        batch.run(3, 1, md, 10, True)
+        fast, fbits = batch.results(), batch.car_bits.cpu().numpy().copy()
+        batch.car_bits.fill_(-1)
+        batch.run(3, 1, md, 10, True, exact=True)
+        ex = batch.results()
+        for k in fast:
+            assert np.array_equal(fast[k], ex[k]), (k, md)
+        assert np.array_equal(fbits, batch.car_bits.cpu().numpy())
+    sb = S.SyntheticBatch(24, cam, TVC, TVR, ncars=16, seed=99)
+    sb.batch.run(3, 1, 50, 10, True)
+    fast = sb.batch.results()
+    sb.batch.run(3, 1, 50, 10, True, exact=True)
+    ex = sb.batch.results()
+    for k in fast:
+        assert np.array_equal(fast[k], ex[k]), k
+    # adversarial frame: back-project pixel positions u + 0.5 + delta (ties and near-ties), the image
+    # border +-1 px and depths around the gate into the velodyne frame, round to float32
+    rng = np.random.default_rng(5)
+    n = 200000
+    K = np.asarray(cam.K)[:3, :3]
+    delta = rng.choice([0.0, 1e-7, -1e-7, 1e-5, -1e-5, 1e-3, -1e-3, 0.25], n)
+    u = rng.integers(-2, cam.width + 2, n) + 0.5 + delta
+    v = rng.integers(-2, cam.height + 2, n) + 0.5 + rng.choice([0.0, 1e-6, -1e-6, 0.3], n)
+    d = rng.choice([0.05, 0.5, 3.0, 12.0, 29.9999, 30.0, 30.0001, 49.99999, 50.0, 50.00001, 70.0, -5.0], n) \
+        * (1 + rng.choice([0.0, 1e-7, -1e-7], n))
+    cam_pts = np.stack([(u - K[0, 2]) * d / K[0, 0], (v - K[1, 2]) * d / K[1, 1], d, np.ones(n)])
+    velo = (np.linalg.inv(TVR) @ cam_pts).T.astype(np.float32)
+    velo[:, 3] = 0
+    full = np.ones((2, cam.height, cam.width), np.uint8)
+    full[1, ::2] = 0
+    c0 = np.array([b['corners_velo'] for b in boxes[0]], dtype=np.float64).reshape(-1, 8, 3)
+    adv = LF.FrameBatch(velo, [n], full, [2], c0, [len(c0)], cam, TVR, want_car_bits=True)
+    for md in (50, 30):
+        uu, vv, dd = P.project_points(velo, TVR, cam)
+        valid = P.filter_valid(uu, vv, dd, cam, md)
+        adv.run(0, 0, md, 10, True)
+        res = adv.results()
+        bits = adv.car_bits.cpu().numpy()
+        assert res['n_valid'][0] == valid.sum()
+        assert np.array_equal((bits & 1).astype(bool), valid)
+        assert np.array_equal(((bits >> 1) & 1).astype(bool), valid & (vv % 2 == 1))
+        assert res['total'].tolist() == [valid.sum(), (valid & (vv % 2 == 1)).sum()]
+        adv.run(0, 0, md, 10, True, exact=True)
+        ex = adv.results()
+        for k in res:
+            assert np.array_equal(res[k], ex[k]), (k, md)
+
+
+def test_point_pass_segment_tails_and_many_tiny_frames(LF, calib):
+    """Frame lengths around the CTA geometry (whole iterations, one point more, one less, a few
+    points) and a batch of more than 65 535 frames (several launches inside lf_fuse_batch):
+    totals equal the per-point membership bits and the numpy projection."""
+    cam, TVC, TVR = calib
+    pts0 = load_frame(100)
+    masks0 = standin(100, cam)[0][:3]
+    lens = [1, 31, 32, 33, 255, 256, 257, 2047, 2048, 2049, 4097, 16384, 16385, 20000]
+    pts = np.concatenate([pts0[20000:20000 + n] for n in lens])
+    masks = np.concatenate([masks0] * len(lens))
+    b = LF.FrameBatch(pts, lens, masks, [3] * len(lens), np.zeros((0, 8, 3)), [0] * len(lens), cam, TVR,
+                      want_car_bits=True)
+    b.run(0, 0, 50, 10, True)
+    res = b.results()
+    bits = b.car_bits.cpu().numpy()
+    o = 0
+    for f, n in enumerate(lens):
+        p = pts0[20000:20000 + n]
+        uu, vv, dd = P.project_points(p, TVR, cam)
+        valid = P.filter_valid(uu, vv, dd, cam, 50)
+        assert res['n_valid'][f] == valid.sum(), n
+        for c in range(3):
+            member = np.zeros(n, bool)
+            member[valid] = masks0[c][vv[valid], uu[valid]] > 0.5
+            assert np.array_equal(((bits[o:o + n] >> c) & 1).astype(bool), member), (n, c)
+            assert res['total'][3 * f + c] == member.sum()
+        o += n
+    # 70 000 frames of 40 points, one shared tiny mask set per frame is too much memory: no masks,
+    # one box per frame; n_valid and n_in_box per frame against numpy
+    F, n = 70000, 40
+    tiny = pts0[10300:10300 + n]
+    big = np.tile(tiny, (F, 1))
+    c0 = np.array(LF.transform_bboxes_to_velodyne(LF.filter_visible_bboxes(load_boxes(100), cam), TVC)[19]
+                  ['corners_velo']).reshape(1, 8, 3)
+    bb = LF.FrameBatch(big, [n] * F, None, [0] * F, np.tile(c0, (F, 1, 1)), [1] * F, cam, TVR)
+    bb.run(0, 0, 50, 10, True)
+    r = bb.results()
+    uu, vv, dd = P.project_points(tiny, TVR, cam)
+    valid = P.filter_valid(uu, vv, dd, cam, 50)
+    assert np.all(r['n_valid'] == valid.sum()) and valid.sum() > 0
+    nin = P.oriented_point_in_bbox(tiny[valid, :3], c0[0]).sum()
+    assert nin > 0 and np.all(r['n_in_box'] == nin)
+
+
 # ------------------------------------------------------------------ ragged / degenerate batches
 
 @pytest.mark.parametrize('persistent', [False, True])
@@ -626,7 +733,7 @@ def test_degenerate_frames_in_one_batch(LF, calib, persistent):
     corners = np.concatenate([c0, c0[:4], c0])
     n_boxes = [len(c0), 4, 0, len(c0), 0]
     batch = LF.FrameBatch(pts, n_pts, masks, n_masks, corners, n_boxes, cam, TVR)
-    batch.run(3, 1, 50, 10, True, persistent=persistent)
+    batch.run(3, 1, 50, 10, True, one_call=persistent)
     res = batch.results()
     want = P.process_frame(pts0, raw0, masks0, cam, TVC, TVR)
     M0 = len(masks0)
@@ -643,12 +750,12 @@ def test_degenerate_frames_in_one_batch(LF, calib, persistent):
     # empty batch and oversize frames
     e = LF.FrameBatch(np.zeros((0, 4), np.float32), [], np.zeros((0, cam.height, cam.width), np.uint8), [],
                       np.zeros((0, 8, 3)), [], cam, TVR)
-    e.run(persistent=persistent)
+    e.run(one_call=persistent)
     assert e.results()['total'].size == 0
     big = LF.FrameBatch(pts0[:1000], [1000], np.zeros((65, cam.height, cam.width), np.uint8), [65], c0[:1], [1], cam,
                         TVR)
     with pytest.raises(ValueError):
-        big.run(persistent=persistent)
+        big.run(one_call=persistent)
 
 
 def test_argument_errors_surface_as_python_exceptions(LF, calib):
@@ -751,7 +858,7 @@ def test_batch_from_packed_masks_equals_batch_from_uint8_masks(LF, calib):
     words = torch.from_numpy(IO.pack_masks(masks).view(np.int32)).cuda()
     for persistent in (False, True):
         b = LF.FrameBatch(pts, npts, LF.PackedMasks(words, cam.height, cam.width, raw=True), nm, corners, nb, cam, TVR)
-        b.run(3, 1, 50, 10, True, persistent=persistent)
+        b.run(3, 1, 50, 10, True, one_call=persistent)
         rb = b.results()
         for k in ra:
             assert np.array_equal(ra[k], rb[k]), (k, persistent)
