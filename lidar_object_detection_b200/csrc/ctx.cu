@@ -35,12 +35,29 @@ extern "C" int lf_create(lf_ctx** out, int device) {
         return LF_E_CUDA;
     }
     c->sm_count = sms > 0 ? sms : 148;
+    int prev = -1;
+    (void)cudaGetDevice(&prev);
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaMalloc((void**)&c->claim_ws, LF_CLAIM_SLOTS * sizeof(unsigned int)) != cudaSuccess) {
+        (void)cudaGetLastError();
+        if (prev >= 0) (void)cudaSetDevice(prev);
+        free(c);
+        return LF_E_CUDA;
+    }
+    if (prev >= 0) (void)cudaSetDevice(prev);
     *out = c;
     return LF_OK;
 }
 
 extern "C" int lf_destroy(lf_ctx* ctx) {
     if (!ctx) return LF_E_ARG;
+    if (ctx->claim_ws) {
+        int prev = -1;
+        (void)cudaGetDevice(&prev);
+        if (cudaSetDevice(ctx->device) == cudaSuccess) (void)cudaFree(ctx->claim_ws);
+        (void)cudaGetLastError();
+        if (prev >= 0) (void)cudaSetDevice(prev);
+    }
     free(ctx);
     return LF_OK;
 }
@@ -101,6 +118,11 @@ extern "C" int lf_set_camera(lf_ctx* ctx, const double TrVeloToRect[16], const d
     if ((double)ctx->cam.kT < kT) ctx->cam.kT = nextafterf(ctx->cam.kT, INFINITY);
     ctx->cam.gS = 3.2451855365842673e+32f;                 // 2^108
     ctx->cam.kTs = ctx->cam.kT * 3.0814879110195774e-33f;  // kT * 2^-108 (exact scaling; kT >= 2^-18 keeps it normal)
+    int tsx = 5, tsy = 3;                                   // 32 x 8 pixel tiles, coarser for large images
+    while ((int64_t)(((W - 1) >> tsx) + 1) * (((H - 1) >> tsy) + 1) > (int64_t)LF_MAP_TILE_WORDS * 32) {
+        if ((W >> tsx) >= (H >> tsy)) ++tsx; else ++tsy;
+    }
+    ctx->cam.tsx = tsx; ctx->cam.tsy = tsy; ctx->cam.ttw = ((W - 1) >> tsx) + 1;
     ctx->cam.cxm = (float)cxm;
     ctx->cam.cym = (float)cym;
     ctx->has_camera = 1;

@@ -1,24 +1,32 @@
 // K1+K4+K5 fused point pass (cvs_erosion.py:342-372 without the erosion): device code of
 // lf_fuse_kernel (fuse.cu).
 //
-// Register streaming, no shared-memory staging of the points and no CTA-level hand-off:
-//   phase A  every thread keeps PER independent 128-bit streaming loads in flight (a warp
-//            owns 32-point groups dealt round-robin over the CTA's warps), then classifies
-//            each group in fp32 in three stages of rising cost, each ended by a warp vote
-//            so that groups without a survivor stop early:
-//              1. depth row only                    -> behind the camera / beyond the range gate
-//              2. centred image rows                -> more than a pixel outside the image
-//              3. pixel = rint(x/d) in fp32 + a residual test that PROVES it equal to the
-//                 reference's float64 result        -> "certain" (pixel known) or "uncertain"
-//            Survivors are compacted (ballot + popc prefix) into two per-warp shared-memory
-//            queues: certain points with their pixel, uncertain ones for the exact chain.
+// Persistent, independent warps; register streaming; no CTA-level hand-off of any kind.
+//   claims   the batch is cut into claims of consecutive points of one frame; every warp of the
+//            (machine-filling) grid takes the next claim from one global counter until none is
+//            left, so warps never wait for each other and the load balances itself.
+//   phase A  per iteration a warp owns 32 * PER consecutive points; the PER 128-bit streaming loads
+//            of the NEXT iteration are issued before the current registers are looked at.  Each
+//            32-point group is classified in fp32 in two stages, each ended by a warp vote so that
+//            groups without a survivor stop early:
+//              1. depth row only          -> behind the camera / beyond the range gate
+//              2. centred image rows      -> more than a pixel outside the image
+//            Survivors ("candidates", ~17 % of an HDL-64 sweep) are compacted (ballot + popc
+//            prefix) into a per-warp shared-memory queue.
+//   stage 3  full 32-lane groups of candidates: pixel = rint(x/d) in fp32 plus a residual test
+//            that PROVES it equal to the reference's float64 result ("certain") or not
+//            ("uncertain" -> exact queue).  Certain points are looked up in the frame's
+//            prefilter map (lf_fuse_maps_kernel): only points whose pixel tile touches a mask's
+//            bounding box or whose xy cell / z touches a box's cull bounds can change a counter
+//            other than n_valid; they go to the work queue, the others are counted and dropped.
 //   exact    whenever 32 uncertain points are queued the warp runs the float64 dgemm-order
 //            chain and the two divisions on all 32 lanes (common.cuh) and moves the points
-//            that pass the gate of cvs_erosion.py:359 to the certain queue.
-//   phase B  full 32-lane groups of certain points: packed-mask gather (L2), box cull,
-//            float64 containment, ballot/popc counters in shared memory.
+//            that pass the gate of cvs_erosion.py:359 to the work queue.
+//   phase B  full 32-lane groups of the work queue: packed-mask gather (L2) behind a mask
+//            bounding-box cull, box cull, float64 containment, ballot/popc counts added to the
+//            global counters with one reduction-atomic per (car, box) and group.
 // Nothing fp32 ever decides a result: a point is "certain" only if the fp32 residual proves
-// the rounded pixel and the gate (error bounds below); everything else takes the exact path.
+// the rounded pixel and the gate (error bounds: lf_set_camera); everything else takes the exact path.
 #pragma once
 #include "common.cuh"
 
@@ -42,17 +50,15 @@ struct FuseArgs {
     float dmax_hi;       // smallest float >= max_depth (stage 1: certainly beyond the gate)
     float dmax_lo;       // largest float < max_depth    (stage 3: certainly inside the gate)
     int use_oriented;
-    int force_exact;     // verification mode: every surviving point takes the float64 chain
-    int smem_boxes;      // boxes staged in shared memory (max over frames)
-    int smem_cars;       // max masks per frame (<= LF_MAX_CARS)
-    int seg_points;      // points per CTA: a multiple of 32 * WARPS
+    int force_exact;     // verification mode: every candidate takes the float64 chain
+    int smem_boxes;      // per-warp cache of box cull bounds (max boxes over frames)
+    int smem_cars;       // per-warp cache of mask bounding boxes (max masks per frame, <= LF_MAX_CARS)
+    unsigned int* claim; // global claim counter, zeroed before the launch
+    const uint32_t* maps; // optional [F][LF_MAP_WORDS] prefilter maps, NULL = every valid point is looked at
+    int F;               // frames of this launch
+    int cpf;             // claims per frame = ceil(max points per frame / claim_points)
+    int claim_points;    // points per claim: a multiple of 32 * PER
 };
-
-__device__ __forceinline__ unsigned long long warp_or64(unsigned long long v) {
-    const unsigned lo = __reduce_or_sync(0xFFFFFFFFu, (unsigned)v);
-    const unsigned hi = __reduce_or_sync(0xFFFFFFFFu, (unsigned)(v >> 32));
-    return ((unsigned long long)hi << 32) | lo;
-}
 
 // warp-wide float min / max in one instruction (redux.sync.f32 is sm_100a-only; SASS CREDUX)
 __device__ __forceinline__ float warp_min_f32(float v) {
@@ -75,48 +81,69 @@ __device__ __forceinline__ float rcp_approx(float v) {
 // d/ee <= 1 <=> d <= ee and d/ee >= 0 <=> d >= 0 for ee > 0, except when a
 // negative d/ee underflows to -0 (which numpy accepts): that corner keeps the
 // division.  ee == 0 gives inf/nan in numpy -> outside.
-__device__ __forceinline__ bool slab(double rx, double ry, double rz, const double* e, double ee) {
-    double d = __dmul_rn(rx, e[0]);
-    d = __fma_rn(ry, e[1], d);
-    d = __fma_rn(rz, e[2], d);
+__device__ __forceinline__ bool slab(double rx, double ry, double rz, double e0, double e1, double e2, double ee) {
+    double d = __dmul_rn(rx, e0);
+    d = __fma_rn(ry, e1, d);
+    d = __fma_rn(rz, e2, d);
     if (!(ee > 0.0)) return false;
     if (d >= 0.0) return d <= ee;
     return __ddiv_rn(d, ee) >= 0.0;
 }
 
-__device__ __forceinline__ bool point_in_box(const lf_box& bx, float x, float y, float z, int oriented) {
+// One box read through the read-only path (all lanes the same address: one L1 transaction per load).
+__device__ __forceinline__ bool point_in_box(const lf_box* bx, float x, float y, float z, int oriented) {
     const double X = (double)x, Y = (double)y, Z = (double)z;
+    const double2* p = (const double2*)bx;                 // lf_box is 192 B, 16-B aligned in the array
     if (oriented) {
-        const double rx = X - bx.c0[0], ry = Y - bx.c0[1], rz = Z - bx.c0[2];
-        return slab(rx, ry, rz, bx.e1, bx.ee[0]) && slab(rx, ry, rz, bx.e2, bx.ee[1]) &&
-               slab(rx, ry, rz, bx.e3, bx.ee[2]);
+        const double2 a0 = __ldg(p), a1 = __ldg(p + 1), a2 = __ldg(p + 2), a3 = __ldg(p + 3), a4 = __ldg(p + 4),
+                      a5 = __ldg(p + 5), a6 = __ldg(p + 6), a7 = __ldg(p + 7);
+        const double rx = X - a0.x, ry = Y - a0.y, rz = Z - a1.x;                     // c0
+        return slab(rx, ry, rz, a1.y, a2.x, a2.y, a6.x) &&                            // e1, ee[0]
+               slab(rx, ry, rz, a3.x, a3.y, a4.x, a6.y) &&                            // e2, ee[1]
+               slab(rx, ry, rz, a4.y, a5.x, a5.y, a7.x);                              // e3, ee[2]
     }
-    return X >= bx.amin[0] && X <= bx.amax[0] && Y >= bx.amin[1] && Y <= bx.amax[1] && Z >= bx.amin[2] &&
-           Z <= bx.amax[2];
+    const double2 a7 = __ldg(p + 7), a8 = __ldg(p + 8), a9 = __ldg(p + 9), a10 = __ldg(p + 10);
+    return X >= a7.y && X <= a9.x && Y >= a8.x && Y <= a9.y && Z >= a8.y && Z <= a10.x;   // amin, amax
 }
 
-// Per-CTA shared state of one (frame, segment) work item.
-struct FuseShared {
-    int4* mbb;            // [smem_cars] mask bounding boxes {x0, y0, x1, y1}
-    lf_box* box;          // [smem_boxes]
-    float* cull;          // [6][smem_boxes] lo.x lo.y lo.z hi.x hi.y hi.z, one box per lane without bank conflicts
-    int32_t* inside;      // [smem_cars][smem_boxes]
-    int32_t* nin;         // [smem_boxes]
-    int32_t* total;       // [smem_cars]
-    int32_t* nvalid;      // [1]
+// What a warp knows about the frame it is working on (per-warp shared-memory caches + CSR entries).
+struct FuseFrame {
+    const int4* mbb;      // [M] mask bounding boxes {x0, y0, x1, y1} (shared memory)
+    const float* cull;    // [6][SB] lo.x lo.y lo.z hi.x hi.y hi.z of the frame's boxes (shared memory, one box per lane)
+    int SB;
+    int M, B;
+    const uint32_t* mask_base;
+    const lf_box* boxes;
+    int32_t* total;       // global counters of this frame
+    int32_t* inside;
+    int32_t* nin;
+    const uint32_t* fmap; // prefilter map of the frame (NULL: none) and its header
+    float gx0, gy0, ginvx, ginvy, gz0, gz1;
 };
 
-// ---- phase B: 32 certain points, one per lane (`have` false only in a warp's last, partial group).
+// counts of one 32-mask block: one reduction-atomic per car present in the group
+__device__ __forceinline__ void add_per_car(unsigned blk, bool pred, int32_t* dst, int stride, int lane) {
+    unsigned un = __reduce_or_sync(0xFFFFFFFFu, pred ? blk : 0u);
+    while (un) {
+        const int c = __ffs((int)un) - 1;
+        un &= un - 1;
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, pred && ((blk >> c) & 1u));
+        if (lane == 0) atomicAdd(dst + (int64_t)c * stride, __popc(bal));
+    }
+}
+
+// ---- phase B: 32 work-queue points, one per lane (`have` false only in a claim's last, partial group).
 // e = {x, y, z, bits(u | v << 16)}.  Returns the lane's membership bits.
-__device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const FuseArgs& A, const FuseShared& S,
-                                                         float4 e, bool have, int lane, int M, int B,
-                                                         const uint32_t* mask_base, int plane32) {
+__device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const FuseArgs& A, const FuseFrame& Fr,
+                                                      float4 e, bool have, int plane32) {
     const unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
     const unsigned uv = __float_as_uint(e.w);
     const int ui = (int)(uv & 0xFFFFu), vi = (int)(uv >> 16);
+    const int M = Fr.M, B = Fr.B;
     // ---- K4: point-in-mask gather (cvs_erosion.py:152-160).  Lanes first test the masks' bounding
     // boxes against the pixel bounds of the group (one mask per lane); only surviving masks are read.
-    unsigned long long bits = 0ULL;
+    unsigned blk[2] = {0u, 0u};                              // membership bits, masks 0..31 and 32..63
     if (M > 0) {
         const int off = vi * cam.wpr + (ui >> 5);            // word offset inside one packed mask
         const int sh = ui & 31;
@@ -124,14 +151,18 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
         const int u1 = __reduce_max_sync(FULL, have ? ui : -1);
         const int v0 = __reduce_min_sync(FULL, have ? vi : 0x7fffffff);
         const int v1 = __reduce_max_sync(FULL, have ? vi : -1);
-        for (int g = 0; g < M; g += 32) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int g = 32 * h;
+            if (g >= M) break;
             const int cl = g + lane;
             bool cand = false;
             if (cl < M) {
-                const int4 bb = S.mbb[cl];
+                const int4 bb = Fr.mbb[cl];
                 cand = u1 >= bb.x && u0 <= bb.z && v1 >= bb.y && v0 <= bb.w;
             }
             unsigned cmask = __ballot_sync(FULL, cand);
+            unsigned acc = 0u;
             // up to four candidate masks per round: their words are requested together, so a
             // group pays one L2 round trip, not one per mask
             while (cmask) {
@@ -139,37 +170,33 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
                 uint32_t w[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    c[j] = cmask ? g + __ffs((int)cmask) - 1 : -1;
+                    c[j] = cmask ? __ffs((int)cmask) - 1 : -1;
                     cmask &= cmask - 1;
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                    w[j] = (have && c[j] >= 0) ? __ldg(mask_base + (unsigned)(off + c[j] * plane32)) : 0u;
+                    w[j] = (have && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off + (g + c[j]) * plane32)) : 0u;
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                    if (c[j] >= 0) bits |= (unsigned long long)((w[j] >> sh) & 1u) << c[j];
+                    if (c[j] >= 0) acc |= ((w[j] >> sh) & 1u) << c[j];
             }
-        }
-        unsigned long long un = warp_or64(bits);
-        while (un) {
-            const int c = __ffsll((long long)un) - 1;
-            un &= un - 1;
-            const unsigned bal = __ballot_sync(FULL, (bits >> c) & 1ULL);
-            if (lane == 0) atomicAdd(&S.total[c], __popc(bal));
+            blk[h] = acc;
+            add_per_car(acc, true, Fr.total + g, 1, lane);
         }
     }
+    const unsigned long long bits = ((unsigned long long)blk[1] << 32) | blk[0];
     if (B == 0) return bits;
     // ---- bounding box of the group's points, then lanes test the boxes' cull bounds in parallel
     const float INF = __int_as_float(0x7f800000);
     const float wx0 = warp_min_f32(have ? e.x : INF), wx1 = warp_max_f32(have ? e.x : -INF);
     const float wy0 = warp_min_f32(have ? e.y : INF), wy1 = warp_max_f32(have ? e.y : -INF);
     const float wz0 = warp_min_f32(have ? e.z : INF), wz1 = warp_max_f32(have ? e.z : -INF);
-    const int SB = A.smem_boxes;
+    const int SB = Fr.SB;
     for (int g = 0; g < B; g += 32) {
         const int bl = g + lane;
         bool cand = false;
         if (bl < B) {
-            const float* cu = S.cull + bl;
+            const float* cu = Fr.cull + bl;
             cand = wx1 >= cu[0] && wx0 <= cu[3 * SB] && wy1 >= cu[SB] && wy0 <= cu[4 * SB] && wz1 >= cu[2 * SB] &&
                    wz0 <= cu[5 * SB];
         }
@@ -178,20 +205,16 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
         while (cmask) {
             const int b = g + __ffs((int)cmask) - 1;
             cmask &= cmask - 1;
-            const lf_box& bx = S.box[b];
-            const bool near = have && e.x >= bx.lo[0] && e.x <= bx.hi[0] && e.y >= bx.lo[1] && e.y <= bx.hi[1] &&
-                              e.z >= bx.lo[2] && e.z <= bx.hi[2];
-            const bool in = near && point_in_box(bx, e.x, e.y, e.z, A.use_oriented);
+            const float* cu = Fr.cull + b;
+            const bool near = have && e.x >= cu[0] && e.x <= cu[3 * SB] && e.y >= cu[SB] && e.y <= cu[4 * SB] &&
+                              e.z >= cu[2 * SB] && e.z <= cu[5 * SB];
+            if (!__any_sync(FULL, near)) continue;
+            const bool in = near && point_in_box(Fr.boxes + b, e.x, e.y, e.z, A.use_oriented);
             const unsigned bal = __ballot_sync(FULL, in);
             if (!bal) continue;
-            if (lane == 0) atomicAdd(&S.nin[b], __popc(bal));
-            unsigned long long un2 = warp_or64(in ? bits : 0ULL);
-            while (un2) {
-                const int c = __ffsll((long long)un2) - 1;
-                un2 &= un2 - 1;
-                const unsigned bb = __ballot_sync(FULL, in && ((bits >> c) & 1ULL));
-                if (lane == 0) atomicAdd(&S.inside[c * SB + b], __popc(bb));
-            }
+            if (lane == 0) atomicAdd(Fr.nin + b, __popc(bal));
+            add_per_car(blk[0], in, Fr.inside + b, B, lane);
+            if (M > 32) add_per_car(blk[1], in, Fr.inside + (int64_t)32 * B + b, B, lane);
         }
     }
     return bits;
@@ -199,11 +222,11 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
 
 // ---- exact path: up to 32 queued uncertain points (one per lane) through the float64 dgemm-order
 // chain and the two divisions (common.cuh); points that pass the gate of cvs_erosion.py:359 are
-// appended to the certain queue.  Rare (a few per cent of the survivors), hence not inlined into
-// the eight unrolled classification stages.  Returns the new fill of the certain queue.
+// appended to the work queue.  Rare (a few per cent of the candidates).  Returns the new fill of
+// the work queue.
 template <bool BITS>
 __device__ __noinline__ int fuse_resolve(const LfCam& cam, const FuseArgs& A, const float4* uq, int cnt, float4* q,
-                                         int* qi, int qn, int64_t seg0, int npts) {
+                                         int* qi, int qn, int64_t seg0) {
     __syncwarp();
     const int lane = threadIdx.x & 31;
     const bool have = lane < cnt;
@@ -216,194 +239,235 @@ __device__ __noinline__ int fuse_resolve(const LfCam& cam, const FuseArgs& A, co
         const int pos = qn + __popc(mk & ((1u << lane) - 1u));
         q[pos] = make_float4(e.x, e.y, e.z, __uint_as_float((unsigned)(int)uqd | ((unsigned)(int)vqd << 16)));
         if (BITS) qi[pos] = __float_as_int(e.w);
-    } else if (BITS && have && __float_as_int(e.w) < npts) {
+    } else if (BITS && have) {
         A.car_bits[seg0 + __float_as_int(e.w)] = 0ULL;
     }
     __syncwarp();
     return qn + __popc(mk);
 }
 
-// One CTA = (frame f, segment `seg` of A.seg_points points).
-//   WARPS  warps per CTA, all of them stream and consume
-//   PER    128-bit loads in flight per thread and iteration (an iteration covers WARPS*PER*32 points)
-//   BITS   per-point membership output (car_bits) wanted: queues carry the point index too
+// Geometry of one warp's working set.
+//   WARPS  warps per CTA (independent workers; the CTA only shares the shared-memory allocation)
+//   PER    128-bit loads in flight per thread and iteration (an iteration covers PER*32 consecutive points)
+//   BITS   per-point membership output (car_bits) wanted: the work queue carries the point index too
 template <int WARPS, int PER, bool BITS>
 struct FuseGeom {
     static constexpr int NT = 32 * WARPS;
-    static constexpr int SPAN = WARPS * PER * 32;          // points per iteration
-    static constexpr int QCAP = PER * 32 + 64;             // certain queue: < 32 left over + PER*32 new + < 32 resolved
+    static constexpr int SPAN = PER * 32;                  // points per iteration of one warp
+    static constexpr int CCAP = PER * 32 + 32;             // candidates (4-byte indices): < 32 left over + PER*32 new
+    static constexpr int QCAP = 64;                        // work queue: < 32 left over + 32 new (drained first)
     static constexpr int UCAP = 64;                        // uncertain queue: < 32 left over + 32 new
-    static constexpr size_t warp_bytes = (size_t)(QCAP + UCAP) * 16 + (BITS ? (size_t)QCAP * 4 : 0);
-    static constexpr size_t queue_bytes = warp_bytes * WARPS;
+    static constexpr size_t queue_bytes = (size_t)(QCAP + UCAP) * 16 + (size_t)CCAP * 4 + (BITS ? (size_t)QCAP * 4 : 0);
+    // + per-warp frame cache: mask bounding boxes (16 B each) and box cull bounds (24 B each)
+    static __host__ __device__ size_t warp_bytes(int cars, int boxes) {
+        return (queue_bytes + sizeof(FuseFrame) + 16 * (size_t)cars + 24 * (size_t)boxes + 24 + 15) & ~(size_t)15;
+    }
 };
 
-__host__ __device__ inline size_t fuse_state_bytes(int cars, int boxes) {
-    // mbb + lf_box + cull + counters (inside, nin, total, nvalid + pad)
-    return 16 * (size_t)cars + (size_t)boxes * sizeof(lf_box) + 24 * (size_t)boxes +
-           4 * ((size_t)cars * boxes + boxes + cars + 4);
+template <int PER>
+__device__ __forceinline__ void fuse_load(float4 (&P)[PER], const float4* src, int base, int npts) {
+    const int k0 = base + (int)(threadIdx.x & 31);
+    if (base + 32 * PER <= npts) {                          // whole iteration inside the claim
+#pragma unroll
+        for (int j = 0; j < PER; ++j) P[j] = ld_stream_f4(src + k0 + 32 * j);
+    } else {                                                // dead lanes are masked by `k < npts` in stage 1
+#pragma unroll
+        for (int j = 0; j < PER; ++j)
+            P[j] = k0 + 32 * j < npts ? ld_stream_f4(src + k0 + 32 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 }
 
 template <int WARPS, int PER, bool BITS>
-__device__ __forceinline__ void fuse_segment(const LfCam& cam, const FuseArgs& A, int f, int seg, uint8_t* smem) {
+__device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs& A, uint8_t* smem) {
     using G = FuseGeom<WARPS, PER, BITS>;
-    constexpr int NT = G::NT, SPAN = G::SPAN, QCAP = G::QCAP, UCAP = G::UCAP;
+    constexpr int SPAN = G::SPAN, CCAP = G::CCAP, QCAP = G::QCAP, UCAP = G::UCAP;
     const unsigned FULL = 0xFFFFFFFFu;
-    const int64_t p0 = A.pt_off[f], p1 = A.pt_off[f + 1];
-    const int64_t seg0 = p0 + (int64_t)seg * A.seg_points;
-    if (seg0 >= p1) return;
-    const int npts = (int)min((int64_t)A.seg_points, p1 - seg0);
-    const int m0 = A.mask_off[f];
-    const int M = A.mask_off[f + 1] - m0;
-    const int b0 = A.box_off[f];
-    const int B = A.box_off[f + 1] - b0;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    // ---- shared memory: per-warp queues, then the frame state
-    uint8_t* wq = smem + (size_t)warp * G::warp_bytes;
-    float4* q = (float4*)wq;                               // [QCAP] certain: x, y, z, bits(u | v << 16)
-    float4* uq = q + QCAP;                                 // [UCAP] uncertain: x, y, z, bits(index in segment)
-    int* qi = (int*)(uq + UCAP);                           // [QCAP] index in segment of the certain entries (BITS)
-    FuseShared S;
-    S.mbb = (int4*)(smem + G::queue_bytes);
-    S.box = (lf_box*)(S.mbb + A.smem_cars);
-    S.cull = (float*)((uint8_t*)S.box + (size_t)A.smem_boxes * sizeof(lf_box));
-    S.inside = (int32_t*)(S.cull + 6 * (size_t)A.smem_boxes);
-    S.nin = S.inside + (size_t)A.smem_cars * A.smem_boxes;
-    S.total = S.nin + A.smem_boxes;
-    S.nvalid = S.total + A.smem_cars;
-    {   // stage the frame's boxes and mask bounding boxes, clear the private counters
-        const double* gsrc = (const double*)(A.boxes + b0);
-        double* sdst = (double*)S.box;
-        const int nd = B * (int)(sizeof(lf_box) / 8);
-        for (int i = threadIdx.x; i < nd; i += NT) sdst[i] = gsrc[i];
-        for (int i = threadIdx.x; i < 6 * B; i += NT) {
-            const int k = i / B, b = i - k * B;
-            const lf_box* gb = A.boxes + b0 + b;
-            S.cull[k * A.smem_boxes + b] = k < 3 ? gb->lo[k] : gb->hi[k - 3];
-        }
-        const int nc = A.smem_cars * A.smem_boxes + A.smem_boxes + A.smem_cars + 1;
-        for (int i = threadIdx.x; i < nc; i += NT) S.inside[i] = 0;
-        for (int c = threadIdx.x; c < M; c += NT) {
-            int4 bb = make_int4(0, 0, cam.W - 1, cam.H - 1);
-            if (A.mask_bbox) {                             // record of lf_erode_pack: zeros = empty mask
-                const int4 r = __ldg((const int4*)A.mask_bbox + m0 + c);
-                bb = make_int4((1 << 20) - r.x, (1 << 20) - r.y, r.z - 1, r.w - 1);
-            }
-            S.mbb[c] = bb;
-        }
-    }
-    __syncthreads();
+    uint8_t* ws = smem + (size_t)warp * G::warp_bytes(A.smem_cars, A.smem_boxes);
+    float4* q = (float4*)ws;                               // [QCAP] work queue: x, y, z, bits(u | v << 16)
+    float4* uq = q + QCAP;                                 // [UCAP] uncertain: x, y, z, bits(index in claim)
+    FuseFrame& Fr = *(FuseFrame*)(uq + UCAP);               // frame state lives in shared memory, not in registers
+    int4* s_mbb = (int4*)((uint8_t*)(uq + UCAP) + ((sizeof(FuseFrame) + 15) & ~(size_t)15));   // [smem_cars]
+    float* s_cull = (float*)(s_mbb + A.smem_cars);         // [6][smem_boxes]
+    int* cq = (int*)(s_cull + 6 * (size_t)A.smem_boxes);   // [CCAP] candidates: index in claim (the point is re-read, an L2 hit)
+    int* qi = cq + CCAP;                                   // [QCAP] index in claim of the work-queue entries (BITS)
 
     const int plane32 = cam.H * cam.wpr;                   // words per packed mask (< 2^25, see lf_set_camera)
-    const uint32_t* mask_base = A.packed + (int64_t)m0 * plane32;
-    const float4* src = A.pts + seg0;
     const unsigned lt = (1u << lane) - 1u;
-    // fp32 classification constants (lf_set_camera; error analysis there and in DESIGN.md section 4)
+    // fp32 classification constants (lf_set_camera)
     const float kT = cam.kT, kTs = cam.kTs, gS = cam.gS, hwx = cam.hwx, hwy = cam.hwy;
     const float cxm = cam.cxm, cym = cam.cym, umax = (float)(cam.W - 1), vmax = (float)(cam.H - 1);
     const float dhi = A.dmax_hi, dlo = A.dmax_lo;
     const bool fast = !A.force_exact;
-    int qn = 0, un = 0;                                    // queue fill, warp-uniform
-    int nval = 0;                                          // certain points consumed by this warp
+    const unsigned n_claims = (unsigned)A.F * (unsigned)A.cpf;
+    const int tsx = cam.tsx, tsy = cam.tsy, ttw = cam.ttw;
 
-    // the exact chain on up to 32 queued uncertain points; survivors join the certain queue
-    auto resolve = [&](int cnt) {
-        qn = fuse_resolve<BITS>(cam, A, uq + (un - cnt), cnt, q, qi, qn, seg0, npts);
-        un -= cnt;
-    };
-    // phase B on the last 32 (or fewer, at the very end) entries of the certain queue
-    auto consume = [&](int cnt) {
-        const bool have = lane < cnt;
-        const int at = qn - cnt + (have ? lane : 0);
-        const float4 e = q[at];
-        const unsigned long long bits = fuse_group(cam, A, S, e, have, lane, M, B, mask_base, plane32);
-        if (BITS && have) A.car_bits[seg0 + qi[at]] = bits;
-        nval += cnt;
-        qn -= cnt;
-    };
+    int cur_f = -1;
 
-    const int niter = (npts + SPAN - 1) / SPAN;
-    for (int it = 0;; ++it) {
-        const bool last = it == niter;                      // pseudo-iteration: flush both queues
-        if (!last) {
-            const int kbase = it * SPAN + warp * 32 + lane; // group j of this warp: kbase + j * NT
-            float4 P[PER];
-            if (it * SPAN + SPAN <= npts) {
-#pragma unroll
-                for (int j = 0; j < PER; ++j) P[j] = ld_stream_f4(src + kbase + j * NT);
-            } else {
-                const float qnan = __int_as_float(0x7fc00000);   // dead lanes: NaN takes the exact path and fails there
-#pragma unroll
-                for (int j = 0; j < PER; ++j)
-                    P[j] = kbase + j * NT < npts ? ld_stream_f4(src + kbase + j * NT) : make_float4(qnan, qnan, qnan, 0.f);
+    unsigned id = 0;
+    if (lane == 0) id = atomicAdd(A.claim, 1u);
+    id = __shfl_sync(FULL, id, 0);
+    while (id < n_claims) {
+        unsigned nxt = 0;
+        if (lane == 0) nxt = atomicAdd(A.claim, 1u);        // next claim requested now, consumed after this one
+        const int f = (int)(id / (unsigned)A.cpf);
+        const int64_t c0 = (int64_t)(id - (unsigned)f * (unsigned)A.cpf) * A.claim_points;
+        const int64_t p0 = A.pt_off[f], nf = A.pt_off[f + 1] - p0;
+        if (c0 < nf) {
+            const int npts = (int)min((int64_t)A.claim_points, nf - c0);
+            const int64_t seg0 = p0 + c0;
+            const float4* src = A.pts + seg0;
+            if (f != cur_f) {                               // frame state into the warp's cache
+                cur_f = f;
+                const int m0 = A.mask_off[f], b0 = A.box_off[f];
+                const int M = A.mask_off[f + 1] - m0, B = A.box_off[f + 1] - b0;
+                __syncwarp();
+                if (lane == 0) {
+                    Fr.mbb = s_mbb; Fr.cull = s_cull; Fr.SB = A.smem_boxes;
+                    Fr.M = M; Fr.B = B;
+                    Fr.mask_base = A.packed + (int64_t)m0 * plane32;
+                    Fr.boxes = A.boxes + b0;
+                    Fr.total = A.total + m0;
+                    Fr.nin = A.n_in_box + b0;
+                    Fr.inside = A.inside + A.cnt_off[f];
+                    Fr.fmap = nullptr;
+                    if (A.maps) {
+                        const uint32_t* fm = A.maps + (size_t)f * LF_MAP_WORDS;
+                        const float4 h0 = __ldg((const float4*)fm);
+                        const float2 h1 = __ldg((const float2*)fm + 2);
+                        Fr.fmap = fm;
+                        Fr.gx0 = h0.x; Fr.gy0 = h0.y; Fr.ginvx = h0.z; Fr.ginvy = h0.w; Fr.gz0 = h1.x; Fr.gz1 = h1.y;
+                    }
+                }
+                for (int c = lane; c < M; c += 32) {
+                    int4 bb = make_int4(0, 0, cam.W - 1, cam.H - 1);
+                    if (A.mask_bbox) {                      // record of lf_erode_pack: zeros = empty mask
+                        const int4 r = __ldg((const int4*)A.mask_bbox + m0 + c);
+                        bb = make_int4((1 << 20) - r.x, (1 << 20) - r.y, r.z - 1, r.w - 1);
+                    }
+                    s_mbb[c] = bb;
+                }
+                for (int b = lane; b < B; b += 32) {
+                    const float2* lh = (const float2*)(A.boxes[b0 + b].lo);    // lo[3], hi[3]: 8-B aligned
+                    const float2 t0 = __ldg(lh), t1 = __ldg(lh + 1), t2 = __ldg(lh + 2);
+                    s_cull[b] = t0.x; s_cull[A.smem_boxes + b] = t0.y; s_cull[2 * A.smem_boxes + b] = t1.x;
+                    s_cull[3 * A.smem_boxes + b] = t1.y; s_cull[4 * A.smem_boxes + b] = t2.x;
+                    s_cull[5 * A.smem_boxes + b] = t2.y;
+                }
+                __syncwarp();
             }
+            int cn = 0, qn = 0, un = 0;                     // queue fills, warp-uniform
+            int nval = 0;                                   // gate-valid points seen in this claim
+            const int niter = (npts + SPAN - 1) / SPAN;
+            for (int it = 0;; ++it) {
+                const bool last = it == niter;              // pseudo-iteration: flush the queues
+                if (!last) {
+                    float4 P[PER];
+                    fuse_load<PER>(P, src, it * SPAN, npts);
 #pragma unroll
-            for (int j = 0; j < PER; ++j) {
-                const float4 p = P[j];
-                const int k = kbase + j * NT;
-                // ---- stage 1: depth row.  tol bounds every fp32 evaluation error of this point
-                // (+inf beyond 2^20 m and for NaN / inf input: such points are never decided here).
-                const float d = fmaf(cam.Pg[8], p.x, fmaf(cam.Pg[9], p.y, fmaf(cam.Pg[10], p.z, cam.Pg[11])));
-                const float tol = fmaf((fabsf(p.x) + fabsf(p.y) + fabsf(p.z)) * gS, kTs, kT);
-                const bool okd = !(d < -tol) & !(d > dhi + tol);     // NaN stays in
-                if (!__any_sync(FULL, okd)) {
-                    if (BITS && k < npts) A.car_bits[seg0 + k] = 0ULL;
-                    continue;
+                    for (int j = 0; j < PER; ++j) {
+                        const float4 p = P[j];
+                        const int k = it * SPAN + 32 * j + lane;
+                        // ---- stage 1: depth row.  tol bounds every fp32 evaluation error of this point
+                        // (+inf beyond 2^20 m and for NaN / inf input: such points are never decided here).
+                        const float d = fmaf(cam.Pg[8], p.x, fmaf(cam.Pg[9], p.y, fmaf(cam.Pg[10], p.z, cam.Pg[11])));
+                        const float tol = fmaf((fabsf(p.x) + fabsf(p.y) + fabsf(p.z)) * gS, kTs, kT);
+                        const bool okd = !(d < -tol) & !(d > dhi + tol) & (k < npts);     // NaN stays in
+                        bool maybe = false;
+                        if (__any_sync(FULL, okd)) {
+                            // ---- stage 2: centred image rows, one pixel of margin
+                            const float x = fmaf(cam.Pg[0], p.x, fmaf(cam.Pg[1], p.y, fmaf(cam.Pg[2], p.z, cam.Pg[3])));
+                            const float y = fmaf(cam.Pg[4], p.x, fmaf(cam.Pg[5], p.y, fmaf(cam.Pg[6], p.z, cam.Pg[7])));
+                            maybe = okd & !(fabsf(x) > fmaf(hwx, d, tol)) & !(fabsf(y) > fmaf(hwy, d, tol));
+                            const unsigned mm = __ballot_sync(FULL, maybe);
+                            if (maybe) cq[cn + __popc(mm & lt)] = k;
+                            cn += __popc(mm);
+                        }
+                        if (BITS && !maybe && k < npts) A.car_bits[seg0 + k] = 0ULL;
+                    }
                 }
-                // ---- stage 2: centred image rows, one pixel of margin
-                const float x = fmaf(cam.Pg[0], p.x, fmaf(cam.Pg[1], p.y, fmaf(cam.Pg[2], p.z, cam.Pg[3])));
-                const float y = fmaf(cam.Pg[4], p.x, fmaf(cam.Pg[5], p.y, fmaf(cam.Pg[6], p.z, cam.Pg[7])));
-                const bool maybe = okd & !(fabsf(x) > fmaf(hwx, d, tol)) & !(fabsf(y) > fmaf(hwy, d, tol));
-                if (!__any_sync(FULL, maybe)) {
-                    if (BITS && k < npts) A.car_bits[seg0 + k] = 0ULL;
-                    continue;
-                }
-                // ---- stage 3: pixel in fp32, proven by the residual |x - (u - cx) d| < d/2 - tol
-                const float r = rcp_approx(d);
-                const float ru = rintf(fmaf(x, r, cxm)), rv = rintf(fmaf(y, r, cym));
-                const float half = fmaf(0.5f, d, -tol);
-                const bool sure = (fabsf(fmaf(cxm - ru, d, x)) < half) & (fabsf(fmaf(cym - rv, d, y)) < half) &
-                                  (ru >= 0.f) & (ru <= umax) & (rv >= 0.f) & (rv <= vmax) &
-                                  (d - tol > 0.f) & (d + tol < dlo) & fast;
-                const bool certain = maybe & sure, unsure = maybe & !sure;
-                const unsigned mc = __ballot_sync(FULL, certain), mu = __ballot_sync(FULL, unsure);
-                if (certain) {
-                    const int pos = qn + __popc(mc & lt);
-                    q[pos] = make_float4(p.x, p.y, p.z, __uint_as_float((unsigned)(int)ru | ((unsigned)(int)rv << 16)));
-                    if (BITS) qi[pos] = k;
-                }
-                qn += __popc(mc);
-                if (BITS && !maybe && k < npts) A.car_bits[seg0 + k] = 0ULL;
-                if (mu) {
+                __syncwarp();
+                // ---- drain the queues: full 32-lane groups only, except at the end of the claim.  One
+                // instance of each step in the code; every condition is warp-uniform.
+                for (;;) {
+                    if (qn >= 32 || (last && cn == 0 && un == 0 && qn > 0)) {
+                        // ---- phase B
+                        const int n = min(qn, 32);
+                        qn -= n;
+                        const bool hv = lane < n;
+                        const int at = qn + (hv ? lane : 0);
+                        const float4 e = q[at];
+                        const unsigned long long bits = fuse_group(cam, A, Fr, e, hv, plane32);
+                        if (BITS && hv) A.car_bits[seg0 + qi[at]] = bits;
+                        nval += n;
+                        __syncwarp();
+                        continue;
+                    }
+                    if (un >= 32 || (last && cn == 0 && un > 0)) {
+                        // ---- exact path
+                        const int n = min(un, 32);
+                        un -= n;
+                        qn = fuse_resolve<BITS>(cam, A, uq + un, n, q, qi, qn, seg0);
+                        continue;
+                    }
+                    if (!(cn >= 32 || (last && cn > 0))) break;
+                    // ---- stage 3: pixel in fp32, proven by the residual |x - (u - cx) d| < d/2 - tol
+                    const int cnt = min(cn, 32);
+                    cn -= cnt;
+                    const bool have = lane < cnt;
+                    const int k = cq[cn + (have ? lane : 0)];
+                    const float4 p = __ldg(src + k);        // read a moment ago: an L2 hit
+                    const float d = fmaf(cam.Pg[8], p.x, fmaf(cam.Pg[9], p.y, fmaf(cam.Pg[10], p.z, cam.Pg[11])));
+                    const float x = fmaf(cam.Pg[0], p.x, fmaf(cam.Pg[1], p.y, fmaf(cam.Pg[2], p.z, cam.Pg[3])));
+                    const float y = fmaf(cam.Pg[4], p.x, fmaf(cam.Pg[5], p.y, fmaf(cam.Pg[6], p.z, cam.Pg[7])));
+                    const float tol = fmaf((fabsf(p.x) + fabsf(p.y) + fabsf(p.z)) * gS, kTs, kT);
+                    const float r = rcp_approx(d);
+                    const float ru = rintf(fmaf(x, r, cxm)), rv = rintf(fmaf(y, r, cym));
+                    const float half = fmaf(0.5f, d, -tol);
+                    const bool sure = (fabsf(fmaf(cxm - ru, d, x)) < half) & (fabsf(fmaf(cym - rv, d, y)) < half) &
+                                      (ru >= 0.f) & (ru <= umax) & (rv >= 0.f) & (rv <= vmax) &
+                                      (d - tol > 0.f) & (d + tol < dlo) & fast;
+                    bool certain = have & sure;
+                    const bool unsure = have & !sure;
+                    const uint32_t* fmap = Fr.fmap;
+                    if (fmap) {
+                        const float gx0 = Fr.gx0, gy0 = Fr.gy0, ginvx = Fr.ginvx, ginvy = Fr.ginvy, gz0 = Fr.gz0, gz1 = Fr.gz1;
+                        // prefilter: a certain point is looked at only if its pixel tile touches a mask's
+                        // bounding box or its xy cell (and z) touches a box's cull bounds; the others are
+                        // gate-valid points that can change no counter but n_valid
+                        const int ui = certain ? (int)ru : 0, vi = certain ? (int)rv : 0;
+                        const int t = (vi >> tsy) * ttw + (ui >> tsx);
+                        const unsigned wt = __ldg(fmap + 8 + LF_MAP_GRID_WORDS + (t >> 5));
+                        int ix = __float2int_rd(__fmul_rn(__fsub_rn(p.x, gx0), ginvx));
+                        int iy = __float2int_rd(__fmul_rn(__fsub_rn(p.y, gy0), ginvy));
+                        const bool inr = certain & (ix >= 0) & (ix <= LF_MAP_GRID) & (iy >= 0) & (iy <= LF_MAP_GRID) &
+                                         (p.z >= gz0) & (p.z <= gz1);
+                        ix = inr ? min(ix, LF_MAP_GRID - 1) : 0;
+                        iy = inr ? min(iy, LF_MAP_GRID - 1) : 0;
+                        const unsigned wg = __ldg(fmap + 8 + iy * (LF_MAP_GRID / 32) + (ix >> 5));
+                        const bool need = (((wt >> (t & 31)) & 1u) != 0u) | (inr & (((wg >> (ix & 31)) & 1u) != 0u));
+                        const bool skip = certain & !need;
+                        nval += __popc(__ballot_sync(FULL, skip));
+                        if (BITS && skip) A.car_bits[seg0 + k] = 0ULL;
+                        certain &= need;
+                    }
+                    const unsigned mc = __ballot_sync(FULL, certain), mu = __ballot_sync(FULL, unsure);
+                    if (certain) {
+                        const int pos = qn + __popc(mc & lt);
+                        q[pos] = make_float4(p.x, p.y, p.z, __uint_as_float((unsigned)(int)ru | ((unsigned)(int)rv << 16)));
+                        if (BITS) qi[pos] = k;
+                    }
+                    qn += __popc(mc);
                     if (unsure) uq[un + __popc(mu & lt)] = make_float4(p.x, p.y, p.z, __int_as_float(k));
                     un += __popc(mu);
-                    if (un >= 32) resolve(32);
+                    __syncwarp();
                 }
+                if (last) break;
             }
-        } else if (un > 0) {
-            resolve(un);
+            if (lane == 0 && nval) atomicAdd(A.n_valid + f, nval);
         }
-        __syncwarp();
-        while (qn >= 32 || (last && qn > 0)) consume(min(qn, 32));
-        if (last) break;
-        __syncwarp();
+        id = __shfl_sync(FULL, nxt, 0);
     }
-    if (lane == 0 && nval) atomicAdd(S.nvalid, nval);
-    __syncthreads();
-    for (int i = threadIdx.x; i < M * B; i += NT) {
-        const int c = i / B, b = i - c * B;
-        const int v = S.inside[c * A.smem_boxes + b];
-        if (v) atomicAdd(A.inside + A.cnt_off[f] + i, v);
-    }
-    for (int c = threadIdx.x; c < M; c += NT) {
-        const int v = S.total[c];
-        if (v) atomicAdd(A.total + m0 + c, v);
-    }
-    for (int b = threadIdx.x; b < B; b += NT) {
-        const int v = S.nin[b];
-        if (v) atomicAdd(A.n_in_box + b0 + b, v);
-    }
-    if (threadIdx.x == 0 && *S.nvalid) atomicAdd(A.n_valid + f, *S.nvalid);
 }
 
 }  // namespace

@@ -1,5 +1,5 @@
 # Kernel experiments: objects of every source once, then one library per set of -D flags for the
-# point-pass sources.  usage: bash scripts/build_variants.sh name1 "-DLF_FUSE_PER=4 -DLF_FUSE_CTAS=3" name2 "..."
+# point-pass sources.  usage: bash scripts/build_variants.sh name1 "-DLF_FUSE_CLAIM=1024" name2 "..."
 # Libraries land in build/variants/liblidarfuse_<name>.so; run with LIDARFUSE_LIB=<path>.
 set -e
 cd "$(dirname "$0")/.."
