@@ -50,8 +50,6 @@ extern "C" {
 #define LF_FUSE_ORIENTED 1   /* oriented slab test (cvs_erosion.py:114-145); clear = axis-aligned (V1:118-139) */
 #define LF_FUSE_EXACT    2   /* verification mode: no point is classified in fp32, every point that may pass the
                                 gate takes the float64 chain (same results by construction; the tests compare) */
-#define LF_FUSE_NOPREFILTER 4 /* verification mode: ignore the scratch of lf_fuse_batch_ws (no per-frame map of
-                                where masks and boxes are; every gate-valid point meets every cull) */
 
 #define LF_POLICY_NEAREST 0  /* z-buffer: smallest depth per pixel (north-star) */
 #define LF_POLICY_LAST    1  /* last point in index order wins (seg_with_pointcloud.py:162-168) */
@@ -162,30 +160,12 @@ int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_of
                   int32_t* total /*DEVICE*/, int32_t* inside /*DEVICE*/, int32_t* n_in_box /*DEVICE*/,
                   int32_t* n_valid /*DEVICE*/, uint64_t* car_bits /*DEVICE or NULL*/, void* stream);
 
-/* lf_fuse_batch with a caller-owned scratch buffer (DEVICE, 16-B aligned, lf_fuse_scratch_bytes(F) bytes =
- * 1056 per frame; contents need not be initialised or kept).  With it the pass first builds, per frame, a
- * bit map of the pixel tiles the masks' bounding boxes touch and of the xy cells (+ z range) the boxes'
- * cull bounds touch; gate-valid points that fall outside both (about two thirds of an HDL-64 sweep in
- * view of the camera) are counted in n_valid and skip the mask gather and the box tests, which they
- * cannot affect.  Same results as lf_fuse_batch (the tests compare them); scratch == NULL is lf_fuse_batch.
- * Replaces the same reference lines as lf_fuse_batch (cvs_erosion.py:342-372). */
-int64_t lf_fuse_scratch_bytes(int F);
-int lf_fuse_batch_ws(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
-                     const uint32_t* packed /*DEVICE*/, const int32_t* mask_bbox /*DEVICE or NULL*/,
-                     const int32_t* mask_off /*DEVICE [F+1]*/, const lf_box* boxes /*DEVICE*/,
-                     const int32_t* box_off /*DEVICE [F+1]*/, const int64_t* cnt_off /*DEVICE [F+1]*/, int F,
-                     int64_t max_points_per_frame, int max_masks_per_frame, int max_boxes_per_frame,
-                     double max_depth, int use_oriented, int32_t* total, int32_t* inside, int32_t* n_in_box,
-                     int32_t* n_valid, uint64_t* car_bits /*DEVICE or NULL*/, void* scratch /*DEVICE or NULL*/,
-                     int64_t scratch_bytes, void* stream);
-
 /* The whole per-batch body of cvs_erosion.process_frames (:342-372) in one call:
  * lf_erode_pack + lf_fuse_batch + lf_car_stats with the same arguments and the same
  * results (three launches on `stream`).  masks == NULL: `packed` and `mask_bbox` are
  * inputs (already packed masks).  best_idx / best_cnt / agg as in lf_car_stats (NULL
- * best_idx skips the decision).  `sched` (scheduler words of version 100's persistent
- * erode+fuse kernel, which was slower than the launches and is gone) now carries the
- * optional scratch of lf_fuse_batch_ws: lf_fuse_scratch_bytes(F) bytes, 16-B aligned, or NULL. */
+ * best_idx skips the decision).  `sched` is reserved and ignored (pass NULL): the
+ * persistent erode+fuse kernel it selected in version 100 was slower than the launches. */
 int lf_process_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
                      const void* masks /*DEVICE [n_masks][H][W] or NULL*/, int mask_mode, int64_t n_masks,
                      const int32_t* mask_off /*DEVICE [F+1]*/, const uint8_t* se /*HOST [k][k]*/, int k,
@@ -194,7 +174,7 @@ int lf_process_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt
                      const int64_t* cnt_off /*DEVICE [F+1]*/, int F, int64_t max_points_per_frame,
                      int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,
                      int min_points, int32_t* total, int32_t* inside, int32_t* n_in_box, int32_t* n_valid,
-                     int32_t* best_idx, int32_t* best_cnt, int64_t* agg, int32_t* sched /*DEVICE scratch or NULL*/,
+                     int32_t* best_idx, int32_t* best_cnt, int64_t* agg, int32_t* sched /*DEVICE or NULL*/,
                      void* stream);
 
 /* A6 stand-alone: bit c of bits[i] = packed mask c is set at (v[i], u[i])

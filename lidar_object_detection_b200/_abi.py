@@ -15,7 +15,7 @@ LF_OK, LF_E_ARG, LF_E_CUDA, LF_E_UNSUPPORTED, LF_E_NOCAMERA = 0, -1, -2, -3, -4
 POLICY_NEAREST, POLICY_LAST = 0, 1
 MODE_U8, MODE_F32_GE1, MODE_F32_GT_HALF, MODE_PACKED = 0, 1, 2, 3
 MAX_CARS = 64
-FUSE_ORIENTED, FUSE_EXACT, FUSE_NOPREFILTER = 1, 2, 4          # flag word `use_oriented` of lf_fuse_batch / lf_process_batch
+FUSE_ORIENTED, FUSE_EXACT = 1, 2          # flag word `use_oriented` of lf_fuse_batch / lf_process_batch
 
 # numpy mirror of struct lf_box (192 bytes)
 BOX_DTYPE = np.dtype([('c0', '<f8', 3), ('e1', '<f8', 3), ('e2', '<f8', 3), ('e3', '<f8', 3),
@@ -48,9 +48,6 @@ SIGNATURES = {
     'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
     'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp]),
-    'lf_fuse_scratch_bytes': (C.c_int64, [_i32]),
-    'lf_fuse_batch_ws': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
-                                   _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     'lf_process_batch': (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                    _i32, _i64, _i32, _i32, _f64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp]),

@@ -25,15 +25,7 @@ struct LfCam {
     // overflows to +inf (= "never certain") for points beyond 2^20 m; cxm, cym = image centre
     // ((W-1)/2, (H-1)/2) the rows 0 / 1 of Pg are shifted by.
     float kT, kTs, gS, cxm, cym;
-    // pixel tiles of the per-frame "a mask may be here" map (fuse.cu): tile = 2^tsx x 2^tsy pixels,
-    // ttw tiles per row, at most LF_MAP_TILE_WORDS * 32 tiles per image
-    int tsx, tsy, ttw;
 };
-// per-frame prefilter map of the point pass: 8 header floats | 64 x 64 xy-grid bits | pixel-tile bits
-#define LF_MAP_GRID 64
-#define LF_MAP_GRID_WORDS (LF_MAP_GRID * LF_MAP_GRID / 32)
-#define LF_MAP_TILE_WORDS 128
-#define LF_MAP_WORDS (8 + LF_MAP_GRID_WORDS + LF_MAP_TILE_WORDS)
 
 struct lf_ctx {
     int device;

@@ -118,11 +118,6 @@ extern "C" int lf_set_camera(lf_ctx* ctx, const double TrVeloToRect[16], const d
     if ((double)ctx->cam.kT < kT) ctx->cam.kT = nextafterf(ctx->cam.kT, INFINITY);
     ctx->cam.gS = 3.2451855365842673e+32f;                 // 2^108
     ctx->cam.kTs = ctx->cam.kT * 3.0814879110195774e-33f;  // kT * 2^-108 (exact scaling; kT >= 2^-18 keeps it normal)
-    int tsx = 5, tsy = 3;                                   // 32 x 8 pixel tiles, coarser for large images
-    while ((int64_t)(((W - 1) >> tsx) + 1) * (((H - 1) >> tsy) + 1) > (int64_t)LF_MAP_TILE_WORDS * 32) {
-        if ((W >> tsx) >= (H >> tsy)) ++tsx; else ++tsy;
-    }
-    ctx->cam.tsx = tsx; ctx->cam.tsy = tsy; ctx->cam.ttw = ((W - 1) >> tsx) + 1;
     ctx->cam.cxm = (float)cxm;
     ctx->cam.cym = (float)cym;
     ctx->has_camera = 1;

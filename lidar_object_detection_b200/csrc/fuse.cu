@@ -4,8 +4,8 @@
 // counter.  Every thread streams its points through registers (128-bit loads, the next
 // iteration's in flight while this one is classified; each point read exactly once: 16 B of
 // HBM traffic per point), classifies them in fp32, and only survivors -- compacted into
-// per-warp shared-memory queues and filtered by a per-frame map of where masks and boxes
-// are -- reach the packed-mask gather (L2) and the float64 containment test (fuse_body.cuh).
+// per-warp shared-memory queues -- reach the packed-mask gather (L2) and the float64
+// containment test (fuse_body.cuh).
 #include <math.h>
 #include "fuse_body.cuh"
 
@@ -15,7 +15,7 @@ namespace {
 #define LF_FUSE_WARPS 8
 #endif
 #ifndef LF_FUSE_PER
-#define LF_FUSE_PER 8            /* loads in flight per thread and iteration */
+#define LF_FUSE_PER 8            /* loads in flight per thread and iteration; the small-queue geometry uses half */
 #endif
 #ifndef LF_FUSE_CTAS
 #define LF_FUSE_CTAS 4           /* launch bound (registers); shared memory decides how many really fit */
@@ -23,95 +23,6 @@ namespace {
 #ifndef LF_FUSE_CLAIM
 #define LF_FUSE_CLAIM 2048       /* points per claim for batches that fill the machine */
 #endif
-
-// Per-frame prefilter maps of the point pass, one warp per frame (LF_MAP_WORDS words each):
-//   header  {gx0, gy0, invx, invy, z0, z1, 0, 0}: origin / inverse cell size of a 64 x 64 grid over the
-//           xy extent of the frame's box cull bounds, and their z extent
-//   grid    bit (iy, ix) set when some box's cull bounds touch the cell.  Cell indices come from the
-//           SAME fp32 expression floor((x - gx0) * invx) here and in the point pass; it is monotonic
-//           in x, so lo <= x <= hi implies cell(lo) <= cell(x) <= cell(hi): no point inside a box's
-//           cull bounds (hence no point inside the box) can land in an unmarked cell
-//   tiles   bit set when some mask's bounding box touches the 2^tsx x 2^tsy pixel tile
-__device__ __forceinline__ int map_cell(float x, float g0, float inv) {
-    const int i = __float2int_rd(__fmul_rn(__fsub_rn(x, g0), inv));
-    return max(0, min(i, LF_MAP_GRID - 1));
-}
-
-__global__ void __launch_bounds__(128)
-lf_fuse_maps_kernel(const __grid_constant__ LfCam cam, const int32_t* __restrict__ mask_bbox,
-                    const int32_t* __restrict__ mask_off, const lf_box* __restrict__ boxes,
-                    const int32_t* __restrict__ box_off, int F, uint32_t* __restrict__ maps) {
-    __shared__ uint32_t sm[4][LF_MAP_WORDS];
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int f = blockIdx.x * 4 + w;
-    if (f >= F) return;
-    uint32_t* m = sm[w];
-    for (int i = lane; i < LF_MAP_WORDS; i += 32) m[i] = 0u;
-    const int b0 = box_off[f], B = box_off[f + 1] - b0;
-    const int m0 = mask_off[f], M = mask_off[f + 1] - m0;
-    const float INF = __int_as_float(0x7f800000);
-    float lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
-    bool finite = true;
-    for (int b = lane; b < B; b += 32)
-        for (int k = 0; k < 3; ++k) {
-            const float l = boxes[b0 + b].lo[k], h = boxes[b0 + b].hi[k];
-            lo[k] = fminf(lo[k], l); hi[k] = fmaxf(hi[k], h);
-            finite &= (fabsf(l) < INF) & (fabsf(h) < INF);      // false for inf and NaN
-        }
-    for (int k = 0; k < 3; ++k) { lo[k] = warp_min_f32(lo[k]); hi[k] = warp_max_f32(hi[k]); }
-    finite = __all_sync(0xFFFFFFFFu, finite);
-    float gx0 = lo[0], gy0 = lo[1], invx = 0.f, invy = 0.f, z0 = lo[2], z1 = hi[2];
-    if (B > 0 && finite) {
-        if (hi[0] > lo[0]) invx = __fdiv_rn((float)LF_MAP_GRID, __fsub_rn(hi[0], lo[0]));
-        if (hi[1] > lo[1]) invy = __fdiv_rn((float)LF_MAP_GRID, __fsub_rn(hi[1], lo[1]));
-        if (!(fabsf(invx) < INF)) invx = 0.f;
-        if (!(fabsf(invy) < INF)) invy = 0.f;
-    } else if (B > 0) {                                     // a box with unbounded cull bounds: every point is looked at
-        gx0 = gy0 = 0.f; z0 = -INF; z1 = INF;
-    }
-    __syncwarp();
-    if (lane == 0) {
-        float* h = (float*)m;                               // B == 0: z0 = +inf > z1 = -inf, no point qualifies
-        h[0] = gx0; h[1] = gy0; h[2] = invx; h[3] = invy; h[4] = z0; h[5] = z1;
-    }
-    uint32_t* grid = m + 8;
-    if (B > 0 && !finite) {
-        for (int i = lane; i < LF_MAP_GRID_WORDS; i += 32) grid[i] = 0xFFFFFFFFu;
-    } else {
-        for (int b = 0; b < B; ++b) {
-            const lf_box* bx = boxes + b0 + b;
-            const int i0 = map_cell(bx->lo[0], gx0, invx), i1 = map_cell(bx->hi[0], gx0, invx);
-            const int j0 = map_cell(bx->lo[1], gy0, invy), j1 = map_cell(bx->hi[1], gy0, invy);
-            for (int j = j0 + lane; j <= j1; j += 32)       // one grid row per lane
-                for (int wd = i0 >> 5; wd <= (i1 >> 5); ++wd) {
-                    const int a = max(i0, 32 * wd) - 32 * wd, e = min(i1, 32 * wd + 31) - 32 * wd;
-                    grid[j * (LF_MAP_GRID / 32) + wd] |= (0xFFFFFFFFu >> (31 - e)) & (0xFFFFFFFFu << a);
-                }
-            __syncwarp();
-        }
-    }
-    uint32_t* tiles = m + 8 + LF_MAP_GRID_WORDS;
-    const int ttw = cam.ttw, tth = ((cam.H - 1) >> cam.tsy) + 1;
-    for (int c = 0; c < M; ++c) {
-        int x0 = 0, y0 = 0, x1 = cam.W - 1, y1 = cam.H - 1;
-        if (mask_bbox) {
-            const int4 r = __ldg((const int4*)mask_bbox + m0 + c);
-            x0 = (1 << 20) - r.x; y0 = (1 << 20) - r.y; x1 = r.z - 1; y1 = r.w - 1;
-        }
-        if (x1 < x0 || y1 < y0) continue;                   // empty mask
-        x0 = max(x0, 0); y0 = max(y0, 0); x1 = min(x1, cam.W - 1); y1 = min(y1, cam.H - 1);
-        const int tx0 = x0 >> cam.tsx, tx1 = x1 >> cam.tsx, ty0 = y0 >> cam.tsy, ty1 = min(y1 >> cam.tsy, tth - 1);
-        for (int ty = ty0; ty <= ty1; ++ty)
-            for (int tx = tx0 + lane; tx <= tx1; tx += 32) {
-                const int t = ty * ttw + tx;
-                atomicOr(&tiles[t >> 5], 1u << (t & 31));
-            }
-        __syncwarp();
-    }
-    __syncwarp();
-    uint32_t* out = maps + (size_t)f * LF_MAP_WORDS;
-    for (int i = lane; i < LF_MAP_WORDS; i += 32) out[i] = m[i];
-}
 
 template <int WARPS, int PER, bool BITS, int CTAS>
 __global__ void __launch_bounds__(32 * WARPS, CTAS)
@@ -138,7 +49,9 @@ cudaError_t launch_fuse(lf_ctx* ctx, FuseArgs A, int F, int64_t max_points_per_f
     const int64_t workers = (int64_t)ctx->sm_count * per_sm * WARPS;
     // claim size: LF_FUSE_CLAIM points for batches that keep every warp busy for many claims,
     // down to one iteration (32 * PER points) for a frame or two
-    int64_t claim = LF_FUSE_CLAIM;
+    // (measured on B200: 2048 for HDL-64 sweeps, where a claim usually starts a new frame and reloads the
+    // frame cache; 512 for multi-sweep frames of millions of points, where dense claims need finer balancing)
+    int64_t claim = max_points_per_frame >= (1 << 20) ? LF_FUSE_CLAIM / 4 : LF_FUSE_CLAIM;
     while (claim > G::SPAN && (int64_t)F * max_points_per_frame / claim < 8 * workers) claim /= 2;
     claim = ((claim + G::SPAN - 1) / G::SPAN) * G::SPAN;
     const int64_t cpf = (max_points_per_frame + claim - 1) / claim;
@@ -163,7 +76,7 @@ cudaError_t launch_fuse_any(lf_ctx* ctx, const FuseArgs& A, int F, int64_t maxn,
     using Gf = FuseGeom<LF_FUSE_WARPS, LF_FUSE_PER, BITS>;
     if (Gf::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 <= (size_t)227 * 1024 / LF_FUSE_CTAS)
         return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
-    return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER / 2, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+    return launch_fuse<LF_FUSE_WARPS, (LF_FUSE_PER / 2), BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -216,15 +129,12 @@ lf_car_stats_kernel(const int32_t* __restrict__ total, const int32_t* __restrict
 
 }  // namespace
 
-extern "C" int64_t lf_fuse_scratch_bytes(int F) { return F > 0 ? (int64_t)F * LF_MAP_WORDS * 4 : 0; }
-
-extern "C" int lf_fuse_batch_ws(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const uint32_t* packed,
-                                const int32_t* mask_bbox, const int32_t* mask_off, const lf_box* boxes,
-                                const int32_t* box_off, const int64_t* cnt_off, int F, int64_t max_points_per_frame,
-                                int max_masks_per_frame, int max_boxes_per_frame, double max_depth,
-                                int use_oriented, int32_t* total, int32_t* inside, int32_t* n_in_box,
-                                int32_t* n_valid, uint64_t* car_bits, void* scratch, int64_t scratch_bytes,
-                                void* stream) {
+extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const uint32_t* packed,
+                             const int32_t* mask_bbox, const int32_t* mask_off, const lf_box* boxes, const int32_t* box_off,
+                             const int64_t* cnt_off, int F, int64_t max_points_per_frame,
+                             int max_masks_per_frame, int max_boxes_per_frame, double max_depth,
+                             int use_oriented, int32_t* total, int32_t* inside, int32_t* n_in_box,
+                             int32_t* n_valid, uint64_t* car_bits, void* stream) {
     if (!ctx || F < 0 || max_points_per_frame < 0 || max_masks_per_frame < 0 || max_boxes_per_frame < 0)
         return LF_E_ARG;
     if (!ctx->has_camera) return LF_E_NOCAMERA;
@@ -233,8 +143,7 @@ extern "C" int lf_fuse_batch_ws(lf_ctx* ctx, const float* pts, const int64_t* pt
     if (max_masks_per_frame > 0 && (!packed || !total)) return LF_E_ARG;
     if (max_boxes_per_frame > 0 && (!boxes || !n_in_box)) return LF_E_ARG;
     if (max_masks_per_frame > 0 && max_boxes_per_frame > 0 && !inside) return LF_E_ARG;
-    if (((uintptr_t)pts & 15) != 0 || ((uintptr_t)mask_bbox & 15) != 0 || ((uintptr_t)scratch & 15) != 0) return LF_E_ARG;
-    if (scratch && scratch_bytes < lf_fuse_scratch_bytes(F)) return LF_E_ARG;
+    if (((uintptr_t)pts & 15) != 0 || ((uintptr_t)mask_bbox & 15) != 0) return LF_E_ARG;
     if ((int64_t)ctx->cam.H * ctx->cam.wpr * LF_MAX_CARS >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
     if (ctx->cam.W > 65535 || ctx->cam.H > 65535) return LF_E_UNSUPPORTED;   // queued pixels are 16 + 16 bits
     if (max_masks_per_frame > LF_MAX_CARS) return LF_E_UNSUPPORTED;           // one 64-bit membership word per point
@@ -255,18 +164,12 @@ extern "C" int lf_fuse_batch_ws(lf_ctx* ctx, const float* pts, const int64_t* pt
     A.dmax_hi = dh; A.dmax_lo = dl;
     A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
     A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
-    A.claim = nullptr; A.maps = nullptr; A.F = 0; A.cpf = 0; A.claim_points = 0;
+    A.claim = nullptr; A.F = 0; A.cpf = 0; A.claim_points = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // the per-warp caches of the largest frame must leave room for the half-size queues
-    if (FuseGeom<LF_FUSE_WARPS, LF_FUSE_PER / 2, true>::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 >
+    if (FuseGeom<LF_FUSE_WARPS, (LF_FUSE_PER / 2), true>::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 >
         (size_t)227 * 1024)
         return LF_E_UNSUPPORTED;
-    if (scratch && (use_oriented & LF_FUSE_NOPREFILTER) == 0) {
-        lf_fuse_maps_kernel<<<(F + 3) / 4, 128, 0, st>>>(ctx->cam, mask_bbox, mask_off, boxes, box_off, F,
-                                                        (uint32_t*)scratch);
-        LF_CUDA(ctx, cudaGetLastError());
-        A.maps = (const uint32_t*)scratch;
-    }
     // the claim space of one launch is 31 bits: very large batches go out in several launches
     // (the CSR arrays are simply entered at frame f0)
     const int64_t fmax = (int64_t)1 << 20;
@@ -274,7 +177,6 @@ extern "C" int lf_fuse_batch_ws(lf_ctx* ctx, const float* pts, const int64_t* pt
         const int nf = (int)(F - f0 < fmax ? F - f0 : fmax);
         FuseArgs Af = A;
         Af.pt_off += f0; Af.mask_off += f0; Af.box_off += f0; Af.cnt_off += f0; Af.n_valid += f0;
-        if (Af.maps) Af.maps += (size_t)f0 * LF_MAP_WORDS;
         if (car_bits)
             LF_CUDA(ctx, launch_fuse_any<true>(ctx, Af, nf, max_points_per_frame, st));
         else
@@ -283,23 +185,13 @@ extern "C" int lf_fuse_batch_ws(lf_ctx* ctx, const float* pts, const int64_t* pt
     return LF_OK;
 }
 
-extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const uint32_t* packed,
-                             const int32_t* mask_bbox, const int32_t* mask_off, const lf_box* boxes, const int32_t* box_off,
-                             const int64_t* cnt_off, int F, int64_t max_points_per_frame,
-                             int max_masks_per_frame, int max_boxes_per_frame, double max_depth,
-                             int use_oriented, int32_t* total, int32_t* inside, int32_t* n_in_box,
-                             int32_t* n_valid, uint64_t* car_bits, void* stream) {
-    return lf_fuse_batch_ws(ctx, pts, pt_off, packed, mask_bbox, mask_off, boxes, box_off, cnt_off, F,
-                            max_points_per_frame, max_masks_per_frame, max_boxes_per_frame, max_depth, use_oriented,
-                            total, inside, n_in_box, n_valid, car_bits, nullptr, 0, stream);
-}
-
 extern "C" int lf_car_stats(lf_ctx* ctx, const int32_t* total, const int32_t* inside, const int32_t* mask_off,
                             const int32_t* box_off, const int64_t* cnt_off, int F, int min_points,
                             int32_t* best_idx, int32_t* best_cnt, int64_t* agg, void* stream) {
     if (!ctx || F < 0) return LF_E_ARG;
     if (F == 0) return LF_OK;
-    if (!total || !inside || !mask_off || !box_off || !cnt_off || !best_idx || !best_cnt) return LF_E_ARG;
+    if (!mask_off || !box_off || !cnt_off) return LF_E_ARG;
+    if (!total || !best_idx || !best_cnt) return LF_OK;      // a batch without masks has no cars to decide
     LF_CUDA(ctx, cudaSetDevice(ctx->device));
     const int wpb = 4;
     lf_car_stats_kernel<<<(F + wpb - 1) / wpb, wpb * 32, 0, (cudaStream_t)stream>>>(
@@ -309,9 +201,8 @@ extern "C" int lf_car_stats(lf_ctx* ctx, const int32_t* total, const int32_t* in
     return LF_OK;
 }
 
-// erode + fuse + decision in one ABI call (stand-alone launches).  `sched` (the scheduler words of the
-// persistent erode+fuse kernel of version 100, which was slower than the launches and is gone) now
-// carries the point pass's optional scratch: lf_fuse_scratch_bytes(F) bytes, or NULL.
+// erode + fuse + decision in one ABI call (three stand-alone launches).  `sched` is reserved: the
+// persistent erode+fuse kernel it once selected was measured slower than the launches and is gone.
 extern "C" int lf_process_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const void* masks, int mask_mode,
                                 int64_t n_masks, const int32_t* mask_off, const uint8_t* se, int k, int iterations,
                                 uint32_t* packed, int32_t* mask_bbox, const lf_box* boxes, const int32_t* box_off,
@@ -319,6 +210,7 @@ extern "C" int lf_process_batch(lf_ctx* ctx, const float* pts, const int64_t* pt
                                 int max_boxes_per_frame, double max_depth, int use_oriented, int min_points,
                                 int32_t* total, int32_t* inside, int32_t* n_in_box, int32_t* n_valid,
                                 int32_t* best_idx, int32_t* best_cnt, int64_t* agg, int32_t* sched, void* stream) {
+    (void)sched;
     if (!ctx || F < 0 || n_masks < 0 || max_points_per_frame < 0 || max_masks_per_frame < 0 ||
         max_boxes_per_frame < 0 || iterations < 0)
         return LF_E_ARG;
@@ -331,10 +223,9 @@ extern "C" int lf_process_batch(lf_ctx* ctx, const float* pts, const int64_t* pt
         if (rc != LF_OK) return rc;
     }
     if (max_points_per_frame > 0) {
-        rc = lf_fuse_batch_ws(ctx, pts, pt_off, packed, mask_bbox, mask_off, boxes, box_off, cnt_off, F,
-                              max_points_per_frame, max_masks_per_frame, max_boxes_per_frame, max_depth, use_oriented,
-                              total, inside, n_in_box, n_valid, nullptr, sched, sched ? lf_fuse_scratch_bytes(F) : 0,
-                              stream);
+        rc = lf_fuse_batch(ctx, pts, pt_off, packed, mask_bbox, mask_off, boxes, box_off, cnt_off, F,
+                           max_points_per_frame, max_masks_per_frame, max_boxes_per_frame, max_depth, use_oriented,
+                           total, inside, n_in_box, n_valid, nullptr, stream);
         if (rc != LF_OK) return rc;
         if (best_idx && best_cnt) {
             rc = lf_car_stats(ctx, total, inside, mask_off, box_off, cnt_off, F, min_points, best_idx, best_cnt, agg,

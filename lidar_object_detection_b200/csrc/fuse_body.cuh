@@ -5,28 +5,29 @@
 //   claims   the batch is cut into claims of consecutive points of one frame; every warp of the
 //            (machine-filling) grid takes the next claim from one global counter until none is
 //            left, so warps never wait for each other and the load balances itself.
-//   phase A  per iteration a warp owns 32 * PER consecutive points; the PER 128-bit streaming loads
-//            of the NEXT iteration are issued before the current registers are looked at.  Each
-//            32-point group is classified in fp32 in two stages, each ended by a warp vote so that
-//            groups without a survivor stop early:
-//              1. depth row only          -> behind the camera / beyond the range gate
-//              2. centred image rows      -> more than a pixel outside the image
-//            Survivors ("candidates", ~17 % of an HDL-64 sweep) are compacted (ballot + popc
-//            prefix) into a per-warp shared-memory queue.
-//   stage 3  full 32-lane groups of candidates: pixel = rint(x/d) in fp32 plus a residual test
-//            that PROVES it equal to the reference's float64 result ("certain") or not
-//            ("uncertain" -> exact queue).  Certain points are looked up in the frame's
-//            prefilter map (lf_fuse_maps_kernel): only points whose pixel tile touches a mask's
-//            bounding box or whose xy cell / z touches a box's cull bounds can change a counter
-//            other than n_valid; they go to the work queue, the others are counted and dropped.
+//   phase A  per iteration a warp owns 32 * PER consecutive points: every thread keeps PER
+//            independent 128-bit streaming loads in flight, then classifies each 32-point group
+//            in fp32 in three stages of rising cost, each ended by a warp vote so that groups
+//            without a survivor stop early:
+//              1. depth row only                    -> behind the camera / beyond the range gate
+//              2. centred image rows                -> more than a pixel outside the image
+//              3. pixel = rint(x/d) in fp32 + a residual test that PROVES it equal to the
+//                 reference's float64 result        -> "certain" (pixel known) or "uncertain"
+//            Survivors are compacted (ballot + popc prefix) into two per-warp shared-memory
+//            queues: certain points with their pixel, uncertain ones for the exact chain.
+//            Consecutive queue entries are consecutive survivors of the sweep, so a group of 32
+//            covers a short arc of one ring: tight pixel and xyz bounds for the culls below.
 //   exact    whenever 32 uncertain points are queued the warp runs the float64 dgemm-order
 //            chain and the two divisions on all 32 lanes (common.cuh) and moves the points
-//            that pass the gate of cvs_erosion.py:359 to the work queue.
-//   phase B  full 32-lane groups of the work queue: packed-mask gather (L2) behind a mask
+//            that pass the gate of cvs_erosion.py:359 to the certain queue.
+//   phase B  full 32-lane groups of certain points: packed-mask gather (L2) behind a mask
 //            bounding-box cull, box cull, float64 containment, ballot/popc counts added to the
 //            global counters with one reduction-atomic per (car, box) and group.
 // Nothing fp32 ever decides a result: a point is "certain" only if the fp32 residual proves
 // the rounded pixel and the gate (error bounds: lf_set_camera); everything else takes the exact path.
+// Measured and dropped: stage 3 as a separate pass over a candidate queue, and a
+// per-frame bit map of where masks and boxes are in front of phase B -- the group-level culls of
+// phase B already skip what such a map skips, and the extra pass costs more than it saves.
 #pragma once
 #include "common.cuh"
 
@@ -54,7 +55,6 @@ struct FuseArgs {
     int smem_boxes;      // per-warp cache of box cull bounds (max boxes over frames)
     int smem_cars;       // per-warp cache of mask bounding boxes (max masks per frame, <= LF_MAX_CARS)
     unsigned int* claim; // global claim counter, zeroed before the launch
-    const uint32_t* maps; // optional [F][LF_MAP_WORDS] prefilter maps, NULL = every valid point is looked at
     int F;               // frames of this launch
     int cpf;             // claims per frame = ceil(max points per frame / claim_points)
     int claim_points;    // points per claim: a multiple of 32 * PER
@@ -117,8 +117,6 @@ struct FuseFrame {
     int32_t* total;       // global counters of this frame
     int32_t* inside;
     int32_t* nin;
-    const uint32_t* fmap; // prefilter map of the frame (NULL: none) and its header
-    float gx0, gy0, ginvx, ginvy, gz0, gz1;
 };
 
 // counts of one 32-mask block: one reduction-atomic per car present in the group
@@ -246,51 +244,36 @@ __device__ __noinline__ int fuse_resolve(const LfCam& cam, const FuseArgs& A, co
     return qn + __popc(mk);
 }
 
+
 // Geometry of one warp's working set.
 //   WARPS  warps per CTA (independent workers; the CTA only shares the shared-memory allocation)
 //   PER    128-bit loads in flight per thread and iteration (an iteration covers PER*32 consecutive points)
-//   BITS   per-point membership output (car_bits) wanted: the work queue carries the point index too
+//   BITS   per-point membership output (car_bits) wanted: queues carry the point index too
 template <int WARPS, int PER, bool BITS>
 struct FuseGeom {
     static constexpr int NT = 32 * WARPS;
     static constexpr int SPAN = PER * 32;                  // points per iteration of one warp
-    static constexpr int CCAP = PER * 32 + 32;             // candidates (4-byte indices): < 32 left over + PER*32 new
-    static constexpr int QCAP = 64;                        // work queue: < 32 left over + 32 new (drained first)
+    static constexpr int QCAP = PER * 32 + 64;             // certain queue: < 32 left over + PER*32 new + < 32 resolved
     static constexpr int UCAP = 64;                        // uncertain queue: < 32 left over + 32 new
-    static constexpr size_t queue_bytes = (size_t)(QCAP + UCAP) * 16 + (size_t)CCAP * 4 + (BITS ? (size_t)QCAP * 4 : 0);
+    static constexpr size_t queue_bytes = (size_t)(QCAP + UCAP) * 16 + (BITS ? (size_t)QCAP * 4 : 0);
     // + per-warp frame cache: mask bounding boxes (16 B each) and box cull bounds (24 B each)
     static __host__ __device__ size_t warp_bytes(int cars, int boxes) {
-        return (queue_bytes + sizeof(FuseFrame) + 16 * (size_t)cars + 24 * (size_t)boxes + 24 + 15) & ~(size_t)15;
+        return (queue_bytes + 16 * (size_t)cars + 24 * (size_t)boxes + 8 + 15) & ~(size_t)15;
     }
 };
-
-template <int PER>
-__device__ __forceinline__ void fuse_load(float4 (&P)[PER], const float4* src, int base, int npts) {
-    const int k0 = base + (int)(threadIdx.x & 31);
-    if (base + 32 * PER <= npts) {                          // whole iteration inside the claim
-#pragma unroll
-        for (int j = 0; j < PER; ++j) P[j] = ld_stream_f4(src + k0 + 32 * j);
-    } else {                                                // dead lanes are masked by `k < npts` in stage 1
-#pragma unroll
-        for (int j = 0; j < PER; ++j)
-            P[j] = k0 + 32 * j < npts ? ld_stream_f4(src + k0 + 32 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-}
 
 template <int WARPS, int PER, bool BITS>
 __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs& A, uint8_t* smem) {
     using G = FuseGeom<WARPS, PER, BITS>;
-    constexpr int SPAN = G::SPAN, CCAP = G::CCAP, QCAP = G::QCAP, UCAP = G::UCAP;
+    constexpr int SPAN = G::SPAN, QCAP = G::QCAP, UCAP = G::UCAP;
     const unsigned FULL = 0xFFFFFFFFu;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t* ws = smem + (size_t)warp * G::warp_bytes(A.smem_cars, A.smem_boxes);
-    float4* q = (float4*)ws;                               // [QCAP] work queue: x, y, z, bits(u | v << 16)
+    float4* q = (float4*)ws;                               // [QCAP] certain: x, y, z, bits(u | v << 16)
     float4* uq = q + QCAP;                                 // [UCAP] uncertain: x, y, z, bits(index in claim)
-    FuseFrame& Fr = *(FuseFrame*)(uq + UCAP);               // frame state lives in shared memory, not in registers
-    int4* s_mbb = (int4*)((uint8_t*)(uq + UCAP) + ((sizeof(FuseFrame) + 15) & ~(size_t)15));   // [smem_cars]
+    int4* s_mbb = (int4*)(uq + UCAP);                      // [smem_cars]
     float* s_cull = (float*)(s_mbb + A.smem_cars);         // [6][smem_boxes]
-    int* cq = (int*)(s_cull + 6 * (size_t)A.smem_boxes);   // [CCAP] candidates: index in claim (the point is re-read, an L2 hit)
-    int* qi = cq + CCAP;                                   // [QCAP] index in claim of the work-queue entries (BITS)
+    int* qi = (int*)(s_cull + 6 * (size_t)A.smem_boxes);   // [QCAP] index in claim of the certain entries (BITS)
 
     const int plane32 = cam.H * cam.wpr;                   // words per packed mask (< 2^25, see lf_set_camera)
     const unsigned lt = (1u << lane) - 1u;
@@ -300,8 +283,10 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
     const float dhi = A.dmax_hi, dlo = A.dmax_lo;
     const bool fast = !A.force_exact;
     const unsigned n_claims = (unsigned)A.F * (unsigned)A.cpf;
-    const int tsx = cam.tsx, tsy = cam.tsy, ttw = cam.ttw;
 
+    FuseFrame Fr;
+    Fr.mbb = s_mbb; Fr.cull = s_cull; Fr.SB = A.smem_boxes;
+    Fr.M = Fr.B = 0; Fr.mask_base = nullptr; Fr.boxes = nullptr; Fr.total = Fr.inside = Fr.nin = nullptr;
     int cur_f = -1;
 
     unsigned id = 0;
@@ -320,26 +305,15 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
             if (f != cur_f) {                               // frame state into the warp's cache
                 cur_f = f;
                 const int m0 = A.mask_off[f], b0 = A.box_off[f];
-                const int M = A.mask_off[f + 1] - m0, B = A.box_off[f + 1] - b0;
+                Fr.M = A.mask_off[f + 1] - m0;
+                Fr.B = A.box_off[f + 1] - b0;
+                Fr.mask_base = A.packed + (int64_t)m0 * plane32;
+                Fr.boxes = A.boxes + b0;
+                Fr.total = A.total + m0;
+                Fr.nin = A.n_in_box + b0;
+                Fr.inside = A.inside + A.cnt_off[f];
                 __syncwarp();
-                if (lane == 0) {
-                    Fr.mbb = s_mbb; Fr.cull = s_cull; Fr.SB = A.smem_boxes;
-                    Fr.M = M; Fr.B = B;
-                    Fr.mask_base = A.packed + (int64_t)m0 * plane32;
-                    Fr.boxes = A.boxes + b0;
-                    Fr.total = A.total + m0;
-                    Fr.nin = A.n_in_box + b0;
-                    Fr.inside = A.inside + A.cnt_off[f];
-                    Fr.fmap = nullptr;
-                    if (A.maps) {
-                        const uint32_t* fm = A.maps + (size_t)f * LF_MAP_WORDS;
-                        const float4 h0 = __ldg((const float4*)fm);
-                        const float2 h1 = __ldg((const float2*)fm + 2);
-                        Fr.fmap = fm;
-                        Fr.gx0 = h0.x; Fr.gy0 = h0.y; Fr.ginvx = h0.z; Fr.ginvy = h0.w; Fr.gz0 = h1.x; Fr.gz1 = h1.y;
-                    }
-                }
-                for (int c = lane; c < M; c += 32) {
+                for (int c = lane; c < Fr.M; c += 32) {
                     int4 bb = make_int4(0, 0, cam.W - 1, cam.H - 1);
                     if (A.mask_bbox) {                      // record of lf_erode_pack: zeros = empty mask
                         const int4 r = __ldg((const int4*)A.mask_bbox + m0 + c);
@@ -347,8 +321,8 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                     }
                     s_mbb[c] = bb;
                 }
-                for (int b = lane; b < B; b += 32) {
-                    const float2* lh = (const float2*)(A.boxes[b0 + b].lo);    // lo[3], hi[3]: 8-B aligned
+                for (int b = lane; b < Fr.B; b += 32) {
+                    const float2* lh = (const float2*)(Fr.boxes[b].lo);    // lo[3], hi[3]: 8-B aligned
                     const float2 t0 = __ldg(lh), t1 = __ldg(lh + 1), t2 = __ldg(lh + 2);
                     s_cull[b] = t0.x; s_cull[A.smem_boxes + b] = t0.y; s_cull[2 * A.smem_boxes + b] = t1.x;
                     s_cull[3 * A.smem_boxes + b] = t1.y; s_cull[4 * A.smem_boxes + b] = t2.x;
@@ -356,113 +330,88 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                 }
                 __syncwarp();
             }
-            int cn = 0, qn = 0, un = 0;                     // queue fills, warp-uniform
-            int nval = 0;                                   // gate-valid points seen in this claim
+            int qn = 0, un = 0;                             // queue fill, warp-uniform
+            int nval = 0;                                   // certain points consumed in this claim
+            // phase B on the last 32 (or fewer, at the very end) entries of the certain queue
+            auto consume = [&](int cnt) {
+                const bool have = lane < cnt;
+                const int at = qn - cnt + (have ? lane : 0);
+                const float4 e = q[at];
+                const unsigned long long bits = fuse_group(cam, A, Fr, e, have, plane32);
+                if (BITS && have) A.car_bits[seg0 + qi[at]] = bits;
+                nval += cnt;
+                qn -= cnt;
+            };
             const int niter = (npts + SPAN - 1) / SPAN;
             for (int it = 0;; ++it) {
-                const bool last = it == niter;              // pseudo-iteration: flush the queues
+                const bool last = it == niter;              // pseudo-iteration: flush both queues
                 if (!last) {
+                    const int kbase = it * SPAN + lane;     // group j: kbase + 32 j
                     float4 P[PER];
-                    fuse_load<PER>(P, src, it * SPAN, npts);
+                    if (it * SPAN + SPAN <= npts) {
+#pragma unroll
+                        for (int j = 0; j < PER; ++j) P[j] = ld_stream_f4(src + kbase + 32 * j);
+                    } else {                                // dead lanes are masked by `k < npts` in stage 1
+#pragma unroll
+                        for (int j = 0; j < PER; ++j)
+                            P[j] = kbase + 32 * j < npts ? ld_stream_f4(src + kbase + 32 * j)
+                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
 #pragma unroll
                     for (int j = 0; j < PER; ++j) {
                         const float4 p = P[j];
-                        const int k = it * SPAN + 32 * j + lane;
+                        const int k = kbase + 32 * j;
                         // ---- stage 1: depth row.  tol bounds every fp32 evaluation error of this point
                         // (+inf beyond 2^20 m and for NaN / inf input: such points are never decided here).
                         const float d = fmaf(cam.Pg[8], p.x, fmaf(cam.Pg[9], p.y, fmaf(cam.Pg[10], p.z, cam.Pg[11])));
                         const float tol = fmaf((fabsf(p.x) + fabsf(p.y) + fabsf(p.z)) * gS, kTs, kT);
                         const bool okd = !(d < -tol) & !(d > dhi + tol) & (k < npts);     // NaN stays in
-                        bool maybe = false;
-                        if (__any_sync(FULL, okd)) {
-                            // ---- stage 2: centred image rows, one pixel of margin
-                            const float x = fmaf(cam.Pg[0], p.x, fmaf(cam.Pg[1], p.y, fmaf(cam.Pg[2], p.z, cam.Pg[3])));
-                            const float y = fmaf(cam.Pg[4], p.x, fmaf(cam.Pg[5], p.y, fmaf(cam.Pg[6], p.z, cam.Pg[7])));
-                            maybe = okd & !(fabsf(x) > fmaf(hwx, d, tol)) & !(fabsf(y) > fmaf(hwy, d, tol));
-                            const unsigned mm = __ballot_sync(FULL, maybe);
-                            if (maybe) cq[cn + __popc(mm & lt)] = k;
-                            cn += __popc(mm);
+                        if (!__any_sync(FULL, okd)) {
+                            if (BITS && k < npts) A.car_bits[seg0 + k] = 0ULL;
+                            continue;
                         }
+                        // ---- stage 2: centred image rows, one pixel of margin
+                        const float x = fmaf(cam.Pg[0], p.x, fmaf(cam.Pg[1], p.y, fmaf(cam.Pg[2], p.z, cam.Pg[3])));
+                        const float y = fmaf(cam.Pg[4], p.x, fmaf(cam.Pg[5], p.y, fmaf(cam.Pg[6], p.z, cam.Pg[7])));
+                        const bool maybe = okd & !(fabsf(x) > fmaf(hwx, d, tol)) & !(fabsf(y) > fmaf(hwy, d, tol));
+                        if (!__any_sync(FULL, maybe)) {
+                            if (BITS && k < npts) A.car_bits[seg0 + k] = 0ULL;
+                            continue;
+                        }
+                        // ---- stage 3: pixel in fp32, proven by the residual |x - (u - cx) d| < d/2 - tol
+                        const float r = rcp_approx(d);
+                        const float ru = rintf(fmaf(x, r, cxm)), rv = rintf(fmaf(y, r, cym));
+                        const float half = fmaf(0.5f, d, -tol);
+                        const bool sure = (fabsf(fmaf(cxm - ru, d, x)) < half) & (fabsf(fmaf(cym - rv, d, y)) < half) &
+                                          (ru >= 0.f) & (ru <= umax) & (rv >= 0.f) & (rv <= vmax) &
+                                          (d - tol > 0.f) & (d + tol < dlo) & fast;
+                        const bool certain = maybe & sure, unsure = maybe & !sure;
+                        const unsigned mc = __ballot_sync(FULL, certain), mu = __ballot_sync(FULL, unsure);
+                        if (certain) {
+                            const int pos = qn + __popc(mc & lt);
+                            q[pos] = make_float4(p.x, p.y, p.z,
+                                                 __uint_as_float((unsigned)(int)ru | ((unsigned)(int)rv << 16)));
+                            if (BITS) qi[pos] = k;
+                        }
+                        qn += __popc(mc);
                         if (BITS && !maybe && k < npts) A.car_bits[seg0 + k] = 0ULL;
+                        if (mu) {
+                            if (unsure) uq[un + __popc(mu & lt)] = make_float4(p.x, p.y, p.z, __int_as_float(k));
+                            un += __popc(mu);
+                            if (un >= 32) {
+                                qn = fuse_resolve<BITS>(cam, A, uq + (un - 32), 32, q, qi, qn, seg0);
+                                un -= 32;
+                            }
+                        }
                     }
+                } else if (un > 0) {
+                    qn = fuse_resolve<BITS>(cam, A, uq, un, q, qi, qn, seg0);
+                    un = 0;
                 }
                 __syncwarp();
-                // ---- drain the queues: full 32-lane groups only, except at the end of the claim.  One
-                // instance of each step in the code; every condition is warp-uniform.
-                for (;;) {
-                    if (qn >= 32 || (last && cn == 0 && un == 0 && qn > 0)) {
-                        // ---- phase B
-                        const int n = min(qn, 32);
-                        qn -= n;
-                        const bool hv = lane < n;
-                        const int at = qn + (hv ? lane : 0);
-                        const float4 e = q[at];
-                        const unsigned long long bits = fuse_group(cam, A, Fr, e, hv, plane32);
-                        if (BITS && hv) A.car_bits[seg0 + qi[at]] = bits;
-                        nval += n;
-                        __syncwarp();
-                        continue;
-                    }
-                    if (un >= 32 || (last && cn == 0 && un > 0)) {
-                        // ---- exact path
-                        const int n = min(un, 32);
-                        un -= n;
-                        qn = fuse_resolve<BITS>(cam, A, uq + un, n, q, qi, qn, seg0);
-                        continue;
-                    }
-                    if (!(cn >= 32 || (last && cn > 0))) break;
-                    // ---- stage 3: pixel in fp32, proven by the residual |x - (u - cx) d| < d/2 - tol
-                    const int cnt = min(cn, 32);
-                    cn -= cnt;
-                    const bool have = lane < cnt;
-                    const int k = cq[cn + (have ? lane : 0)];
-                    const float4 p = __ldg(src + k);        // read a moment ago: an L2 hit
-                    const float d = fmaf(cam.Pg[8], p.x, fmaf(cam.Pg[9], p.y, fmaf(cam.Pg[10], p.z, cam.Pg[11])));
-                    const float x = fmaf(cam.Pg[0], p.x, fmaf(cam.Pg[1], p.y, fmaf(cam.Pg[2], p.z, cam.Pg[3])));
-                    const float y = fmaf(cam.Pg[4], p.x, fmaf(cam.Pg[5], p.y, fmaf(cam.Pg[6], p.z, cam.Pg[7])));
-                    const float tol = fmaf((fabsf(p.x) + fabsf(p.y) + fabsf(p.z)) * gS, kTs, kT);
-                    const float r = rcp_approx(d);
-                    const float ru = rintf(fmaf(x, r, cxm)), rv = rintf(fmaf(y, r, cym));
-                    const float half = fmaf(0.5f, d, -tol);
-                    const bool sure = (fabsf(fmaf(cxm - ru, d, x)) < half) & (fabsf(fmaf(cym - rv, d, y)) < half) &
-                                      (ru >= 0.f) & (ru <= umax) & (rv >= 0.f) & (rv <= vmax) &
-                                      (d - tol > 0.f) & (d + tol < dlo) & fast;
-                    bool certain = have & sure;
-                    const bool unsure = have & !sure;
-                    const uint32_t* fmap = Fr.fmap;
-                    if (fmap) {
-                        const float gx0 = Fr.gx0, gy0 = Fr.gy0, ginvx = Fr.ginvx, ginvy = Fr.ginvy, gz0 = Fr.gz0, gz1 = Fr.gz1;
-                        // prefilter: a certain point is looked at only if its pixel tile touches a mask's
-                        // bounding box or its xy cell (and z) touches a box's cull bounds; the others are
-                        // gate-valid points that can change no counter but n_valid
-                        const int ui = certain ? (int)ru : 0, vi = certain ? (int)rv : 0;
-                        const int t = (vi >> tsy) * ttw + (ui >> tsx);
-                        const unsigned wt = __ldg(fmap + 8 + LF_MAP_GRID_WORDS + (t >> 5));
-                        int ix = __float2int_rd(__fmul_rn(__fsub_rn(p.x, gx0), ginvx));
-                        int iy = __float2int_rd(__fmul_rn(__fsub_rn(p.y, gy0), ginvy));
-                        const bool inr = certain & (ix >= 0) & (ix <= LF_MAP_GRID) & (iy >= 0) & (iy <= LF_MAP_GRID) &
-                                         (p.z >= gz0) & (p.z <= gz1);
-                        ix = inr ? min(ix, LF_MAP_GRID - 1) : 0;
-                        iy = inr ? min(iy, LF_MAP_GRID - 1) : 0;
-                        const unsigned wg = __ldg(fmap + 8 + iy * (LF_MAP_GRID / 32) + (ix >> 5));
-                        const bool need = (((wt >> (t & 31)) & 1u) != 0u) | (inr & (((wg >> (ix & 31)) & 1u) != 0u));
-                        const bool skip = certain & !need;
-                        nval += __popc(__ballot_sync(FULL, skip));
-                        if (BITS && skip) A.car_bits[seg0 + k] = 0ULL;
-                        certain &= need;
-                    }
-                    const unsigned mc = __ballot_sync(FULL, certain), mu = __ballot_sync(FULL, unsure);
-                    if (certain) {
-                        const int pos = qn + __popc(mc & lt);
-                        q[pos] = make_float4(p.x, p.y, p.z, __uint_as_float((unsigned)(int)ru | ((unsigned)(int)rv << 16)));
-                        if (BITS) qi[pos] = k;
-                    }
-                    qn += __popc(mc);
-                    if (unsure) uq[un + __popc(mu & lt)] = make_float4(p.x, p.y, p.z, __int_as_float(k));
-                    un += __popc(mu);
-                    __syncwarp();
-                }
+                while (qn >= 32 || (last && qn > 0)) consume(min(qn, 32));
                 if (last) break;
+                __syncwarp();
             }
             if (lane == 0 && nval) atomicAdd(A.n_valid + f, nval);
         }

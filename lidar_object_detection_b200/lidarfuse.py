@@ -605,9 +605,6 @@ class FrameBatch:
         self.best_idx = self.counters[self._ob:self._ob + sm]
         self.best_cnt = self.counters[self._ob + sm:self._ob + 2 * sm]
         self.agg = self.counters[self._nz:].view(torch.int64)
-        # scratch of the point pass (per-frame prefilter maps, lf_fuse_batch_ws)
-        self.fuse_scratch = torch.empty(max(int(ctx.lib.lf_fuse_scratch_bytes(self.F)), 16) // 4, dtype=torch.int32,
-                                        device=ctx.device)
         self.car_bits = torch.empty(self.points.shape[0], dtype=torch.int64, device=ctx.device) \
             if want_car_bits else None
         self._native = None
@@ -632,15 +629,14 @@ class FrameBatch:
         self.launches_per_run = 0
 
     def run(self, erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True,
-            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, one_call=False, exact=False, prefilter=True):
+            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, one_call=False, exact=False):
         """memset + erode/pack + fused point pass + per-car decision, all async
         on the current stream.  Returns nothing; read ``results()`` / ``table()``.
 
         ``one_call=True`` issues erode + point pass + decision through the single ABI entry
         ``lf_process_batch`` instead of the three calls (``mark(name)`` between them);
         ``exact=True`` is the verification mode of the point pass (``LF_FUSE_EXACT``: no point
-        is classified in fp32), ``prefilter=False`` switches the per-frame mask / box map of the
-        point pass off (``LF_FUSE_NOPREFILTER``) -- same results, the tests compare them."""
+        is classified in fp32) -- same results, the tests compare the two."""
         ctx, lib = self.ctx, self.ctx.lib
         ctx.set_camera(self.TrVeloToRect, self.camera.K, self.camera.width, self.camera.height)
         st = ctx.stream
@@ -675,8 +671,7 @@ class FrameBatch:
                 mode = _mask_mode(self.masks, float_threshold)
                 mt = self.masks.view(torch.uint8) if self.masks.dtype == torch.bool else self.masks
         bbox = self.packed.bbox if pre and not self.masks.raw else self.mask_bbox
-        flags = (_abi.FUSE_ORIENTED if use_oriented else 0) | (_abi.FUSE_EXACT if exact else 0) | \
-            (0 if prefilter else _abi.FUSE_NOPREFILTER)
+        flags = (_abi.FUSE_ORIENTED if use_oriented else 0) | (_abi.FUSE_EXACT if exact else 0)
         if one_call and self.car_bits is None and getattr(self, '_native', None) is None:
             check(lib.lf_process_batch(
                 ctx.h, ptr(self.points), ptr(self.pt_off), ptr(mt) if raw else None, mode, len(mt) if raw else 0,
@@ -684,9 +679,9 @@ class FrameBatch:
                 ptr(self.packed.words), ptr(bbox), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
                 self.F, self.max_n, self.max_m, self.max_b, float(max_depth), flags, int(min_points),
                 ptr(self.total), ptr(self.inside), ptr(self.n_in_box), ptr(self.n_valid),
-                ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), ptr(self.fuse_scratch), st), ctx.h)
+                ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), None, st), ctx.h)
             mark('car_stats')
-            self.launches_per_run = 1 + (1 if raw else 0) + (4 if (self.F and self.max_n) else 0)
+            self.launches_per_run = 1 + (1 if raw else 0) + (2 if (self.F and self.max_n) else 0)
             return
         if raw:
             check(lib.lf_erode_pack(ctx.h, ptr(mt), mode, len(mt), self.camera.height, self.camera.width,
@@ -695,17 +690,16 @@ class FrameBatch:
             launches += 1
         mark('erode_pack')
         if self.F and self.max_n:
-            check(lib.lf_fuse_batch_ws(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
+            check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
                                     ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
                                     self.F, self.max_n, self.max_m, self.max_b, float(max_depth),
                                     flags, ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
-                                    ptr(self.n_valid), ptr(self.car_bits), ptr(self.fuse_scratch),
-                                    self.fuse_scratch.numel() * 4, st), ctx.h)
+                                    ptr(self.n_valid), ptr(self.car_bits), st), ctx.h)
             mark('fuse')
             check(lib.lf_car_stats(ctx.h, ptr(self.total), ptr(self.inside), ptr(self.mask_off),
                                    ptr(self.box_off), ptr(self.cnt_off), self.F, int(min_points),
                                    ptr(self.best_idx), ptr(self.best_cnt), ptr(self.agg), st), ctx.h)
-            launches += 4              # prefilter maps, claim-counter memset, point pass, decision
+            launches += 2
         mark('car_stats')
         self.launches_per_run = launches
 

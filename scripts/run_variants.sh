@@ -1,7 +1,7 @@
 # usage: bash scripts/run_variants.sh name1 name2 ...   (libraries from scripts/build_variants.sh)
 mkdir -p gpurun_out
 for v in "$@"; do
-  LIDARFUSE_LIB=$PWD/build/variants/liblidarfuse_$v.so timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-e2e --no-parity --no-packed > gpurun_out/var_$v.json 2> gpurun_out/var_$v.err || echo "$v failed"
+  LIDARFUSE_LIB=$PWD/build/variants/liblidarfuse_$v.so timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-e2e --no-parity --no-packed $BENCH_EXTRA > gpurun_out/var_$v.json 2> gpurun_out/var_$v.err || echo "$v failed"
   python - "$v" <<'PY'
 import json, sys
 v = sys.argv[1]
