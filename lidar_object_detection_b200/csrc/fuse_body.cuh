@@ -31,6 +31,10 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef LF_FUSE_PFDIST
+#define LF_FUSE_PFDIST 1           /* iterations the L2 prefetch runs ahead of the loads */
+#endif
+
 namespace {
 
 struct FuseArgs {
@@ -347,6 +351,10 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                 const bool last = it == niter;              // pseudo-iteration: flush both queues
                 if (!last) {
                     const int kbase = it * SPAN + lane;     // group j: kbase + 32 j
+                    {   // PER * 4 lines (128 B each) of the iteration after next, one per lane, towards L2
+                        const int kn = (it + LF_FUSE_PFDIST) * SPAN + lane * 8;
+                        if (lane < PER * 4 && kn < npts) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + kn));
+                    }
                     float4 P[PER];
                     if (it * SPAN + SPAN <= npts) {
 #pragma unroll
