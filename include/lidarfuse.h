@@ -42,6 +42,7 @@ extern "C" {
 #define LF_E_CUDA       -2   /* a CUDA call failed; lf_last_cuda_error() has the cudaError_t */
 #define LF_E_UNSUPPORTED -3  /* size beyond what the kernels are built for */
 #define LF_E_NOCAMERA   -4   /* lf_set_camera has not been called */
+#define LF_E_LIMIT      -5   /* beyond the fixed capacity of a no-allocation entry point (lf_depth_maps_noalloc) */
 
 #define LF_MAX_SE 15         /* structuring elements up to 15x15 */
 #define LF_MAX_CARS 64       /* masks per frame handled in one pass of lf_fuse_batch */
@@ -50,6 +51,8 @@ extern "C" {
 #define LF_FUSE_ORIENTED 1   /* oriented slab test (cvs_erosion.py:114-145); clear = axis-aligned (V1:118-139) */
 #define LF_FUSE_EXACT    2   /* verification mode: no point is classified in fp32, every point that may pass the
                                 gate takes the float64 chain (same results by construction; the tests compare) */
+
+#define LF_NOALLOC_MAX_PIXELS (1 << 20)   /* W * H limit of lf_depth_maps_noalloc: 8 MiB of static device memory */
 
 #define LF_POLICY_NEAREST 0  /* z-buffer: smallest depth per pixel (north-star) */
 #define LF_POLICY_LAST    1  /* last point in index order wins (seg_with_pointcloud.py:162-168) */
@@ -231,6 +234,20 @@ int lf_publish_table(lf_ctx* ctx, const int32_t* total /*DEVICE*/, const int32_t
                      const int32_t* box_off /*DEVICE [F+1]*/, const int64_t* agg /*DEVICE [8] or NULL*/, int F,
                      int max_cars, int64_t row0, void* const* peers /*DEVICE [world]*/, int world, int rank,
                      int64_t table_off_bytes, int64_t agg_off_bytes, void* stream);
+
+/* lf_depth_maps that allocates nothing and takes no scratch from the caller.  NO COUNTERPART IN THE
+ * REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The 64-bit key image
+ * lives in a file-scope static device array of LF_NOALLOC_MAX_PIXELS keys (8 MiB, held by every GPU
+ * that loads the library until exit); W * H beyond that returns LF_E_LIMIT.  Inputs and outputs are
+ * still the caller's; results are those of lf_depth_maps.  Calls no cudaMalloc / cudaFree / allocating
+ * routine.  Every call on a device shares the array and starts by clearing it, so calls that overlap
+ * on the GPU (two streams, or two contexts on one device) race: serialise them. */
+int64_t lf_depth_maps_noalloc_max_pixels(void);
+int lf_depth_maps_noalloc(lf_ctx* ctx, const float* pts /*DEVICE [n][4]*/, int64_t n, double max_depth, int policy,
+                          const uint32_t* packed /*DEVICE [m][H][wpr] or NULL*/, int m,
+                          double* full /*DEVICE [H][W] or NULL*/, double* per_car /*DEVICE [m][H][W] or NULL*/,
+                          void* stream);
 
 /* A10 for a batch of frames: the loop of seg_with_pointcloud.py:153-170 over F frames in
  * three launches (key images cleared, one atomic per gated point, resolve).  Frames are

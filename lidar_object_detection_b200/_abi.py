@@ -11,7 +11,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get('LIDARFUSE_LIB') or os.path.join(HERE, '_lib', 'liblidarfuse.so')   # override: kernel experiments
 
-LF_OK, LF_E_ARG, LF_E_CUDA, LF_E_UNSUPPORTED, LF_E_NOCAMERA = 0, -1, -2, -3, -4
+LF_OK, LF_E_ARG, LF_E_CUDA, LF_E_UNSUPPORTED, LF_E_NOCAMERA, LF_E_LIMIT = 0, -1, -2, -3, -4, -5
 POLICY_NEAREST, POLICY_LAST = 0, 1
 MODE_U8, MODE_F32_GE1, MODE_F32_GT_HALF, MODE_PACKED = 0, 1, 2, 3
 MAX_CARS = 64
@@ -57,6 +57,8 @@ SIGNATURES = {
     'lf_car_stats': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     'lf_zero_counters': (C.c_int, [_vp, _vp, _i64, _vp]),
     'lf_depth_maps': (C.c_int, [_vp, _vp, _i64, _f64, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
+    'lf_depth_maps_noalloc_max_pixels': (C.c_int64, []),
+    'lf_depth_maps_noalloc': (C.c_int, [_vp, _vp, _i64, _f64, _i32, _vp, _i32, _vp, _vp, _vp]),
     'lf_depth_maps_batch': (C.c_int, [_vp, _vp, _vp, _i32, _i64, _f64, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),
     'lf_resize_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _i32, _vp]),
     'lf_resize_pack': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _i32, _i32, _vp]),
@@ -101,7 +103,7 @@ def check(code, ctx=None):
     msg = lib.lf_strerror(code).decode()
     if code == LF_E_CUDA and ctx is not None:
         msg += ' [cudaError_t %d]' % lib.lf_last_cuda_error(ctx)
-    if code in (LF_E_ARG, LF_E_UNSUPPORTED):
+    if code in (LF_E_ARG, LF_E_UNSUPPORTED, LF_E_LIMIT):
         raise ValueError('lidarfuse: ' + msg)
     raise LidarFuseError('lidarfuse: ' + msg)
 

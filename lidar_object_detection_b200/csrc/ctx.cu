@@ -13,6 +13,7 @@ extern "C" const char* lf_strerror(int code) {
         case LF_E_CUDA: return "CUDA error (see lf_last_cuda_error)";
         case LF_E_UNSUPPORTED: return "size not supported by the kernels";
         case LF_E_NOCAMERA: return "lf_set_camera has not been called";
+        case LF_E_LIMIT: return "beyond the fixed capacity of the no-allocation entry point";
         default: return "unknown lidarfuse error";
     }
 }

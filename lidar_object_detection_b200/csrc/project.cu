@@ -147,6 +147,38 @@ extern "C" int lf_depth_maps(lf_ctx* ctx, const float* pts, int64_t n, double ma
 }
 
 // ---------------------------------------------------------------------------
+// lf_depth_maps without any caller- or library-side allocation: the key image lives in a
+// file-scope device array (LF_NOALLOC_MAX_PIXELS 64-bit keys = 8 MiB per GPU that loads the
+// library, held until exit).  No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  In host code the array's name is only a stand-in: its device
+// address is taken once per device with cudaGetSymbolAddress.  Every call on a device shares
+// the array (the fill launch at the start of each call clears it), so calls that overlap on
+// the GPU -- different streams, or different contexts on one device -- race.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long lf_noalloc_keys[LF_NOALLOC_MAX_PIXELS];
+static unsigned long long* lf_noalloc_ptr[64];             // device address of the array, per device ordinal
+
+extern "C" int64_t lf_depth_maps_noalloc_max_pixels(void) { return LF_NOALLOC_MAX_PIXELS; }
+
+extern "C" int lf_depth_maps_noalloc(lf_ctx* ctx, const float* pts, int64_t n, double max_depth, int policy,
+                                     const uint32_t* packed, int m, double* full, double* per_car, void* stream) {
+    if (!ctx) return LF_E_ARG;
+    if (!ctx->has_camera) return LF_E_NOCAMERA;
+    if ((int64_t)ctx->cam.W * ctx->cam.H > (int64_t)LF_NOALLOC_MAX_PIXELS) return LF_E_LIMIT;
+    if (ctx->device < 0 || ctx->device >= 64) return LF_E_UNSUPPORTED;
+    LF_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!lf_noalloc_ptr[ctx->device]) {                     // set-up, once per device, that device current
+        void* p = nullptr;
+        LF_CUDA(ctx, cudaGetSymbolAddress(&p, lf_noalloc_keys));
+        if (!p) return LF_E_CUDA;
+        lf_noalloc_ptr[ctx->device] = (unsigned long long*)p;
+    }
+    return lf_depth_maps(ctx, pts, n, max_depth, policy, packed, m, (uint64_t*)lf_noalloc_ptr[ctx->device], full, per_car,
+                         stream);
+}
+
+// ---------------------------------------------------------------------------
 // K2 for a batch of frames: the same two passes over F frames at once.
 //   scatter: CTA = (frame, segment of DM_SEG points); eight independent 128-bit loads per
 //            thread in flight, the fp32 pre-gate (common.cuh) drops the ~75 % of points that
