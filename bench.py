@@ -54,10 +54,12 @@ def algorithmic_bytes_per_frame(n_points, n_masks, n_boxes):
 
 # --------------------------------------------------------------------------- CPU arm
 
-def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue, workload='cfg3'):
+def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue, workload='cfg3', kind='port'):
     """One host process: generate ``nframes`` synthetic frames with numpy (untimed),
-    then run ``warm`` + ``steps`` frames of the oracle's per-frame pipeline
-    (cycling over its frames); only the ``steps`` part is timed."""
+    then run ``warm`` + ``steps`` frames of the CPU path (cycling over its frames); only the
+    ``steps`` part is timed.  kind 'reference': the reference's OWN functions, from the unmodified
+    scripts (oracle/reference_frame.py: cvs_erosion.py:338-372 once each, nothing added);
+    'port': the oracle's numpy restatement (only where the scripts are not staged)."""
     os.environ['OPENBLAS_NUM_THREADS'] = '1'
     os.environ['OMP_NUM_THREADS'] = '1'
     import numpy as np
@@ -76,13 +78,21 @@ def _cpu_worker(rank, nframes, warm, steps, seed, barrier, queue, workload='cfg3
         raw = [{'corners_cam0': b['corners_cam0']} for b in boxes[f]]
         frames.append((pts, raw, masks))
     rows = 0
+    if kind == 'reference':
+        from oracle import reference_frame as RF
+        cvs = RF.load()
+
+        def one(fr):
+            return len(RF.process_frame(cvs, *fr, cam, TVC, TVR, erosion_kernel_size=KSIZE))
+    else:
+        def one(fr):
+            return len(P.process_frame(*fr, cam, TVC, TVR, erosion_kernel_size=KSIZE)['stats'])
     for i in range(warm):
-        P.process_frame(*frames[i % nframes], cam, TVC, TVR, erosion_kernel_size=KSIZE)
+        one(frames[i % nframes])
     barrier.wait()
     t0 = time.time()
     for i in range(steps):
-        out = P.process_frame(*frames[i % nframes], cam, TVC, TVR, erosion_kernel_size=KSIZE)
-        rows += len(out['stats'])
+        rows += one(frames[i % nframes])
     t1 = time.time()
     queue.put((rank, t0, t1, steps * len(frames[0][0]), rows))
 
@@ -94,14 +104,24 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_reference_throughput(steps, warm=1, distinct_frames=2, workers=None, workload='cfg3'):
+def cpu_kind():
+    """'reference' when the reference's scripts are present (/root/reference or staged oracle/_ref)."""
+    try:
+        from oracle import reference_loader as RL
+        return 'reference' if RL.available() else 'port'
+    except Exception:
+        return 'port'
+
+
+def cpu_reference_throughput(steps, warm=1, distinct_frames=2, workers=None, workload='cfg3', kind=None):
     """points/s of the CPU path, one process per host core, each timing ``steps``
     frames (a bounded sample of the workload)."""
     import multiprocessing as mp
     workers = workers or host_cores()
+    kind = kind or cpu_kind()
     ctx = mp.get_context('spawn')
     barrier, queue = ctx.Barrier(workers), ctx.Queue()
-    procs = [ctx.Process(target=_cpu_worker, args=(r, distinct_frames, warm, steps, SEED, barrier, queue, workload))
+    procs = [ctx.Process(target=_cpu_worker, args=(r, distinct_frames, warm, steps, SEED, barrier, queue, workload, kind))
              for r in range(workers)]
     for p in procs:
         p.start()
@@ -112,7 +132,25 @@ def cpu_reference_throughput(steps, warm=1, distinct_frames=2, workers=None, wor
     t1 = max(r[2] for r in res)
     points = sum(r[3] for r in res)
     return {'value': points / (t1 - t0), 'seconds': t1 - t0, 'points': points, 'cores': workers,
-            'frames': steps * workers, 'rows': sum(r[4] for r in res)}
+            'frames': steps * workers, 'rows': sum(r[4] for r in res), 'kind': kind}
+
+
+CPU_KIND_NOTE = {'reference': "the reference's own functions from its unmodified scripts (cvs_erosion.py:338-372, "
+                              'float32 masks in, per-car dicts out)',
+                 'port': "the oracle's numpy port (reference scripts not staged)"}
+
+
+def bench_config(workload, frames, n_pts, world, step_bytes=None, exchange=None):
+    """The `config` object both arms print (same workload, same keys)."""
+    if step_bytes is None:
+        step_bytes = frames * algorithmic_bytes_per_frame(n_pts, NCARS, NCARS)
+    return {'workload': '%s: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes per GPU, '
+                        '%dx%d ellipse erosion, 50 m gate' % (workload, frames, n_pts, NCARS, W_IMG, H_IMG,
+                                                             NCARS, KSIZE, KSIZE),
+            'frames_per_gpu': frames, 'points_per_frame': n_pts, 'masks_per_frame': NCARS,
+            'l2_policy': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush' % (step_bytes / 1e9),
+            'parallelism': 'frames sharded, dp%d' % world,
+            'exchange': exchange}
 
 
 # --------------------------------------------------------------------------- clocks
@@ -179,9 +217,9 @@ def run_gpu(args):
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         c = cpu_reference_throughput(steps=args.cpu_frames, warm=1, workload=args.workload)
-        cpu = {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': 'port',
+        cpu = {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': c['kind'],
                'sample': '%d synthetic frames (%d per host process, %d processes, OPENBLAS/cv2 threads = 1), '
-                         '%.1f s wall' % (c['frames'], args.cpu_frames, c['cores'], c['seconds'])}
+                         '%.1f s wall; %s' % (c['frames'], args.cpu_frames, c['cores'], c['seconds'], CPU_KIND_NOTE[c['kind']])}
 
     from lidar_object_detection_b200 import distributed as D, kitti360 as K, synthetic as S
     cam, TVC, TVR = K.calibration_chain(CALIB_ROOT)
@@ -433,13 +471,7 @@ def run_gpu(args):
             'warmup': max(args.warmup, 3), 'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f64 projection/containment, u32 bit-masks, i32 counters',
             'data': 'synthetic',
-            'config': {'workload': '%s: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes per GPU, '
-                                   '%dx%d ellipse erosion, 50 m gate' % (args.workload, frames, n_pts, NCARS, W_IMG, H_IMG,
-                                                                        NCARS, KSIZE, KSIZE),
-                       'frames_per_gpu': frames, 'points_per_frame': n_pts, 'masks_per_frame': NCARS,
-                       'l2_policy': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush' % (step_bytes / 1e9),
-                       'parallelism': 'frames sharded, dp%d' % world,
-                       'exchange': exch_kind if world > 1 else None},
+            'config': bench_config(args.workload, frames, n_pts, world, step_bytes, exch_kind if world > 1 else None),
             'gpu_launches': int(batch.launches_per_run - 1) * K_steps,
             'kernel_ms': kern_ms,
             'step_hbm': {'algorithmic_bytes_per_step': step_bytes, 'achieved_gbs': step_bytes / (ms_step * 1e-3) / 1e9,
@@ -458,22 +490,25 @@ def run_gpu(args):
 # --------------------------------------------------------------------------- reference arm
 
 def run_reference(args):
+    """The reference's CPU implementation of the path on the host cores: every step is one frame per
+    host process (a bounded sample of the workload: `cores` frames of the same shape), `--steps` timed
+    steps after `--warmup` untimed ones, exactly as asked.  Rank 0 alone works."""
     rank = int(os.environ.get('RANK', 0))
     if rank != 0:
         return
-    steps = min(args.steps, 200)             # ~70 ms of CPU work per step and process
-    c = cpu_reference_throughput(steps=steps, warm=min(max(args.warmup, 1), 3), workload=args.workload)
+    world = int(os.environ.get('WORLD_SIZE', args.gpus))
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    c = cpu_reference_throughput(steps=steps, warm=warm, workload=args.workload)
     n_pts = RINGS * AZ
+    sample = '%d frames of the workload\'s shape per step (one per host process), %d steps, %.1f s wall; %s' % (
+        c['cores'], steps, c['seconds'], CPU_KIND_NOTE[c['kind']])
     line = {'impl': 'reference', 'metric': METRIC, 'value': c['value'], 'unit': 'points/s',
-            'n_gpus': int(os.environ.get('WORLD_SIZE', args.gpus)), 'steps': steps, 'warmup': min(max(args.warmup, 1), 3),
+            'n_gpus': world, 'steps': steps, 'warmup': warm,
             'ms_per_step': c['seconds'] / steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f64 (numpy) + u8 (cv2)', 'data': 'synthetic',
-            'config': {'workload': '%s-shaped frames: %d pts x %d masks (%dx%d) x <=%d boxes, %dx%d ellipse erosion; '
-                                   'one step = one frame per host process' % (args.workload, n_pts, NCARS, W_IMG, H_IMG,
-                                                                              NCARS, KSIZE, KSIZE),
-                       'points_per_frame': n_pts, 'masks_per_frame': NCARS},
-            'cpu_baseline': {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': 'port',
-                             'sample': '%d frames over %d host processes, %.1f s' % (c['frames'], c['cores'], c['seconds'])},
+            'config': bench_config(args.workload, FRAMES, n_pts, world),
+            'cpu_baseline': {'value': c['value'], 'unit': 'points/s', 'cores': c['cores'], 'kind': c['kind'],
+                             'sample': sample},
             'e2e': {'value': c['value'], 'unit': 'points/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line))

@@ -489,14 +489,60 @@ def _stats_from_counts(totals, cnt, colors, min_points, extra=None):
 
 
 def calculate_car_point_statistics(car_point_sets, bboxes_3d, colors, min_points=10, use_oriented=True,
-                                   device=None):
+                                   device=None, return_points=False):
     """Per-car dicts {car_id, matched_bbox_id, total_points, points_inside_bbox,
     points_outside_bbox, inside_percentage, outside_percentage, color}
-    (cvs_erosion.py:165-229; V3:320-428 adds ``use_oriented``)."""
+    (cvs_erosion.py:165-229; V3:320-428 adds ``use_oriented``).
+
+    ``return_points=True`` gives the V2 / V3 form of the dicts (V3_point_cloud_with_erosion.py:386-398,
+    416-428; V2_point_cloud_without_erosion.py has the same body): additionally ``corners_velo`` (8x3
+    array of the matched box), ``inside_mask`` (bool per car point, against the matched box) and
+    ``car_points``; None / None / the points for unmatched cars -- what
+    ``create_colored_point_cloud_with_bbox_analysis`` (V3:471-515) and ``print_summary_statistics``
+    consume."""
     if not bboxes_3d or len(car_point_sets) == 0:
         return []
     cnt = inside_count_matrix(car_point_sets, bboxes_3d, use_oriented, device)
-    return _stats_from_counts([len(s) for s in car_point_sets], cnt, colors, min_points)
+    extra = None
+    if return_points:
+        def extra(ci, s):
+            bi = s['matched_bbox_id']
+            if bi < 0:
+                return {'corners_velo': None, 'inside_mask': None, 'car_points': car_point_sets[ci]}
+            corners = np.array(bboxes_3d[bi]['corners_velo'])
+            return {'corners_velo': corners, 'inside_mask': _in_box(car_point_sets[ci], corners, use_oriented, device),
+                    'car_points': car_point_sets[ci]}
+    return _stats_from_counts([len(s) for s in car_point_sets], cnt, colors, min_points, extra)
+
+
+def summary_statistics_text(car_statistics):
+    """The text ``print_summary_statistics`` prints (V3_point_cloud_with_erosion.py:431-468;
+    V2_point_cloud_without_erosion.py:409-446), as one string."""
+    if not car_statistics:
+        return '\nNo car statistics to display.\n'
+    matched = [s for s in car_statistics if s['matched_bbox_id'] >= 0]
+    rule = '-' * 60
+    lines = ['', '=' * 60, '{:^60}'.format('SUMMARY STATISTICS'), '=' * 60,
+             'Total cars detected: {}'.format(len(car_statistics)),
+             'Successfully matched: {}'.format(len(matched)),
+             'Unmatched: {}'.format(len(car_statistics) - len(matched))]
+    if matched:
+        row = '{:<8} {:<8} {:<8} {:<8} {:<8} {:<10}'
+        lines += ['', row.format('Car ID', 'BBox ID', 'Total', 'Inside', 'Outside', 'Inside %'), rule]
+        num = '{:<8} {:<8} {:<8} {:<8} {:<8} {:<10.1f}'
+        for s in matched:
+            lines.append(num.format(s['car_id'], s['matched_bbox_id'], s['total_points'], s['points_inside_bbox'],
+                                    s['points_outside_bbox'], s['inside_percentage']))
+        tp = sum(s['total_points'] for s in matched)
+        ti = sum(s['points_inside_bbox'] for s in matched)
+        to = sum(s['points_outside_bbox'] for s in matched)
+        lines += [rule, num.format('TOTAL', '', tp, ti, to, (ti / tp * 100) if tp > 0 else 0)]
+    return '\n'.join(lines) + '\n'
+
+
+def print_summary_statistics(car_statistics):
+    """Summary table of the per-car statistics, printed as the reference prints it (V3:431-468)."""
+    print(summary_statistics_text(car_statistics), end='')
 
 
 def match_car_points_to_bboxes(car_point_sets, bboxes_3d, colors, min_points=10, use_oriented=True,
@@ -566,9 +612,12 @@ class FrameBatch:
         n_m = len(self.masks) if self.masks is not None else 0
         if n_m != int(n_masks.sum()):
             raise ValueError('mask count != sum of per-frame counts')
+        self._h_corners = None
         if isinstance(boxes, torch.Tensor):
             self.boxes = boxes.to(ctx.device).contiguous()
         else:
+            if not (isinstance(boxes, np.ndarray) and boxes.dtype == _abi.BOX_DTYPE):
+                self._h_corners = np.asarray(boxes, dtype=np.float64).reshape(-1, 8, 3)
             host = boxes if isinstance(boxes, np.ndarray) and boxes.dtype == _abi.BOX_DTYPE else \
                 _abi.prepare_boxes(boxes)
             self.boxes = torch.from_numpy(np.ascontiguousarray(host).view(np.uint8).reshape(-1, 192).copy()) \
@@ -785,9 +834,13 @@ class FrameBatch:
         return {'total': total, 'n_in_box': n_in_box, 'n_valid': n_valid, 'inside': inside, 'agg': agg,
                 'best_idx': c[self._ob:self._ob + sm].copy(), 'best_cnt': c[self._ob + sm:self._ob + 2 * sm].copy()}
 
-    def frame_stats(self, res, f, min_points=10, colors=None, extended=False):
+    def frame_stats(self, res, f, min_points=10, colors=None, extended=False, return_points=False,
+                    use_oriented=True):
         """The list of per-car dicts of frame f, as calculate_car_point_statistics
-        returns them (cvs_erosion.py:165-229)."""
+        returns them (cvs_erosion.py:165-229).  ``extended=True`` adds the point-level precision /
+        recall / point_iou / match_ratio (README.md:14, 38; ``extension_metrics``).
+        ``return_points=True`` (batch built with ``want_car_bits=True``) adds the V2 / V3 keys
+        ``corners_velo``, ``inside_mask``, ``car_points`` (V3:386-398) from the membership bits."""
         m0, m1 = self.h_mask_off[f], self.h_mask_off[f + 1]
         b0, b1 = self.h_box_off[f], self.h_box_off[f + 1]
         M, B = m1 - m0, b1 - b0
@@ -803,26 +856,50 @@ class FrameBatch:
                 if s['matched_bbox_id'] < 0:
                     return extension_metrics(0, s['total_points'], 0)
                 return extension_metrics(s['points_inside_bbox'], s['total_points'], nin[s['matched_bbox_id']])
+        if return_points:
+            if self.car_bits is None:
+                raise ValueError('return_points needs a batch built with want_car_bits=True')
+            p0, p1 = int(self.h_pt_off[f]), int(self.h_pt_off[f + 1])
+            bits, fpts = self.car_bits[p0:p1], self.points[p0:p1, :3]
+            corners = self.host_corners(f)
+            metrics = extra
+
+            def extra(ci, s):
+                out = metrics(ci, s) if metrics is not None else {}
+                cp = fpts[((bits >> ci) & 1).to(torch.bool)].cpu().numpy()
+                bi = s['matched_bbox_id']
+                out.update({'corners_velo': corners[bi] if bi >= 0 else None,
+                            'inside_mask': _in_box(cp, corners[bi], use_oriented, self.ctx.device) if bi >= 0 else None,
+                            'car_points': cp})
+                return out
         return _stats_from_counts(res['total'][m0:m1], cnt, colors, min_points, extra)
+
+    def host_corners(self, f):
+        """[B_f,8,3] float64 corners_velo of frame f's boxes, when the batch was built from corners."""
+        if self._h_corners is None:
+            raise ValueError('this batch was built from prepared lf_box records: corners are not kept')
+        return self._h_corners[int(self.h_box_off[f]):int(self.h_box_off[f + 1])]
 
 
 def process_frames_batched(points, n_points, masks, n_masks, bboxes_per_frame, camera, TrVeloToRect,
                            erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10,
-                           use_oriented=True, device=None, extended=False):
+                           use_oriented=True, device=None, extended=False, return_points=False):
     """Body of the per-frame loop of cvs_erosion.process_frames (:342-372) for F
     frames at once.  ``bboxes_per_frame``: list (per frame) of lists of box
     dicts carrying ``corners_velo``.  Returns a list (per frame) of per-car
-    statistics lists."""
+    statistics lists; ``extended`` / ``return_points`` as in ``FrameBatch.frame_stats``."""
     corners = [np.array([b['corners_velo'] for b in fr], dtype=np.float64).reshape(-1, 8, 3)
                for fr in bboxes_per_frame]
     n_boxes = [len(c) for c in corners]
     allc = np.concatenate(corners) if corners else np.zeros((0, 8, 3))
-    batch = FrameBatch(points, n_points, masks, n_masks, allc, n_boxes, camera, TrVeloToRect, device)
+    batch = FrameBatch(points, n_points, masks, n_masks, allc, n_boxes, camera, TrVeloToRect, device,
+                       want_car_bits=return_points)
     batch.run(erosion_kernel_size, erosion_iterations, max_depth, min_points, use_oriented)
     res = batch.results()
     out = []
     for f in range(batch.F):
-        out.append(batch.frame_stats(res, f, min_points, extended=extended) if res['n_valid'][f] > 0 else [])
+        out.append(batch.frame_stats(res, f, min_points, extended=extended, return_points=return_points,
+                                     use_oriented=use_oriented) if res['n_valid'][f] > 0 else [])
     return out
 
 

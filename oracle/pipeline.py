@@ -174,12 +174,15 @@ def inside_count_matrix(car_point_sets, bboxes_3d, use_oriented=True):
     return cnt
 
 
-def calculate_car_point_statistics(car_point_sets, bboxes_3d, colors, min_points=10, use_oriented=True):
+def calculate_car_point_statistics(car_point_sets, bboxes_3d, colors, min_points=10, use_oriented=True,
+                                   return_points=False):
     """Per-car dicts (cvs_erosion.py:165-229; V3:320-428 adds use_oriented).
 
     best box = first strict maximum of the inside count starting from 0; a
     match needs best_count >= min_points; cars with no points are skipped but
-    keep their index."""
+    keep their index.  ``return_points=True``: the V2 / V3 form of the dicts with
+    ``corners_velo``, ``inside_mask`` (of the best box) and ``car_points``
+    (V3_point_cloud_with_erosion.py:386-398, 416-428); None / None for unmatched cars."""
     stats = []
     if not bboxes_3d or len(car_point_sets) == 0:
         return stats
@@ -204,7 +207,37 @@ def calculate_car_point_statistics(car_point_sets, bboxes_3d, colors, min_points
                           'points_inside_bbox': 0, 'points_outside_bbox': total,
                           'inside_percentage': 0.0, 'outside_percentage': 100.0,
                           'color': colors[ci]})
+        if return_points:
+            test = oriented_point_in_bbox if use_oriented else point_in_bbox
+            bi = stats[-1]['matched_bbox_id']
+            corners = np.array(bboxes_3d[bi]['corners_velo']) if bi >= 0 else None
+            stats[-1].update({'corners_velo': corners, 'inside_mask': test(pts, corners) if bi >= 0 else None,
+                              'car_points': pts})
     return stats
+
+
+def summary_statistics_text(car_statistics):
+    """What print_summary_statistics prints (V3_point_cloud_with_erosion.py:431-468; V2:409-446), as one string."""
+    if not car_statistics:
+        return '\nNo car statistics to display.\n'
+    matched = [s for s in car_statistics if s['matched_bbox_id'] >= 0]
+    lines = ['\n' + '=' * 60, format('SUMMARY STATISTICS', '^60'), '=' * 60,
+             'Total cars detected: %d' % len(car_statistics), 'Successfully matched: %d' % len(matched),
+             'Unmatched: %d' % (len(car_statistics) - len(matched))]
+    if matched:
+        lines.append('\n%-8s %-8s %-8s %-8s %-8s %-10s' % ('Car ID', 'BBox ID', 'Total', 'Inside', 'Outside', 'Inside %'))
+        lines.append('-' * 60)
+        for s in matched:
+            lines.append('%-8s %-8s %-8s %-8s %-8s %s' % (s['car_id'], s['matched_bbox_id'], s['total_points'],
+                                                          s['points_inside_bbox'], s['points_outside_bbox'],
+                                                          format(s['inside_percentage'], '<10.1f')))
+        tp = sum(s['total_points'] for s in matched)
+        ti = sum(s['points_inside_bbox'] for s in matched)
+        to = sum(s['points_outside_bbox'] for s in matched)
+        avg = (ti / tp * 100) if tp > 0 else 0
+        lines.append('-' * 60)
+        lines.append('%-8s %-8s %-8s %-8s %-8s %s' % ('TOTAL', '', tp, ti, to, format(avg, '<10.1f')))
+    return '\n'.join(lines) + '\n'
 
 
 def match_car_points_to_bboxes(car_point_sets, bboxes_3d, colors, min_points=10, use_oriented=True):

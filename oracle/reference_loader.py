@@ -1,10 +1,13 @@
 """Import the reference's scripts UNMODIFIED so their own functions can be run.
 
-ORACLE / TEST INFRASTRUCTURE ONLY.  Works only where ``/root/reference``
-exists (the build container); the GPU box never has it, so nothing in
-``-m gpu`` tests, ``smoke()`` or ``bench.py`` may call this.  It is used by
-``oracle/gen_golden.py`` (fixture generation) and by the CPU test that
-re-checks the restatement against the live reference when it is present.
+ORACLE / TEST INFRASTRUCTURE ONLY.  Reads the scripts from ``/root/reference``
+where it exists (the build container) and otherwise from ``oracle/_ref/``,
+the byte-for-byte copies ``oracle/stage_reference.py`` makes at ``build()`` time
+(git-ignored, shipped to the GPU box with the snapshot) -- nothing at run time
+on the GPU box reads ``/root/reference``.  Used by ``oracle/gen_golden*.py``
+(fixture generation), by the CPU tests that re-check the restatement against the
+live reference, and by ``bench.py --impl reference`` / the ``cpu_baseline`` leg
+(``oracle/reference_frame.py``), which time the reference's own functions.
 
 The scripts cannot be imported as they are: at import time they build
 ``YOLO('yolo11x-seg.pt')`` (weights absent, ultralytics not installed), import
@@ -29,9 +32,18 @@ import types
 
 import numpy as np
 
+_HERE = os.path.dirname(os.path.abspath(__file__))
 REFERENCE_ROOT = os.environ.get('LIDAR_REFERENCE_ROOT', '/root/reference')
+STAGED = False
+if not os.path.isfile(os.path.join(REFERENCE_ROOT, 'Coding_testes', 'cvs_erosion.py')) and \
+        os.path.isfile(os.path.join(_HERE, '_ref', 'Coding_testes', 'cvs_erosion.py')):
+    # the GPU box: byte-for-byte copies staged by oracle/stage_reference.py at build() time
+    REFERENCE_ROOT, STAGED = os.path.join(_HERE, '_ref'), True
 SCRIPTS = os.path.join(REFERENCE_ROOT, 'Coding_testes')
 SAMPLE = os.path.join(REFERENCE_ROOT, 'KITTI360_sample')
+if not os.path.isdir(SAMPLE):
+    # only the scripts are staged; the committed fixtures hold the sample's calibration and boxes
+    SAMPLE = os.path.join(os.path.dirname(_HERE), 'tests', 'golden', 'kitti360_sample')
 
 _provider = None
 

@@ -712,6 +712,130 @@ def test_point_pass_segment_tails_and_many_tiny_frames(LF, calib):
     assert nin > 0 and np.all(r['n_in_box'] == nin)
 
 
+def _sha16(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+
+
+def _v3_digest(stats):
+    out = []
+    for s in stats:
+        out.append({'car_id': int(s['car_id']), 'matched_bbox_id': int(s['matched_bbox_id']),
+                    'total_points': int(s['total_points']), 'points_inside_bbox': int(s['points_inside_bbox']),
+                    'points_outside_bbox': int(s['points_outside_bbox']),
+                    'inside_percentage': float(s['inside_percentage']),
+                    'outside_percentage': float(s['outside_percentage']),
+                    'inside_mask_sha': None if s['inside_mask'] is None else
+                    _sha16(np.packbits(np.asarray(s['inside_mask'], bool))),
+                    'inside_mask_len': None if s['inside_mask'] is None else int(len(s['inside_mask'])),
+                    'corners_velo_sha': None if s['corners_velo'] is None else
+                    _sha16(np.asarray(s['corners_velo'], np.float64)),
+                    'car_points_sha': _sha16(np.asarray(s['car_points'], np.float32)),
+                    'keys': sorted(s.keys())})
+    return out
+
+
+@pytest.fixture(scope='module')
+def golden_v3():
+    import json
+    import os
+    from conftest import GOLDEN
+    with open(os.path.join(GOLDEN, 'golden_v3.json')) as f:
+        return json.load(f)
+
+
+def test_v3_return_shape_matches_the_reference_vectors(LF, calib, golden, golden_v3, capsys):
+    """calculate_car_point_statistics(return_points=True) -- the V2 / V3 dicts with corners_velo,
+    inside_mask and car_points (V3:386-398, 416-428) -- and print_summary_statistics (V3:431-468)
+    against what the UNMODIFIED reference functions returned / printed (oracle/gen_golden_v3.py):
+    the function surface on every sample frame, the batch path (membership bits -> car points)
+    on all frames in one batch."""
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames']
+    pts, masks, boxes, raws = _batch_inputs(frames, cam, TVC, LF)
+    for variant, k in (('erosion3', 3), ('noerosion', 0)):
+        batch = LF.process_frames_batched(np.concatenate(pts), [len(p) for p in pts], np.concatenate(masks),
+                                          [len(m) for m in masks], boxes, cam, TVR, erosion_kernel_size=k,
+                                          return_points=True)
+        for i, fr in enumerate(frames):
+            g = golden_v3[str(fr)]
+            assert _v3_digest(batch[i]) == g[variant + '_oriented']['stats'], (fr, variant, 'batch')
+            assert LF.summary_statistics_text(batch[i]) == g[variant + '_oriented']['summary_text']
+            if fr not in (100, 947, 2449, 570):
+                continue
+            u, v, d = LF.project_points(pts[i], TVR, cam)
+            valid = LF.filter_valid(u, v, d, cam, 50)
+            em = LF.erode_masks(masks[i], 3, 1) if k else masks[i]
+            sets = LF.extract_car_points_by_mask(pts[i][valid, :3], u[valid], v[valid], em, cam)
+            colors = LF.generate_colors(len(masks[i]))
+            for oname, oriented in (('oriented', True), ('aabb', False)):
+                st = LF.calculate_car_point_statistics(sets, boxes[i], colors, 10, oriented, return_points=True)
+                want = g['%s_%s' % (variant, oname)]
+                assert _v3_digest(st) == want['stats'], (fr, variant, oname)
+                capsys.readouterr()
+                LF.print_summary_statistics(st)
+                assert capsys.readouterr().out == want['summary_text']
+                ref = P.calculate_car_point_statistics(sets, boxes[i], colors, 10, oriented, return_points=True)
+                assert _v3_digest(ref) == want['stats']
+
+
+def test_extension_metrics_match_the_oracle(LF, calib, golden):
+    """Point-level precision / recall / IoU / match ratio (north-star item 5; README.md:14, 38 -- the
+    reference names them and has no code for them, SURVEY 0.1 D3, so parity is against the oracle's
+    definition): FrameBatch.frame_stats(extended=True) and process_frames_batched(extended=True) on the 20
+    sample frames and on a synthetic batch, every value equal to oracle.pipeline.extension_metrics of the
+    oracle's own counters; match_ratio is inf when no point of the car lies outside the box."""
+    from lidar_object_detection_b200 import synthetic as S
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames']
+    pts, masks, boxes, raws = _batch_inputs(frames, cam, TVC, LF)
+    keys = ('precision', 'recall', 'point_iou', 'match_ratio')
+
+    def want_metrics(w):
+        out = []
+        for s in w['stats']:
+            if s['matched_bbox_id'] < 0:
+                out.append(P.extension_metrics(0, s['total_points'], 0))
+            else:
+                out.append(P.extension_metrics(s['points_inside_bbox'], s['total_points'],
+                                               w['n_in_box'][s['matched_bbox_id']]))
+        return out
+
+    got = LF.process_frames_batched(np.concatenate(pts), [len(p) for p in pts], np.concatenate(masks),
+                                    [len(m) for m in masks], boxes, cam, TVR, extended=True)
+    n = 0
+    for i in range(len(frames)):
+        w = P.process_frame(pts[i], raws[i], masks[i], cam, TVC, TVR)
+        wm = want_metrics(w)
+        assert _norm_stats(got[i]) == _norm_stats(w['stats'])
+        assert len(got[i]) == len(wm)
+        for s, m in zip(got[i], wm):
+            for k in keys:
+                assert s[k] == m[k], (frames[i], s['car_id'], k)       # same float64 expression: exact
+            assert 0.0 <= s['precision'] <= 1.0 and 0.0 <= s['recall'] <= 1.0 and 0.0 <= s['point_iou'] <= 1.0
+            if s['matched_bbox_id'] >= 0:
+                assert s['precision'] == s['inside_percentage'] / 100 or abs(s['precision'] - s['inside_percentage'] / 100) < 1e-12
+            n += 1
+    assert n > 80
+    # synthetic frames: tight stand-in masks make cars whose every point is inside the box -> inf ratio
+    sb = S.SyntheticBatch(12, cam, TVC, TVR, ncars=16, seed=321)
+    sb.batch.run(3, 1, 50, 10, True)
+    res = sb.batch.results()
+    infs = 0
+    for f in range(12):
+        p, m, b = sb.host_frame(f)
+        w = P.process_frame(p, b, m.astype(np.float32), cam, TVC, TVR)
+        st = sb.batch.frame_stats(res, f, extended=True)
+        for s, mm in zip(st, want_metrics(w)):
+            for k in keys:
+                assert s[k] == mm[k], (f, s['car_id'], k)
+            infs += s['match_ratio'] == float('inf')
+    assert LF.extension_metrics(5, 5, 9) == {'precision': 1.0, 'recall': 5 / 9, 'point_iou': 5 / 9,
+                                             'match_ratio': float('inf')}
+    assert LF.extension_metrics(0, 0, 0) == {'precision': 0.0, 'recall': 0.0, 'point_iou': 0.0,
+                                             'match_ratio': float('inf')}
+
+
 # ------------------------------------------------------------------ ragged / degenerate batches
 
 @pytest.mark.parametrize('persistent', [False, True])

@@ -191,3 +191,81 @@ def test_c_restatement_matches_numpy_bit_for_bit(oracle_calib):
             got = np.empty(len(xyz), np.uint8)
             lib.oracle_oriented_in(xyz.ctypes.data, len(xyz), c.ctypes.data, got.ctypes.data)
             assert np.array_equal(got.astype(bool), P.oriented_point_in_bbox(xyz, c))
+
+
+def test_v3_dicts_and_summary_text_match_the_reference_vectors():
+    """Oracle restatement of the V2 / V3 form of calculate_car_point_statistics (V3:320-428) and of
+    print_summary_statistics (V3:431-468) against tests/golden/golden_v3.json, which the unmodified
+    reference functions produced (oracle/gen_golden_v3.py); the product's text formatter is host code and
+    is checked here too."""
+    import hashlib
+    import json
+    import os
+    from conftest import GOLDEN, SAMPLE, load_boxes, load_frame
+    from lidar_object_detection_b200 import lidarfuse as LF
+    from oracle import kitti360_restated as k360, mask_provider as MP, pipeline as P
+
+    def sha(a):
+        return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+    with open(os.path.join(GOLDEN, 'golden_v3.json')) as f:
+        gold = json.load(f)
+    cam, TVC, TVR = k360.calibration_chain(SAMPLE)
+    checked = 0
+    for fr in gold['_meta']['frames'][::3]:
+        pts, raw = load_frame(fr), load_boxes(fr)
+        masks, _, _ = MP.standin_detections(raw, cam)
+        for name, k in (('erosion3', 3), ('noerosion', 0)):
+            w = P.process_frame(pts, raw, masks, cam, TVC, TVR, erosion_kernel_size=k)
+            colors = [(int(i * 60) % 255, int(i * 120) % 255, int(i * 180) % 255) for i in range(len(masks))]
+            for oname, oriented in (('oriented', True), ('aabb', False)):
+                want = gold[str(fr)]['%s_%s' % (name, oname)]
+                st = P.calculate_car_point_statistics(w['car_point_sets'], w['boxes'], colors, 10, oriented,
+                                                      return_points=True)
+                assert len(st) == len(want['stats'])
+                for s, g in zip(st, want['stats']):
+                    assert sorted(s.keys()) == g['keys']
+                    assert [int(s[k]) for k in ('car_id', 'matched_bbox_id', 'total_points', 'points_inside_bbox',
+                                                'points_outside_bbox')] == \
+                        [g[k] for k in ('car_id', 'matched_bbox_id', 'total_points', 'points_inside_bbox',
+                                        'points_outside_bbox')]
+                    assert s['inside_percentage'] == g['inside_percentage']
+                    assert sha(np.asarray(s['car_points'], np.float32)) == g['car_points_sha']
+                    if g['inside_mask_sha'] is None:
+                        assert s['inside_mask'] is None and s['corners_velo'] is None
+                    else:
+                        assert sha(np.packbits(np.asarray(s['inside_mask'], bool))) == g['inside_mask_sha']
+                        assert sha(np.asarray(s['corners_velo'], np.float64)) == g['corners_velo_sha']
+                    checked += 1
+                assert P.summary_statistics_text(st) == want['summary_text']
+                assert LF.summary_statistics_text(st) == want['summary_text']
+    assert checked > 50
+    assert LF.summary_statistics_text([]) == P.summary_statistics_text([]) == '\nNo car statistics to display.\n'
+
+
+def test_port_and_reference_functions_give_identical_rows_on_synthetic_frames():
+    """bench.py --impl reference times oracle/reference_frame.py (the reference's own functions from the
+    unmodified / staged scripts); the oracle port must give the same per-car rows on the frames the bench
+    uses (synthetic HDL-64 frames, float32 masks), for both erosion sizes of the workloads."""
+    from conftest import SAMPLE
+    from lidar_object_detection_b200 import synthetic as S
+    from oracle import kitti360_restated as k360, pipeline as P, reference_loader as RL
+    if not RL.available():
+        pytest.skip('reference scripts neither mounted nor staged')
+    from oracle import reference_frame as RF
+    cvs = RF.load()
+    cam, TVC, TVR = k360.calibration_chain(SAMPLE)
+    cars = S.sort_cars_by_image_area(S.make_cars(2, 16, 77), cam, TVR)
+    boxes = S.reference_boxes(cars, cam, TVC)
+    key = ('car_id', 'matched_bbox_id', 'total_points', 'points_inside_bbox', 'points_outside_bbox')
+    rows = 0
+    for f in range(2):
+        pts = S.numpy_frame(cars[f], 77 + f, 64, 2048)
+        masks = S.numpy_masks(cars[f], cam, TVR).astype(np.float32)
+        raw = [{'corners_cam0': b['corners_cam0']} for b in boxes[f]]
+        for k in (3, 7):
+            ref = RF.process_frame(cvs, pts, raw, masks, cam, TVC, TVR, erosion_kernel_size=k)
+            port = P.process_frame(pts, raw, masks, cam, TVC, TVR, erosion_kernel_size=k)['stats']
+            assert [[int(s[c]) for c in key] for s in ref] == [[int(s[c]) for c in key] for s in port]
+            assert [s['inside_percentage'] for s in ref] == [s['inside_percentage'] for s in port]
+            rows += len(ref)
+    assert rows > 20
