@@ -196,6 +196,214 @@ class ClockSampler:
                 'samples': len(mhz)}
 
 
+# --------------------------------------------------------------------------- host cores of a rank
+
+def _gpu_numa_node(torch, index):
+    """NUMA node of GPU `index` from sysfs (-1 when the platform does not say)."""
+    try:
+        p = torch.cuda.get_device_properties(index)
+        bdf = '%04x:%02x:%02x.0' % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open('/sys/bus/pci/devices/%s/numa_node' % bdf) as fh:
+            return int(fh.read().strip())
+    except Exception:
+        return -1
+
+
+def _node_cpus(node):
+    try:
+        with open('/sys/devices/system/node/node%d/cpulist' % node) as fh:
+            out = []
+            for part in fh.read().strip().split(','):
+                a, _, b = part.partition('-')
+                out += list(range(int(a), int(b or a) + 1))
+            return out
+    except Exception:
+        return []
+
+
+def bind_host(torch, local, world):
+    """At N > 1 every rank gets a disjoint set of host cores on its GPU's NUMA node (its pack threads
+    and the pages of its pinned buffers then live there); at N = 1 the process keeps every core."""
+    allowed = sorted(os.sched_getaffinity(0))
+    node = _gpu_numa_node(torch, local)
+    mine = allowed
+    if world > 1:
+        nodes = [_gpu_numa_node(torch, r) for r in range(world)]
+        peers = [r for r in range(world) if nodes[r] == node]          # ranks that share this node's cores
+        pool = [c for c in _node_cpus(node) if c in allowed] if node >= 0 else []
+        if len(pool) < len(peers):                                      # no NUMA information: split what we may use
+            pool, peers = allowed, list(range(world))
+        k = peers.index(local)
+        per = max(1, len(pool) // len(peers))
+        mine = pool[k * per:(k + 1) * per] or pool
+        try:
+            os.sched_setaffinity(0, mine)
+        except Exception:
+            mine = allowed
+    return {'threads': max(1, len(mine)), 'shared_host': world > 1,
+            'report': {'cores': len(mine), 'first_core': mine[0], 'numa_node': node, 'bound': world > 1}}
+
+
+# --------------------------------------------------------------------------- side measurements
+
+def _peak_gbs():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as fh:
+            return float(json.load(fh)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def side_cfg4(torch, dist, D, S, world, rank, local, dev, cam, TVC, TVR, sb0, exch, total_frames=65536, pool=8,
+              repeats=3):
+    """BASELINE.json configs[3]: 65 536 HDL-64 frames sharded over the ranks, 1024 per batch, a pool of
+    distinct resident batches per rank walked round-robin (uint8 masks of a whole shard do not fit HBM below
+    N = 8), the per-car table of every batch exchanged as in the headline step.  Strong scaling: the job is
+    fixed.  Checks: every exchanged table equals the one recorded for that pool batch, row totals add up."""
+    FB = 1024
+    per_rank = total_frames // world
+    nb = per_rank // FB
+    if nb * FB * world != total_frames:
+        return {'skipped': 'world size does not divide the job into 1024-frame batches'}
+    pool = min(pool, nb)
+    stream = torch.cuda.current_stream(dev)
+    sbs = [sb0] + [S.SyntheticBatch(FB, cam, TVC, TVR, ncars=NCARS, seed=SEED, rings=RINGS, azimuths=AZ, device=local,
+                                    first_frame=(world + rank) * FB + (i - 1) * world * FB + 7 * total_frames)
+                   for i in range(1, pool)]
+    if exch is not None and hasattr(exch, 'bind'):
+        for b in sbs:
+            exch.bind(b.batch.h_mask_off, b.n_boxes)
+    want, rows = [], []
+    for b in sbs:
+        b.batch.run(KSIZE, 1, 50, 10, True)
+        if exch is not None:
+            t, _ = exch.exchange_batch(b.batch)
+            want.append(t.clone())
+            rows.append(exch.agg.clone())
+        else:
+            want.append(torch.cat([b.batch.total, b.batch.best_idx, b.batch.best_cnt]).clone())
+            rows.append(b.batch.agg.clone())
+    torch.cuda.synchronize(dev)
+    ok = torch.ones((), dtype=torch.int32, device=dev)
+    agg_sum = torch.zeros_like(rows[0])
+
+    def job(check):
+        for i in range(nb):
+            b = sbs[i % pool].batch
+            b.run(KSIZE, 1, 50, 10, True)
+            if exch is not None:
+                t, _ = exch.exchange_batch(b)
+                got, agg = t, exch.agg
+            else:
+                got, agg = None, b.agg
+            if check:
+                if got is None:
+                    got = torch.cat([b.total, b.best_idx, b.best_cnt])
+                ok.mul_((got == want[i % pool]).all().to(torch.int32))
+                agg_sum.add_(agg)
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    job(True)                                              # warm-up pass, with the checks
+    sync()
+    expect = sum(rows[i % pool] for i in range(nb))
+    good = bool(ok.item()) and torch.equal(agg_sum, expect)
+    times = []
+    for _ in range(repeats):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync()
+        e0.record(stream)
+        job(False)
+        e1.record(stream)
+        sync()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        times.append(float(t.item()))
+    flag = torch.tensor([int(good)], device=dev)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if not bool(flag.item()):
+        raise SystemExit('PARITY FAILURE: cfg4 job tables / row totals differ')
+    ms = sorted(times)[len(times) // 2]
+    n_pts = sb0.n
+    out = {'value': total_frames * n_pts / (ms * 1e-3), 'unit': 'points/s', 'scaling': 'strong', 'job_ms': ms,
+           'job_ms_all': times, 'frames': total_frames, 'batches_per_rank': nb, 'frames_per_batch': FB,
+           'distinct_resident_frames_per_rank': pool * FB,
+           'workload': 'cfg4: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes over %d GPU(s)' % (
+               total_frames, n_pts, NCARS, W_IMG, H_IMG, NCARS, world),
+           'checks': {'tables_equal_recorded_and_row_totals_add_up': True, 'rows': int(expect[1].item()),
+                      'matched_rows': int(expect[2].item())}}
+    del sbs[1:]
+    torch.cuda.empty_cache()
+    return out
+
+
+def side_cfg5(torch, dist, D, S, world, rank, local, dev, cam, TVC, TVR, steps):
+    """BASELINE.json configs[4]: 64 frames x 2 097 152 points x 64 masks, 7x7 ellipse erosion, per rank."""
+    w = WORKLOADS['cfg5']
+    sb5 = S.SyntheticBatch(w['frames'], cam, TVC, TVR, ncars=w['ncars'], seed=SEED + 5, rings=w['rings'],
+                           azimuths=w['az'], device=local, first_frame=rank * w['frames'])
+    b = sb5.batch
+    ex = None
+    if world > 1:
+        ex = D.CounterExchange(world * w['frames'], w['ncars'], rank, world, dev)
+        ex.bind(b.h_mask_off, sb5.n_boxes)
+    stream = torch.cuda.current_stream(dev)
+
+    def step(mark=None):
+        b.run(w['ksize'], 1, 50, 10, True, mark=mark)
+        if ex is not None:
+            ex.exchange_batch(b)
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(3):
+        step()
+    sync()
+    marks = []
+
+    def mk(lst):
+        def mark(name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            lst.append((name, e))
+        return mark
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        lst = []
+        step(mk(lst))
+        marks.append(dict(lst))
+    e1.record(stream)
+    sync()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    km = {k2: sum(d[k1].elapsed_time(d[k2]) for d in marks) / len(marks)
+          for k1, k2 in (('zero', 'erode_pack'), ('erode_pack', 'fuse'), ('fuse', 'car_stats'))}
+    peak, _ = _peak_gbs()
+    sbytes = sum(16 * sb5.n + w['ncars'] * H_IMG * W_IMG + 192 * nb + 8 * w['ncars'] * (nb + 3) for nb in sb5.n_boxes)
+    fuse_gbs = 16.0 * sb5.n * w['frames'] / (km['fuse'] * 1e-3) / 1e9
+    erode_gbs = float(w['ncars']) * H_IMG * W_IMG * w['frames'] / (km['erode_pack'] * 1e-3) / 1e9
+    return {'value': world * w['frames'] * sb5.n / (ms * 1e-3), 'unit': 'points/s', 'ms_per_step': ms, 'steps': steps,
+            'workload': 'cfg5: %d frames x %d pts x %d masks (%dx%d uint8) x <=%d boxes per GPU, 7x7 ellipse erosion'
+                        % (w['frames'], sb5.n, w['ncars'], W_IMG, H_IMG, w['ncars']),
+            'kernel_ms': km, 'algorithmic_bytes_per_step': sbytes,
+            'step_frac_of_measured_peak': sbytes / (ms * 1e-3) / 1e9 / peak,
+            'roofline': {'kernel': 'lf_fuse_kernel (dominant on this workload)', 'bound': 'hbm', 'achieved': fuse_gbs,
+                         'peak': peak, 'unit': 'GB/s', 'frac': fuse_gbs / peak,
+                         'algorithmic_bytes_per_launch': 16 * sb5.n * w['frames']},
+            'erode_frac_of_measured_peak': erode_gbs / peak}
+
+
 # --------------------------------------------------------------------------- GPU arm
 
 def run_gpu(args):
@@ -212,6 +420,7 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     frames = FRAMES
+    host_bind = None
 
     # CPU baseline first (rank 0, N = 1 only): spawned host processes, GPU idle meanwhile
     cpu = None
@@ -221,6 +430,7 @@ def run_gpu(args):
                'sample': '%d synthetic frames (%d per host process, %d processes, OPENBLAS/cv2 threads = 1), '
                          '%.1f s wall; %s' % (c['frames'], args.cpu_frames, c['cores'], c['seconds'], CPU_KIND_NOTE[c['kind']])}
 
+    host_bind = bind_host(torch, local, world)
     from lidar_object_detection_b200 import distributed as D, kitti360 as K, synthetic as S
     cam, TVC, TVR = K.calibration_chain(CALIB_ROOT)
     sb = S.SyntheticBatch(frames, cam, TVC, TVR, ncars=NCARS, seed=SEED, rings=RINGS, azimuths=AZ, device=local,
@@ -265,18 +475,31 @@ def run_gpu(args):
         step()
     sync_all()
 
-    # parity spot check against the oracle (checker only): two frames of this very batch
+    # parity spot check against the oracle (checker only): frames of this very batch, spread over it --
+    # 32 for HDL-64 frames, 2 for the multi-sweep workload (the oracle needs seconds per such frame);
+    # counters, the decision (best box, best count) and the per-car rows
     parity_frames = 0
     if rank == 0 and not args.no_parity:
         from oracle import pipeline as P
         res = batch.results()
-        for f in (0, frames - 1):
+        n_check = min(frames, args.parity_frames if n_pts <= (1 << 18) else 2)
+        for f in sorted({int(x) for x in np.linspace(0, frames - 1, n_check)}):
             pts, masks, boxes = sb.host_frame(f)
             want = P.process_frame(pts, boxes, masks.astype(np.float32), cam, TVC, TVR, erosion_kernel_size=KSIZE)
-            got_t = res['total'][batch.h_mask_off[f]:batch.h_mask_off[f + 1]]
+            m0, m1 = batch.h_mask_off[f], batch.h_mask_off[f + 1]
+            got_t = res['total'][m0:m1]
             got_i = res['inside'][batch.h_cnt_off[f]:batch.h_cnt_off[f + 1]].reshape(want['inside'].shape)
-            if not (np.array_equal(got_t, want['total']) and np.array_equal(got_i, want['inside'])
-                    and res['n_valid'][f] == want['valid'].sum()):
+            ok = np.array_equal(got_t, want['total']) and np.array_equal(got_i, want['inside']) \
+                and res['n_valid'][f] == want['valid'].sum()
+            wi = want['inside']
+            w_best = wi.max(axis=1) if wi.size else np.zeros(len(wi), np.int64)
+            w_idx = np.where(w_best > 0, wi.argmax(axis=1), -1) if wi.size else -np.ones(len(wi), np.int64)
+            ok = ok and np.array_equal(res['best_idx'][m0:m1], w_idx) and np.array_equal(res['best_cnt'][m0:m1], w_best)
+            got_rows = [(s['car_id'], s['matched_bbox_id'], s['total_points'], s['points_inside_bbox'])
+                        for s in batch.frame_stats(res, f)]
+            want_rows = [(s['car_id'], s['matched_bbox_id'], s['total_points'], int(s['points_inside_bbox']))
+                         for s in want['stats']]
+            if not (ok and got_rows == want_rows):
                 raise SystemExit('PARITY FAILURE on synthetic frame %d: refusing to report a number' % f)
             parity_frames += 1
 
@@ -323,54 +546,51 @@ def run_gpu(args):
             kern.setdefault(b, []).append(d[a].elapsed_time(d[b]))
     kern_ms = {k: sum(v) / len(v) for k, v in kern.items()}
 
-    # ---- end to end: host buffers in, host counters out, copies inside the timed region
-    e2e = None
-    if not args.no_e2e:
-        h_pts = torch.empty(batch.points.shape, dtype=batch.points.dtype, pin_memory=True)
-        h_masks = torch.empty(batch.masks.shape, dtype=batch.masks.dtype, pin_memory=True)
-        h_out = torch.empty(batch.counters.shape, dtype=batch.counters.dtype, pin_memory=True)
-        h_pts.copy_(batch.points)
-        h_masks.copy_(batch.masks)
-        torch.cuda.synchronize(dev)
+    launches_per_step = int(batch.launches_per_run - 1) + (0 if exch is None else 2)   # kernels of ours (memsets not counted)
 
-        def e2e_step():
-            batch.upload(h_pts, h_masks)
-            step()
-            batch.download(h_out)
+    # ---- end to end through the public API: pinned HOST points + masks in, per-car table on the HOST out;
+    # the H2D copies, the kernels, the D2H of the counter block and the vectorised table are all inside the
+    # timed region.  Three input encodings of the same masks:
+    #   f32_packed  float32 host masks (the reference's boundary format, cvs_erosion.py:87, 103 -- what the
+    #               CPU arm is fed), binarised + bit-packed on the host (lf_pack_masks_host) for the transfer
+    #   u8_packed   uint8 host masks, packed the same way
+    #   u8_plain    uint8 host masks copied as they are
+    # The headline `e2e` is f32_packed (like for like with the reference arm); the others stay beside it.
+    e2e, packed_in = None, None
+    from lidar_object_detection_b200 import io as IO, lidarfuse as LF
+    words = LF.erode_pack(batch.masks, 0, 0, device=local).words
+    pb = LF.FrameBatch(batch.points, [n_pts] * frames, LF.PackedMasks(words, H_IMG, W_IMG, raw=True), [NCARS] * frames,
+                       batch.boxes, sb.n_boxes, cam, TVR, device=local)
+
+    def pstep(mark=None):
+        pb.run(KSIZE, 1, 50, 10, True, mark=mark)
+        if exch is not None:
+            exch.exchange_batch(pb)
+
+    def time_e2e(b, stepfn, h_pts, h_masks, n, **kw):
+        h_out = b.download()                                  # pinned, allocated once
+
+        def one():
+            b.upload(h_pts, h_masks, **kw)
+            stepfn()
+            b.download(h_out)
             stream.synchronize()
+            return b.table(h_out, 10)                         # the rows the caller gets (cvs_erosion.py:197-225)
 
-        e2e_step()
+        tab = one()
         sync_all()
-        n_e2e = max(1, min(args.e2e_steps, K_steps))
         t0 = time.perf_counter()
-        for _ in range(n_e2e):
-            e2e_step()
+        for _ in range(n):
+            tab = one()
         sync_all()
-        dt = (time.perf_counter() - t0) / n_e2e
+        dt = (time.perf_counter() - t0) / n
         if world > 1:
             t = torch.tensor([dt], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e2e = {'value': world * frames * n_pts / dt, 'unit': 'points/s',
-               'h2d_bytes_per_step': int(h_pts.numel() * 4 + h_masks.numel()),
-               'd2h_bytes_per_step': int(h_out.numel() * 4), 'steps': n_e2e, 'ms_per_step': dt * 1e3,
-               'api': 'FrameBatch.upload (pinned host points + uint8 masks as they are) / run / download (counters)'}
-        t_end = time.time()
+        return dt, tab, h_out
 
-    # ---- secondary accounting (SURVEY 8(d) "packed-masks-in"): the masks cross PCIe and enter HBM at one
-    # bit per pixel (lf_pack_masks_host on the sending side), erosion runs on the device from the words
-    packed_in = None
     if not args.no_packed:
-        from lidar_object_detection_b200 import io as IO, lidarfuse as LF
-        words = LF.erode_pack(batch.masks, 0, 0, device=local).words
-        pb = LF.FrameBatch(batch.points, [n_pts] * frames, LF.PackedMasks(words, H_IMG, W_IMG, raw=True), [NCARS] * frames,
-                           batch.boxes, sb.n_boxes, cam, TVR, device=local)
-
-        def pstep(mark=None):
-            pb.run(KSIZE, 1, 50, 10, True, mark=mark)
-            if exch is not None:
-                exch.exchange_batch(pb)
-
         for _ in range(3):
             pstep()
         sync_all()
@@ -401,49 +621,90 @@ def run_gpu(args):
                      'algorithmic_bytes_per_step': pbytes, 'achieved_gbs': pbytes / (pms * 1e-3) / 1e9,
                      'erode_gbs_in_plus_out': 2 * frames * NCARS * H_IMG * wpr * 4 / (er_ms * 1e-3) / 1e9,
                      'note': 'lf_erode_pack mode 3 (masks arrive as uint32 words); results identical with the uint8 step'}
-        if e2e is not None:
-            hm = h_masks.numpy()
-            h_words = torch.empty(words.shape, dtype=words.dtype, pin_memory=True)
-            hw = h_words.numpy()
-            threads = max(1, (os.cpu_count() or 1) // world)       # the ranks share the host's cores
-
-            def e2e_packed_step():
-                pb.upload(h_pts, h_masks, threads=threads)         # packs a slice while the previous one is on the wire
-                pstep()
-                pb.download(h_out)
-                stream.synchronize()
-
-            e2e_packed_step()
-            if not torch.equal(h_out, batch.counters.cpu()):
-                raise SystemExit('PARITY FAILURE: host-packed end-to-end step differs')
-            sync_all()
-            tp0 = time.perf_counter()
-            for _ in range(n_e2e):
-                e2e_packed_step()
-            sync_all()
-            dtp = (time.perf_counter() - tp0) / n_e2e
-            if world > 1:
-                t = torch.tensor([dtp], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                dtp = float(t.item())
-            tq0 = time.perf_counter()
-            IO.pack_masks(hm, threads=threads, out=hw)
-            tq = time.perf_counter() - tq0
-            packed_in['e2e'] = {'value': world * frames * n_pts / dtp, 'unit': 'points/s', 'ms_per_step': dtp * 1e3,
-                                'h2d_bytes_per_step': int(h_pts.numel() * 4 + words.numel() * 4),
-                                'd2h_bytes_per_step': int(h_out.numel() * 4), 'host_pack_threads': threads,
-                                'host_pack_gbs_alone': hm.nbytes / tq / 1e9,
-                                'api': 'FrameBatch.upload on PackedMasks(raw=True): lf_pack_masks_host in 16 slices '
-                                       'overlapped with their H2D / run / download; pinned uint8 masks in, counters out'}
         t_end = time.time()
-        del pb
-        # the end-to-end headline is the faster of the two host-to-host calls; the other stays beside it
-        if e2e is not None and 'e2e' in packed_in and packed_in['e2e']['value'] > e2e['value']:
-            plain = e2e
-            e2e = dict(packed_in['e2e'], variant='masks bit-packed on the host for the transfer (erosion on the device)',
-                       plain_transfer=plain)
-        elif e2e is not None:
-            e2e['variant'] = 'masks sent as uint8 arrays'
+
+    if not args.no_e2e:
+        import psutil
+        n_e2e = max(1, min(args.e2e_steps, K_steps))
+        threads = host_bind['threads']
+        h_pts = torch.empty(batch.points.shape, dtype=batch.points.dtype, pin_memory=True)
+        h_pts.copy_(batch.points)
+        want = batch.table(None, 10)
+        variants = {}
+        d2h = int(batch.counters.numel() * 4)
+
+        def record(name, dt, tab, h2d, note, extra=None):
+            for k in want:
+                if not np.array_equal(tab[k], want[k]):
+                    raise SystemExit('PARITY FAILURE: end-to-end variant %s returns another per-car table (%s)' % (name, k))
+            variants[name] = dict({'value': world * frames * n_pts / dt, 'unit': 'points/s', 'ms_per_step': dt * 1e3,
+                                   'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': d2h, 'steps': n_e2e,
+                                   'rows_per_step': int(len(tab['frame'])), 'api': note}, **(extra or {}))
+
+        # uint8 host masks
+        h_u8 = torch.empty(batch.masks.shape, dtype=torch.uint8, pin_memory=True)
+        h_u8.copy_(batch.masks)
+        torch.cuda.synchronize(dev)
+        dt, tab, _ = time_e2e(batch, step, h_pts, h_u8, n_e2e)
+        record('u8_plain', dt, tab, h_pts.numel() * 4 + h_u8.numel(),
+               'FrameBatch.upload (pinned uint8 masks copied as they are) / run / download / table')
+        tmp_words = np.empty(tuple(words.shape), np.uint32)
+        pack_u8_gbs = 0.0
+        for _ in range(2):
+            tq0 = time.perf_counter()
+            IO.pack_masks(h_u8.numpy(), threads=threads, out=tmp_words)
+            pack_u8_gbs = max(pack_u8_gbs, h_u8.numel() / (time.perf_counter() - tq0) / 1e9)
+        del tmp_words
+        dt, tab, _ = time_e2e(pb, pstep, h_pts, h_u8, n_e2e, threads=threads)
+        record('u8_packed', dt, tab, h_pts.numel() * 4 + words.numel() * 4,
+               'FrameBatch.upload on PackedMasks(raw=True): lf_pack_masks_host in 16 slices overlapped with their H2D / '
+               'run / download / table', {'host_pack_threads': threads, 'host_pack_gbs_alone': pack_u8_gbs})
+        del h_u8
+        # float32 host masks: 4 bytes per pixel of pinned host memory -- only when the host has room for it
+        f32_bytes = batch.masks.numel() * 4
+        free = psutil.virtual_memory().available
+        if not args.no_f32 and free > 2.5 * f32_bytes * max(1, world if host_bind['shared_host'] else 1):
+            h_f32 = torch.empty(batch.masks.shape, dtype=torch.float32, pin_memory=True)
+            sl = max(1, len(batch.masks) // 64)
+            for a0 in range(0, len(batch.masks), sl):          # converted on the device slice by slice, copied back
+                h_f32[a0:a0 + sl].copy_(batch.masks[a0:a0 + sl].to(torch.float32))
+            torch.cuda.synchronize(dev)
+            pack_f32_gbs = 0.0
+            for _ in range(2):                                # best of two: the first pass touches the pages
+                tq0 = time.perf_counter()
+                IO.pack_masks(h_f32.numpy(), threads=threads, out=pb._h_words.numpy())
+                pack_f32_gbs = max(pack_f32_gbs, f32_bytes / (time.perf_counter() - tq0) / 1e9)
+            dt, tab, _ = time_e2e(pb, pstep, h_pts, h_f32, n_e2e, threads=threads)
+            host_bytes = f32_bytes + 2 * words.numel() * 4 + h_pts.numel() * 4     # mask read + packed write + DMA reads
+            record('f32_packed', dt, tab, h_pts.numel() * 4 + words.numel() * 4,
+                   'FrameBatch.upload on PackedMasks(raw=True) from pinned FLOAT32 host masks (the reference\'s boundary '
+                   'format): lf_pack_masks_host mode 1 in 16 slices overlapped with their H2D / run / download / table',
+                   {'host_pack_threads': threads, 'host_pack_gbs_alone': pack_f32_gbs,
+                    'host_mask_bytes_per_step': int(f32_bytes),
+                    'host_dram_bytes_per_step': int(host_bytes),
+                    'host_dram_floor_ms': host_bytes / (pack_f32_gbs * 1e9) * 1e3,
+                    'host_floor_note': 'bytes through host DRAM per step / the read rate the packer reaches alone on '
+                                       'this rank\'s cores = the time the host memory system needs whatever the GPU does'})
+            del h_f32
+        head = 'f32_packed' if 'f32_packed' in variants else 'u8_packed'
+        e2e = dict(variants[head], variant=head, input_dtype='float32 masks' if head == 'f32_packed' else 'uint8 masks',
+                   host=host_bind['report'], other_variants={k: v for k, v in variants.items() if k != head})
+        if packed_in is not None:
+            packed_in['e2e'] = variants['u8_packed']
+        t_end = time.time()
+    del pb
+
+    # ---- BASELINE.json configs[3] and configs[4] beside the headline, measured by this very run with the
+    # shipped kernels: cfg4 = the 65 536-frame job over the N ranks (STRONG scaling), cfg5 = dense stress
+    cfg4 = None
+    if not args.no_cfg4 and args.workload == 'cfg3' and frames == 1024:
+        cfg4 = side_cfg4(torch, dist, D, S, world, rank, local, dev, cam, TVC, TVR, sb, exch)
+    cfg5 = None
+    if not args.no_cfg5 and args.workload == 'cfg3':
+        del batch
+        sb.batch = None
+        torch.cuda.empty_cache()
+        cfg5 = side_cfg5(torch, dist, D, S, world, rank, local, dev, cam, TVC, TVR, max(5, min(K_steps, 20)))
 
     clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
     if rank == 0:
@@ -460,10 +721,15 @@ def run_gpu(args):
         kname, kkey, tkey = 'lf_erode_fast_kernel<%s> (lf_erode_pack)' % se_name, 'erode_pack', 'lf_erode_fast_kernel'
         mask_bytes = frames * NCARS * H_IMG * W_IMG
         ach = mask_bytes / (kern_ms[kkey] * 1e-3) / 1e9
-        traffic = None
+        # DRAM bytes of one launch of the dominant kernel from the committed ncu capture (not measured by this
+        # run: `traffic_source` names the file and the capture it summarises; null when it does not cover the kernel)
+        traffic, traffic_src = None, None
         try:
-            with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json' if args.workload == 'cfg3' else 'none')) as fh:
-                traffic = json.load(fh).get(tkey + '_dram_bytes_per_launch')
+            with open(os.path.join(ROOT, 'profiles', 'dram_traffic.json')) as fh:
+                tj = json.load(fh)
+            if args.workload == 'cfg3' and tj.get(tkey + '_dram_bytes_per_launch'):
+                traffic = tj[tkey + '_dram_bytes_per_launch']
+                traffic_src = 'profiles/dram_traffic.json <- ' + str(tj.get('source'))
         except Exception:
             pass
         line = {
@@ -472,15 +738,15 @@ def run_gpu(args):
             'vs_baseline': None, 'dtype': 'f64 projection/containment, u32 bit-masks, i32 counters',
             'data': 'synthetic',
             'config': bench_config(args.workload, frames, n_pts, world, step_bytes, exch_kind if world > 1 else None),
-            'gpu_launches': int(batch.launches_per_run - 1) * K_steps,
+            'gpu_launches': launches_per_step * K_steps,
             'kernel_ms': kern_ms,
             'step_hbm': {'algorithmic_bytes_per_step': step_bytes, 'achieved_gbs': step_bytes / (ms_step * 1e-3) / 1e9,
                          'frac_of_measured_peak': step_bytes / (ms_step * 1e-3) / 1e9 / peak,
                          'frac_of_8000_nominal': step_bytes / (ms_step * 1e-3) / 1e9 / 8000.0},
             'roofline': {'kernel': kname, 'bound': 'hbm', 'achieved': ach, 'peak': peak,
-                         'unit': 'GB/s', 'frac': ach / peak, 'traffic': traffic, 'peak_source': peak_src,
+                         'unit': 'GB/s', 'frac': ach / peak, 'traffic': traffic, 'traffic_source': traffic_src, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': mask_bytes},
-            'e2e': e2e, 'packed_masks_in': packed_in, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,
+            'e2e': e2e, 'cfg4_job': cfg4, 'cfg5': cfg5, 'packed_masks_in': packed_in, 'cpu_baseline': cpu, 'clocks': clocks, 'parity_checked_frames': parity_frames,
         }
         print(json.dumps(line))
     if world > 1:
@@ -527,8 +793,12 @@ def main():
                     help='frames each host process times for cpu_baseline (~70 ms each: ~1.5 s wall, ~20 core-seconds)')
     ap.add_argument('--e2e-steps', type=int, default=3)
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-cfg4', action='store_true', help='skip the 65 536-frame strong-scaling job (cfg4_job object)')
+    ap.add_argument('--no-cfg5', action='store_true', help='skip the dense-stress side measurement (cfg5 object)')
+    ap.add_argument('--no-f32', action='store_true', help='skip the float32-host-mask end-to-end variant (34.7 GB pinned)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-parity', action='store_true')
+    ap.add_argument('--parity-frames', type=int, default=32, help='frames of the batch checked against the oracle')
     ap.add_argument('--no-packed', action='store_true', help='skip the packed-masks-in secondary measurement')
     ap.add_argument('--exchange', default='peer', choices=['peer', 'nccl'],
                     help='N > 1: per-car table exchanged by stores into peer memory (default) or by the NCCL all-reduce')

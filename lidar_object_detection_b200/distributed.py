@@ -61,6 +61,10 @@ class CounterExchange:
         mo = torch.as_tensor(np.asarray(mask_off), device=dev, dtype=torch.int64)
         F = mo.numel() - 1
         counts = mo[1:] - mo[:-1]
+        if F != self.hi - self.lo:
+            raise ValueError('layout has %d frames, this rank\'s shard of the table has %d' % (F, self.hi - self.lo))
+        if F and int(counts.max()) > self.max_cars:
+            raise ValueError('a frame has %d masks, the table has %d car slots per frame' % (int(counts.max()), self.max_cars))
         frame_of = torch.repeat_interleave(torch.arange(F, device=dev), counts)
         car_of = torch.arange(int(mo[-1]), device=dev) - mo[frame_of]
         self._dest = ((self.lo + frame_of) * self.max_cars + car_of) * TABLE_COLS
@@ -92,12 +96,22 @@ class CounterExchange:
         return self.table, self.agg
 
 
+def _check_batch(batch, n_frames, max_cars):
+    """A batch must be this rank's shard and fit the table's car slots (rows would be dropped or mixed)."""
+    if batch.F != n_frames:
+        raise ValueError('batch holds %d frames, this rank\'s shard of the table has %d' % (batch.F, n_frames))
+    if batch.max_m > max_cars:
+        raise ValueError('a frame has %d masks, the table has %d car slots per frame' % (batch.max_m, max_cars))
+
+
 class PeerCounterExchange:
     """The same exchange without a reduction: ``lf_publish_table`` stores this rank's rows and
     aggregates straight into every rank's copy of the table (NVLink peer stores into torch
     symmetric memory), then ONE signal-pad barrier orders the ranks -- two launches per batch
     instead of zero-fill + scatter + all-reduce.  Tables are int32 [F_global, max_cars, 4] and
-    double-buffered: the table ``exchange_batch`` returns stays valid until the call after next.
+    double-buffered: the table ``exchange_batch`` returns is valid for work ENQUEUED (on the same stream)
+    before the next ``exchange_batch`` -- a peer that has passed barrier i+1 may already be storing step i+2
+    into the half that holds step i, so clone it if it must outlive the next call.
     Needs one node with peer access (NVLink / NVSwitch); ``available()`` tells."""
 
     @staticmethod
@@ -138,6 +152,7 @@ class PeerCounterExchange:
         (``.agg`` sums them)."""
         from ._abi import check, ptr
         ctx = batch.ctx
+        _check_batch(batch, self.hi - self.lo, self.max_cars)
         half = self._step & 1
         self._step += 1
         off = half * self._half

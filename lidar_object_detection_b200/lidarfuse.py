@@ -664,6 +664,10 @@ class FrameBatch:
             self.packed = PackedMasks(torch.empty((n_m, H, (W + 31) // 32), dtype=torch.int32,
                                                   device=ctx.device), H, W)
         elif isinstance(self.masks, PackedMasks):
+            if n_m and (self.masks.H, self.masks.W) != (camera.height, camera.width):
+                # final packed masks are read with the camera's row stride: another size would be read out of bounds
+                raise ValueError('final PackedMasks must be at camera resolution (%dx%d); use resize_pack first'
+                                 % (camera.width, camera.height))
             self.packed = self.masks
         else:
             H, W = camera.height, camera.width
@@ -833,6 +837,36 @@ class FrameBatch:
         agg = c[self._nz:].view(np.int64).copy()
         return {'total': total, 'n_in_box': n_in_box, 'n_valid': n_valid, 'inside': inside, 'agg': agg,
                 'best_idx': c[self._ob:self._ob + sm].copy(), 'best_cnt': c[self._ob + sm:self._ob + 2 * sm].copy()}
+
+    def table(self, host=None, min_points=10):
+        """The per-car table of the whole batch, vectorised on the host from ONE copy of the counter block
+        (``download()`` / ``results``): a dict of equally long arrays {frame (index in the batch), car_id,
+        matched_bbox_id, total_points, points_inside_bbox, points_outside_bbox, inside_percentage,
+        outside_percentage} with one row per car that has points in a frame that has boxes and gated
+        points -- the rows ``calculate_car_point_statistics`` returns (cvs_erosion.py:197-225), in order."""
+        c = self.counters.cpu().numpy() if host is None else (host.numpy() if isinstance(host, torch.Tensor) else host)
+        sm, sb = int(self.h_mask_off[-1]), int(self.h_box_off[-1])
+        if getattr(self, '_h_car_frame', None) is None:
+            nm = np.diff(self.h_mask_off)
+            self._h_car_frame = np.repeat(np.arange(self.F, dtype=np.int64), nm)
+            self._h_car_id = np.arange(sm, dtype=np.int64) - np.repeat(self.h_mask_off[:-1].astype(np.int64), nm)
+            self._h_car_hasbox = np.repeat(np.diff(self.h_box_off) > 0, nm)
+        o = self._o
+        total = c[o:o + sm]
+        n_valid = c[o + sm + sb:o + sm + sb + self.F]
+        bi = c[self._ob:self._ob + sm]
+        bc = c[self._ob + sm:self._ob + 2 * sm]
+        keep = (total > 0) & self._h_car_hasbox & (n_valid[self._h_car_frame] > 0)
+        total = total[keep].astype(np.int64)
+        bi, bc = bi[keep], bc[keep].astype(np.int64)
+        matched = (bi >= 0) & (bc >= min_points)
+        inside = np.where(matched, bc, 0)
+        outside = total - inside
+        return {'frame': self._h_car_frame[keep], 'car_id': self._h_car_id[keep],
+                'matched_bbox_id': np.where(matched, bi, -1).astype(np.int64), 'total_points': total,
+                'points_inside_bbox': inside, 'points_outside_bbox': outside,
+                'inside_percentage': np.where(matched, (inside / total) * 100, 0.0),
+                'outside_percentage': np.where(matched, (outside / total) * 100, 100.0)}
 
     def frame_stats(self, res, f, min_points=10, colors=None, extended=False, return_points=False,
                     use_oriented=True):
