@@ -186,6 +186,25 @@ int lf_mask_gather(lf_ctx* ctx, const uint32_t* packed /*DEVICE [m][H][wpr]*/, i
                    const int64_t* u /*DEVICE*/, const int64_t* v /*DEVICE*/, int64_t n,
                    uint64_t* bits /*DEVICE [n]*/, void* stream);
 
+/* A4 stand-alone: valid[i] = 0 <= u < W, 0 <= v < H, 0 < depth < max_depth on already projected arrays
+ * (the boolean gate of cvs_erosion.py:359; 30 m in V4:275, V5:508, seg_with_pointcloud.py:154-158). */
+int lf_filter_valid(lf_ctx* ctx, const int64_t* u /*DEVICE*/, const int64_t* v /*DEVICE*/, const double* depth /*DEVICE*/,
+                    int64_t n, int W, int H, double max_depth, uint8_t* valid /*DEVICE [n]*/, void* stream);
+
+/* A6 compaction: car_points = points_valid[mask_indices] for ALL masks of a frame at once
+ * (extract_car_points_by_mask, cvs_erosion.py:156-160), order-preserving, from the membership words of
+ * lf_mask_gather.  Two calls around one small read-back:
+ *   lf_car_counts   counts[c] = points mask c selects (DEVICE int32 [m]); fills `scratch` (DEVICE int32
+ *                   [lf_car_scratch_elems(n, m)], 8-byte aligned) with the offsets lf_car_compact needs
+ *   lf_car_compact  out_xyz (DEVICE [sum counts][3], float32 or float64 like xyz) holds car 0's points, then
+ *                   car 1's, ... each in point order; out_idx (optional) the point indices. */
+int64_t lf_car_scratch_elems(int64_t n, int m);
+int lf_car_counts(lf_ctx* ctx, const uint64_t* bits /*DEVICE [n]*/, int64_t n, int m, int32_t* scratch /*DEVICE*/,
+                  int32_t* counts /*DEVICE [m]*/, void* stream);
+int lf_car_compact(lf_ctx* ctx, const uint64_t* bits /*DEVICE [n]*/, int64_t n, int m, const void* xyz /*DEVICE*/,
+                   int is_f64, int stride_elems, const int32_t* scratch /*DEVICE, from lf_car_counts*/,
+                   void* out_xyz /*DEVICE*/, int32_t* out_idx /*DEVICE or NULL*/, void* stream);
+
 /* A8 stand-alone: out[i] = point i inside the box (oriented_point_in_bbox,
  * cvs_erosion.py:114-145; point_in_bbox, V1:118-139 when use_oriented == 0).
  * xyz: DEVICE float32 or float64 rows of stride_elems elements (x, y, z first). */

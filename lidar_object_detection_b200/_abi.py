@@ -52,6 +52,10 @@ SIGNATURES = {
                                    _i32, _i64, _i32, _i32, _f64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp]),
     'lf_mask_gather': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp]),
+    'lf_filter_valid': (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _f64, _vp, _vp]),
+    'lf_car_scratch_elems': (C.c_int64, [_i64, _i32]),
+    'lf_car_counts': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp]),
+    'lf_car_compact': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     'lf_points_in_box': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _i32, _vp, _vp]),
     'lf_count_in_boxes': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _vp, _vp, _i32, _i32, _vp, _vp]),
     'lf_car_stats': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, '_lib', 'liblidarfuse.so')
-SOURCES = ['ctx.cu', 'project.cu', 'erode.cu', 'fuse.cu', 'boxes2d.cu', 'resize.cu', 'colour.cu', 'csvfmt.cu', 'packhost.cu', 'points.cu', 'synth.cu', 'publish.cu']
+SOURCES = ['ctx.cu', 'project.cu', 'erode.cu', 'fuse.cu', 'boxes2d.cu', 'resize.cu', 'colour.cu', 'csvfmt.cu', 'packhost.cu', 'points.cu', 'compact.cu', 'synth.cu', 'publish.cu']
 HEADERS = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith('.cuh')) + \
     [os.path.join(ROOT, 'include', 'lidarfuse.h')]
 

@@ -126,11 +126,17 @@ def gated_pixels(points, TrVeloToRect, camera, max_depth=50, device=None):
 
 def filter_valid(u, v, depth, camera, max_depth=50, device=None):
     """Boolean gate of cvs_erosion.py:359 (max_depth 30 in V4:275, V5:508,
-    seg_with_pointcloud.py:154-158) on already projected arrays."""
+    seg_with_pointcloud.py:154-158) on already projected arrays (one launch, ``lf_filter_valid``)."""
     ctx = get_ctx(device)
     was_np = _is_np(u)
-    uu, vv, dd = _dev(u, ctx), _dev(v, ctx), _dev(depth, ctx)
-    valid = ((uu >= 0) & (uu < camera.width) & (vv >= 0) & (vv < camera.height) & (dd > 0) & (dd < max_depth))
+    uu, vv, dd = _dev(u, ctx, torch.int64), _dev(v, ctx, torch.int64), _dev(depth, ctx, torch.float64)
+    n = uu.shape[0]
+    if vv.shape[0] != n or dd.shape[0] != n:
+        raise ValueError('u, v, depth must have equal length')
+    valid = torch.empty(n, dtype=torch.uint8, device=ctx.device)
+    check(ctx.lib.lf_filter_valid(ctx.h, ptr(uu), ptr(vv), ptr(dd), n, int(camera.width), int(camera.height),
+                                  float(max_depth), ptr(valid), ctx.stream), ctx.h)
+    valid = valid.view(torch.bool)
     return valid.cpu().numpy() if was_np else valid
 
 
@@ -344,15 +350,31 @@ def extract_car_points_by_mask(points_valid, u_valid, v_valid, masks, camera, de
         return []
     bits = mask_membership(u_valid, v_valid, masks, camera, device)
     pts = _dev(points_valid, ctx)
-    sets = []
+    if pts.dtype not in (torch.float32, torch.float64):
+        pts = pts.to(torch.float64)
+    if pts.ndim != 2 or pts.shape[1] < 3 or pts.shape[0] != bits.shape[0]:
+        raise ValueError('points_valid must be [n,>=3] with one row per (u, v)')
+    n = pts.shape[0]
+    # counts of all masks, then ONE order-preserving compaction of every car's points (CSR), two read-backs
+    scratch = torch.empty(max(int(ctx.lib.lf_car_scratch_elems(n, M)), 2), dtype=torch.int32, device=ctx.device)
+    counts = torch.zeros(M, dtype=torch.int32, device=ctx.device)
+    check(ctx.lib.lf_car_counts(ctx.h, ptr(bits), n, M, ptr(scratch), ptr(counts), ctx.stream), ctx.h)
+    h_counts = counts.cpu().numpy()
+    total = int(h_counts.sum())
+    out = torch.empty((max(total, 1), 3), dtype=pts.dtype, device=ctx.device)
+    if total:
+        check(ctx.lib.lf_car_compact(ctx.h, ptr(bits), n, M, ptr(pts), int(pts.dtype == torch.float64), pts.shape[1],
+                                     ptr(scratch), ptr(out), None, ctx.stream), ctx.h)
+    data = out.cpu().numpy() if was_np else out
+    sets, o = [], 0
     for c in range(M):
-        sel = ((bits >> c) & 1).to(torch.bool)
-        got = pts[sel]
-        if got.shape[0] == 0:
+        k = int(h_counts[c])
+        if k == 0:
             sets.append(np.array([]).reshape(0, 3) if was_np else
                         torch.zeros((0, 3), dtype=torch.float64, device=ctx.device))
         else:
-            sets.append(got.cpu().numpy() if was_np else got)
+            sets.append(data[o:o + k])
+        o += k
     return sets
 
 

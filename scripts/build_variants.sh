@@ -5,7 +5,7 @@ set -e
 cd "$(dirname "$0")/.."
 C=lidar_object_detection_b200/csrc; O=build/variants; mkdir -p $O
 FLAGS="-O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-O3 -I include -I $C -DLF_BUILDING=1"
-for f in ctx project erode boxes2d resize colour csvfmt packhost points synth publish; do
+for f in ctx project erode boxes2d resize colour csvfmt packhost points compact synth publish; do
   if [ ! -f $O/$f.o ] || [ $C/$f.cu -nt $O/$f.o ]; then nvcc $FLAGS -c $C/$f.cu -o $O/$f.o & fi
 done
 wait
@@ -14,6 +14,6 @@ while [ $# -ge 2 ]; do
   nvcc $FLAGS $defs -c $C/fuse.cu -o $O/fuse_$name.o &
   wait
   nvcc -shared -o $O/liblidarfuse_$name.so $O/fuse_$name.o $O/ctx.o $O/project.o $O/erode.o $O/boxes2d.o \
-    $O/resize.o $O/colour.o $O/csvfmt.o $O/packhost.o $O/points.o $O/synth.o $O/publish.o
+    $O/resize.o $O/colour.o $O/csvfmt.o $O/packhost.o $O/points.o $O/compact.o $O/synth.o $O/publish.o
   echo built $name "($defs)"
 done

@@ -846,6 +846,60 @@ def test_extension_metrics_match_the_oracle(LF, calib, golden):
                                              'match_ratio': float('inf')}
 
 
+def test_device_compaction_and_gate_kernels(LF, calib):
+    """lf_filter_valid against the numpy gate (cvs_erosion.py:359) including the INT64_MIN pixels numpy
+    gives NaN / inf points, and lf_car_counts + lf_car_compact against boolean indexing
+    (cvs_erosion.py:156-160): 64 overlapping random membership words over several block sizes, float32
+    rows of stride 4 and float64 rows of stride 3, point indices returned in order."""
+    import ctypes as C
+    import torch
+    from lidar_object_detection_b200 import _abi
+    cam, TVC, TVR = calib
+    rng = np.random.default_rng(3)
+    n = 50000
+    u = rng.integers(-50, cam.width + 50, n)
+    v = rng.integers(-50, cam.height + 50, n)
+    d = rng.uniform(-5, 60, n)
+    u[:5] = np.iinfo(np.int64).min
+    d[5:9] = [0.0, 50.0, np.nan, np.inf]
+    for md in (50, 30):
+        want = (u >= 0) & (u < cam.width) & (v >= 0) & (v < cam.height) & (d > 0) & (d < md)
+        got = LF.filter_valid(u, v, d, cam, md)
+        assert got.dtype == np.bool_ and np.array_equal(got, want)
+    assert LF.filter_valid(u[:0], v[:0], d[:0], cam).shape == (0,)
+    ctx = LF.get_ctx()
+    lib = ctx.lib
+    p = lambda t: C.c_void_p(t.data_ptr())
+    for n, m, f64 in ((1, 1, False), (31, 3, False), (2048, 64, True), (2049, 17, False), (70001, 64, False), (5000, 40, True)):
+        dens = rng.uniform(0, 0.3, m)
+        member = rng.random((m, n)) < dens[:, None]
+        member[m // 2] = False                                  # an empty car in the middle
+        bits = np.zeros(n, np.uint64)
+        for c in range(m):
+            bits |= member[c].astype(np.uint64) << np.uint64(c)
+        stride = 3 if f64 else 4
+        pts = rng.normal(size=(n, stride)).astype(np.float64 if f64 else np.float32)
+        tb = torch.from_numpy(bits.view(np.int64)).cuda()
+        tp = torch.from_numpy(pts).cuda()
+        scratch = torch.empty(int(lib.lf_car_scratch_elems(n, m)), dtype=torch.int32, device='cuda')
+        counts = torch.full((m,), -1, dtype=torch.int32, device='cuda')
+        assert lib.lf_car_counts(ctx.h, p(tb), n, m, p(scratch), p(counts), ctx.stream) == _abi.LF_OK
+        hc = counts.cpu().numpy()
+        assert np.array_equal(hc, member.sum(axis=1))
+        tot = int(hc.sum())
+        out = torch.full((max(tot, 1), 3), 7.0, dtype=tp.dtype, device='cuda')
+        idx = torch.full((max(tot, 1),), -1, dtype=torch.int32, device='cuda')
+        assert lib.lf_car_compact(ctx.h, p(tb), n, m, p(tp), int(f64), stride, p(scratch), p(out), p(idx),
+                                  ctx.stream) == _abi.LF_OK
+        ho, hi, o = out.cpu().numpy(), idx.cpu().numpy(), 0
+        for c in range(m):
+            sel = np.nonzero(member[c])[0]
+            assert np.array_equal(hi[o:o + len(sel)], sel), (n, m, c)
+            assert np.array_equal(ho[o:o + len(sel)], pts[sel, :3])
+            o += len(sel)
+        assert o == tot
+
+
 # ------------------------------------------------------------------ ragged / degenerate batches
 
 @pytest.mark.parametrize('persistent', [False, True])
