@@ -146,7 +146,7 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     if (((uintptr_t)pts & 15) != 0 || ((uintptr_t)mask_bbox & 15) != 0) return LF_E_ARG;
     if ((int64_t)ctx->cam.H * ctx->cam.wpr * LF_MAX_CARS >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
     if (ctx->cam.W > 65535 || ctx->cam.H > 65535) return LF_E_UNSUPPORTED;   // queued pixels are 16 + 16 bits
-    if (max_masks_per_frame > LF_MAX_CARS) return LF_E_UNSUPPORTED;           // one 64-bit membership word per point
+    if (max_masks_per_frame > LF_MAX_CARS && car_bits) return LF_E_UNSUPPORTED;   // one 64-bit membership word per point
     LF_CUDA(ctx, cudaSetDevice(ctx->device));
 
     FuseArgs A;
@@ -163,8 +163,8 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     if (!((double)dl < max_depth)) dl = nextafterf(dl, -INFINITY);
     A.dmax_hi = dh; A.dmax_lo = dl;
     A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
-    A.smem_cars = max_masks_per_frame > 0 ? max_masks_per_frame : 1;
-    A.claim = nullptr; A.F = 0; A.cpf = 0; A.claim_points = 0;
+    A.smem_cars = max_masks_per_frame > 0 ? (max_masks_per_frame < LF_MAX_CARS ? max_masks_per_frame : LF_MAX_CARS) : 1;
+    A.claim = nullptr; A.F = 0; A.cpf = 0; A.claim_points = 0; A.group = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // the per-warp caches of the largest frame must leave room for the half-size queues
     if (FuseGeom<LF_FUSE_WARPS, (LF_FUSE_PER / 2), true>::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 >
@@ -173,15 +173,22 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     // the claim space of one launch is 31 bits: very large batches go out in several launches
     // (the CSR arrays are simply entered at frame f0)
     const int64_t fmax = (int64_t)1 << 20;
-    for (int64_t f0 = 0; f0 < F; f0 += fmax) {
-        const int nf = (int)(F - f0 < fmax ? F - f0 : fmax);
-        FuseArgs Af = A;
-        Af.pt_off += f0; Af.mask_off += f0; Af.box_off += f0; Af.cnt_off += f0; Af.n_valid += f0;
-        if (car_bits)
-            LF_CUDA(ctx, launch_fuse_any<true>(ctx, Af, nf, max_points_per_frame, st));
-        else
-            LF_CUDA(ctx, launch_fuse_any<false>(ctx, Af, nf, max_points_per_frame, st));
-    }
+    // frames with more than LF_MAX_CARS masks: one pass over the points per group of 64 masks; the passes
+    // after the first add to the per-car counters only (n_valid and n_in_box are per frame / per box)
+    const int groups = max_masks_per_frame > LF_MAX_CARS ? (max_masks_per_frame + LF_MAX_CARS - 1) / LF_MAX_CARS : 1;
+    for (int g = 0; g < groups; ++g)
+        for (int64_t f0 = 0; f0 < F; f0 += fmax) {
+            const int nf = (int)(F - f0 < fmax ? F - f0 : fmax);
+            FuseArgs Af = A;
+            Af.group = g;
+            Af.pt_off += f0; Af.mask_off += f0; Af.box_off += f0; Af.cnt_off += f0;
+            Af.n_valid = g == 0 ? A.n_valid + f0 : nullptr;
+            if (g > 0) Af.n_in_box = nullptr;
+            if (car_bits)
+                LF_CUDA(ctx, launch_fuse_any<true>(ctx, Af, nf, max_points_per_frame, st));
+            else
+                LF_CUDA(ctx, launch_fuse_any<false>(ctx, Af, nf, max_points_per_frame, st));
+        }
     return LF_OK;
 }
 

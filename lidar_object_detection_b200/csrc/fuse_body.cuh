@@ -62,6 +62,7 @@ struct FuseArgs {
     int F;               // frames of this launch
     int cpf;             // claims per frame = ceil(max points per frame / claim_points)
     int claim_points;    // points per claim: a multiple of 32 * PER
+    int group;           // masks 64*group .. 64*group+63 of every frame (frames with more than LF_MAX_CARS masks take several passes)
 };
 
 // warp-wide float min / max in one instruction (redux.sync.f32 is sm_100a-only; SASS CREDUX)
@@ -214,7 +215,7 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
             const bool in = near && point_in_box(Fr.boxes + b, e.x, e.y, e.z, A.use_oriented);
             const unsigned bal = __ballot_sync(FULL, in);
             if (!bal) continue;
-            if (lane == 0) atomicAdd(Fr.nin + b, __popc(bal));
+            if (lane == 0 && Fr.nin) atomicAdd(Fr.nin + b, __popc(bal));
             add_per_car(blk[0], in, Fr.inside + b, B, lane);
             if (M > 32) add_per_car(blk[1], in, Fr.inside + (int64_t)32 * B + b, B, lane);
         }
@@ -308,14 +309,15 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
             const float4* src = A.pts + seg0;
             if (f != cur_f) {                               // frame state into the warp's cache
                 cur_f = f;
-                const int m0 = A.mask_off[f], b0 = A.box_off[f];
-                Fr.M = A.mask_off[f + 1] - m0;
+                const int b0 = A.box_off[f];
+                const int m0 = min(A.mask_off[f] + LF_MAX_CARS * A.group, A.mask_off[f + 1]);
+                Fr.M = min(A.mask_off[f + 1] - m0, LF_MAX_CARS);
                 Fr.B = A.box_off[f + 1] - b0;
                 Fr.mask_base = A.packed + (int64_t)m0 * plane32;
                 Fr.boxes = A.boxes + b0;
                 Fr.total = A.total + m0;
-                Fr.nin = A.n_in_box + b0;
-                Fr.inside = A.inside + A.cnt_off[f];
+                Fr.nin = A.n_in_box ? A.n_in_box + b0 : nullptr;      // passes after the first count per-car only
+                Fr.inside = A.inside + A.cnt_off[f] + (int64_t)LF_MAX_CARS * A.group * Fr.B;
                 __syncwarp();
                 for (int c = lane; c < Fr.M; c += 32) {
                     int4 bb = make_int4(0, 0, cam.W - 1, cam.H - 1);
@@ -421,7 +423,7 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                 if (last) break;
                 __syncwarp();
             }
-            if (lane == 0 && nval) atomicAdd(A.n_valid + f, nval);
+            if (lane == 0 && nval && A.n_valid) atomicAdd(A.n_valid + f, nval);
         }
         id = __shfl_sync(FULL, nxt, 0);
     }

@@ -348,6 +348,12 @@ def extract_car_points_by_mask(points_valid, u_valid, v_valid, masks, camera, de
     M = len(masks)
     if M == 0:
         return []
+    if M > _abi.MAX_CARS and not isinstance(masks, PackedMasks):
+        # one 64-bit membership word per point and call: more masks go in groups of 64
+        out = []
+        for g in range(0, M, _abi.MAX_CARS):
+            out += extract_car_points_by_mask(points_valid, u_valid, v_valid, masks[g:g + _abi.MAX_CARS], camera, device)
+        return out
     bits = mask_membership(u_valid, v_valid, masks, camera, device)
     pts = _dev(points_valid, ctx)
     if pts.dtype not in (torch.float32, torch.float64):
@@ -617,6 +623,8 @@ class FrameBatch:
 
     def __init__(self, points, n_points, masks, n_masks, boxes, n_boxes, camera, TrVeloToRect, device=None,
                  want_car_bits=False):
+        """Any number of frames; any number of masks per frame (beyond 64 the point pass runs once per group
+        of 64 masks, inside ``lf_fuse_batch``) unless ``want_car_bits`` (one 64-bit word per point)."""
         ctx = get_ctx(device)
         self.ctx, self.camera = ctx, camera
         self.TrVeloToRect = np.asarray(TrVeloToRect, dtype=np.float64)

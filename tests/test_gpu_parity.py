@@ -940,10 +940,31 @@ def test_degenerate_frames_in_one_batch(LF, calib, persistent):
                       np.zeros((0, 8, 3)), [], cam, TVR)
     e.run(one_call=persistent)
     assert e.results()['total'].size == 0
+    # more than 64 masks per frame: the point pass runs once per group of 64 masks; per-point membership
+    # words cannot hold them
     big = LF.FrameBatch(pts0[:1000], [1000], np.zeros((65, cam.height, cam.width), np.uint8), [65], c0[:1], [1], cam,
-                        TVR)
+                        TVR, want_car_bits=True)
     with pytest.raises(ValueError):
         big.run(one_call=persistent)
+    rng = np.random.default_rng(17)
+    many = np.concatenate([masks0] * 14)[:130]                    # 130 masks: groups of 64 + 64 + 2
+    many = many[rng.permutation(130)]
+    b130 = LF.FrameBatch(np.concatenate([pts0, pts0[:30000]]), [len(pts0), 30000], np.concatenate([many, many[:70]]),
+                         [130, 70], np.concatenate([c0, c0[:5]]), [len(c0), 5], cam, TVR)
+    b130.run(3, 1, 50, 10, True, one_call=persistent)
+    r130 = b130.results()
+    w130 = P.process_frame(pts0, raw0, many, cam, TVC, TVR)
+    assert np.array_equal(r130['total'][:130], w130['total'])
+    assert np.array_equal(r130['inside'][:b130.h_cnt_off[1]].reshape(130, len(c0)), w130['inside'])
+    assert np.array_equal(r130['n_in_box'][:len(c0)], w130['n_in_box']) and r130['n_valid'][0] == w130['valid'].sum()
+    assert _norm_stats(b130.frame_stats(r130, 0)) == _norm_stats(w130['stats'])
+    w70 = P.process_frame(pts0[:30000], raw0, many[:70], cam, TVC, TVR)
+    assert np.array_equal(r130['total'][130:], w70['total']) and r130['n_valid'][1] == w70['valid'].sum()
+    assert np.array_equal(r130['inside'][b130.h_cnt_off[1]:].reshape(70, 5), w70['inside'][:, :5])
+    u, v, d = LF.project_points(pts0, TVR, cam)
+    valid = LF.filter_valid(u, v, d, cam, 50)
+    sets = LF.extract_car_points_by_mask(pts0[valid, :3], u[valid], v[valid], LF.erode_masks(many, 3, 1), cam)
+    assert len(sets) == 130 and [len(x) for x in sets] == w130['total'].tolist()
 
 
 def test_argument_errors_surface_as_python_exceptions(LF, calib):
