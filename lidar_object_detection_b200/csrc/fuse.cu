@@ -20,6 +20,9 @@ namespace {
 #ifndef LF_FUSE_CTAS
 #define LF_FUSE_CTAS 4           /* launch bound (registers); shared memory decides how many really fit */
 #endif
+#ifndef LF_FUSE_SMEM_BOXES
+#define LF_FUSE_SMEM_BOXES 512   /* most boxes per frame whose cull bounds a warp caches in shared memory */
+#endif
 #ifndef LF_FUSE_CLAIM
 #define LF_FUSE_CLAIM 2048       /* points per claim for batches that fill the machine */
 #endif
@@ -71,12 +74,18 @@ cudaError_t launch_fuse(lf_ctx* ctx, FuseArgs A, int F, int64_t max_points_per_f
 
 template <bool BITS>
 cudaError_t launch_fuse_any(lf_ctx* ctx, const FuseArgs& A, int F, int64_t maxn, cudaStream_t st) {
-    // LF_FUSE_PER loads per iteration when LF_FUSE_CTAS such CTAs fit one SM; else half the candidate
-    // queue (frames with hundreds of boxes: 24 B of cull cache per box and warp)
+    // LF_FUSE_PER loads per iteration when LF_FUSE_CTAS such CTAs fit one SM; half of it when the per-warp
+    // caches of the frame state are large.  Small batches (a frame or two: latency, not throughput) take
+    // shorter iterations still, so that a claim -- one warp's serial work -- is 128 or 64 points and the
+    // frame spreads over every warp of the machine.
     using Gf = FuseGeom<LF_FUSE_WARPS, LF_FUSE_PER, BITS>;
-    if (Gf::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 <= (size_t)227 * 1024 / LF_FUSE_CTAS)
-        return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
-    return launch_fuse<LF_FUSE_WARPS, (LF_FUSE_PER / 2), BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+    int per = LF_FUSE_PER;
+    if (Gf::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 > (size_t)227 * 1024 / LF_FUSE_CTAS) per /= 2;
+    const int64_t warps = (int64_t)ctx->sm_count * LF_FUSE_CTAS * LF_FUSE_WARPS;
+    while (per > 2 && (int64_t)F * maxn / (32 * per) < 2 * warps) per /= 2;
+    if (per >= LF_FUSE_PER) return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+    if (per >= LF_FUSE_PER / 2) return launch_fuse<LF_FUSE_WARPS, (LF_FUSE_PER / 2), BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+    return launch_fuse<LF_FUSE_WARPS, (LF_FUSE_PER / 4), BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -162,12 +171,14 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     if ((double)dh < max_depth) dh = nextafterf(dh, INFINITY);
     if (!((double)dl < max_depth)) dl = nextafterf(dl, -INFINITY);
     A.dmax_hi = dh; A.dmax_lo = dl;
-    A.smem_boxes = max_boxes_per_frame > 0 ? max_boxes_per_frame : 1;
+    // up to 64 boxes per frame: cull bounds cached per warp in shared memory; more (real frames have up to 314):
+    // read from the box records through L1 -- no 7.5 KB reload per claim, and the CTAs keep their occupancy
+    A.smem_boxes = max_boxes_per_frame > LF_FUSE_SMEM_BOXES ? 0 : (max_boxes_per_frame > 0 ? max_boxes_per_frame : 1);
     A.smem_cars = max_masks_per_frame > 0 ? (max_masks_per_frame < LF_MAX_CARS ? max_masks_per_frame : LF_MAX_CARS) : 1;
     A.claim = nullptr; A.F = 0; A.cpf = 0; A.claim_points = 0; A.group = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // the per-warp caches of the largest frame must leave room for the half-size queues
-    if (FuseGeom<LF_FUSE_WARPS, (LF_FUSE_PER / 2), true>::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 >
+    if (FuseGeom<LF_FUSE_WARPS, (LF_FUSE_PER / 4), true>::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 >
         (size_t)227 * 1024)
         return LF_E_UNSUPPORTED;
     // the claim space of one launch is 31 bits: very large batches go out in several launches

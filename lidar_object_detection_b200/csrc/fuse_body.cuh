@@ -56,7 +56,8 @@ struct FuseArgs {
     float dmax_lo;       // largest float < max_depth    (stage 3: certainly inside the gate)
     int use_oriented;
     int force_exact;     // verification mode: every candidate takes the float64 chain
-    int smem_boxes;      // per-warp cache of box cull bounds (max boxes over frames)
+    int smem_boxes;      // per-warp cache of box cull bounds (max boxes over frames); 0: frames with many boxes read them
+                         // from the lf_box records through L1 instead (no per-claim reload, no shared memory)
     int smem_cars;       // per-warp cache of mask bounding boxes (max masks per frame, <= LF_MAX_CARS)
     unsigned int* claim; // global claim counter, zeroed before the launch
     int F;               // frames of this launch
@@ -123,6 +124,20 @@ struct FuseFrame {
     int32_t* inside;
     int32_t* nin;
 };
+
+// lo.x lo.y lo.z hi.x hi.y hi.z of box b: from the warp's shared-memory cache, or (frames with many boxes)
+// from the lf_box record itself -- bytes 168..191 of it, one 32-byte sector, L1-cached
+__device__ __forceinline__ void cull_bounds(const FuseFrame& Fr, int b, float (&c)[6]) {
+    if (Fr.SB > 0) {
+        const float* cu = Fr.cull + b;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) c[k] = cu[k * Fr.SB];
+    } else {
+        const float2* lh = (const float2*)(Fr.boxes[b].lo);
+        const float2 t0 = __ldg(lh), t1 = __ldg(lh + 1), t2 = __ldg(lh + 2);
+        c[0] = t0.x; c[1] = t0.y; c[2] = t1.x; c[3] = t1.y; c[4] = t2.x; c[5] = t2.y;
+    }
+}
 
 // counts of one 32-mask block: one reduction-atomic per car present in the group
 __device__ __forceinline__ void add_per_car(unsigned blk, bool pred, int32_t* dst, int stride, int lane) {
@@ -194,23 +209,22 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
     const float wx0 = warp_min_f32(have ? e.x : INF), wx1 = warp_max_f32(have ? e.x : -INF);
     const float wy0 = warp_min_f32(have ? e.y : INF), wy1 = warp_max_f32(have ? e.y : -INF);
     const float wz0 = warp_min_f32(have ? e.z : INF), wz1 = warp_max_f32(have ? e.z : -INF);
-    const int SB = Fr.SB;
     for (int g = 0; g < B; g += 32) {
         const int bl = g + lane;
         bool cand = false;
         if (bl < B) {
-            const float* cu = Fr.cull + bl;
-            cand = wx1 >= cu[0] && wx0 <= cu[3 * SB] && wy1 >= cu[SB] && wy0 <= cu[4 * SB] && wz1 >= cu[2 * SB] &&
-                   wz0 <= cu[5 * SB];
+            float c[6];
+            cull_bounds(Fr, bl, c);
+            cand = wx1 >= c[0] && wx0 <= c[3] && wy1 >= c[1] && wy0 <= c[4] && wz1 >= c[2] && wz0 <= c[5];
         }
         unsigned cmask = __ballot_sync(FULL, cand);
         // ---- K5: containment (cvs_erosion.py:114-145 / V1:118-139) on the candidates
         while (cmask) {
             const int b = g + __ffs((int)cmask) - 1;
             cmask &= cmask - 1;
-            const float* cu = Fr.cull + b;
-            const bool near = have && e.x >= cu[0] && e.x <= cu[3 * SB] && e.y >= cu[SB] && e.y <= cu[4 * SB] &&
-                              e.z >= cu[2 * SB] && e.z <= cu[5 * SB];
+            float c[6];
+            cull_bounds(Fr, b, c);
+            const bool near = have && e.x >= c[0] && e.x <= c[3] && e.y >= c[1] && e.y <= c[4] && e.z >= c[2] && e.z <= c[5];
             if (!__any_sync(FULL, near)) continue;
             const bool in = near && point_in_box(Fr.boxes + b, e.x, e.y, e.z, A.use_oriented);
             const unsigned bal = __ballot_sync(FULL, in);
@@ -327,7 +341,7 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                     }
                     s_mbb[c] = bb;
                 }
-                for (int b = lane; b < Fr.B; b += 32) {
+                for (int b = lane; A.smem_boxes > 0 && b < Fr.B; b += 32) {
                     const float2* lh = (const float2*)(Fr.boxes[b].lo);    // lo[3], hi[3]: 8-B aligned
                     const float2 t0 = __ldg(lh), t1 = __ldg(lh + 1), t2 = __ldg(lh + 2);
                     s_cull[b] = t0.x; s_cull[A.smem_boxes + b] = t0.y; s_cull[2 * A.smem_boxes + b] = t1.x;
