@@ -31,6 +31,9 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef LF_FUSE_GATHER
+#define LF_FUSE_GATHER 4           /* mask words requested together per round of the gather */
+#endif
 #ifndef LF_FUSE_PFDIST
 #define LF_FUSE_PFDIST 1           /* iterations the L2 prefetch runs ahead of the loads */
 #endif
@@ -181,21 +184,22 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
             }
             unsigned cmask = __ballot_sync(FULL, cand);
             unsigned acc = 0u;
-            // up to four candidate masks per round: their words are requested together, so a
-            // group pays one L2 round trip, not one per mask
+            // LF_FUSE_GATHER candidate masks per round: their words are requested together, so a
+            // group pays one L2 round trip for them, not one per mask (after the bounding-box cull a
+            // group of neighbouring points rarely has more than two candidates)
             while (cmask) {
-                int c[4];
-                uint32_t w[4];
+                int c[LF_FUSE_GATHER];
+                uint32_t w[LF_FUSE_GATHER];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < LF_FUSE_GATHER; ++j) {
                     c[j] = cmask ? __ffs((int)cmask) - 1 : -1;
                     cmask &= cmask - 1;
                 }
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
+                for (int j = 0; j < LF_FUSE_GATHER; ++j)
                     w[j] = (have && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off + (g + c[j]) * plane32)) : 0u;
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
+                for (int j = 0; j < LF_FUSE_GATHER; ++j)
                     if (c[j] >= 0) acc |= ((w[j] >> sh) & 1u) << c[j];
             }
             blk[h] = acc;
