@@ -650,6 +650,7 @@ def run_gpu(args):
                'FrameBatch.upload (pinned uint8 masks copied as they are) / run / download / table')
         tmp_words = np.empty(tuple(words.shape), np.uint32)
         pack_u8_gbs = 0.0
+        sync_all()
         for _ in range(2):
             tq0 = time.perf_counter()
             IO.pack_masks(h_u8.numpy(), threads=threads, out=tmp_words)
@@ -670,6 +671,7 @@ def run_gpu(args):
                 h_f32[a0:a0 + sl].copy_(batch.masks[a0:a0 + sl].to(torch.float32))
             torch.cuda.synchronize(dev)
             pack_f32_gbs = 0.0
+            sync_all()                                        # every rank packs at the same time: the host is shared
             for _ in range(2):                                # best of two: the first pass touches the pages
                 tq0 = time.perf_counter()
                 IO.pack_masks(h_f32.numpy(), threads=threads, out=pb._h_words.numpy())
