@@ -105,8 +105,10 @@ lf_project_boxes_kernel(const __grid_constant__ LfCam cam, const double* __restr
     out[b] = r;
 }
 
-// One thread per (detection, box) pair of a frame.
-__global__ void __launch_bounds__(256)
+// One thread per (detection, box) pair of a frame.  A CTA lives for two dependent memory latencies (offsets, then
+// records) and a few hundred float64 instructions, so what bounds the kernel is how many CTAs an SM holds:
+// 32 registers -> 8 CTAs of 256 threads.
+__global__ void __launch_bounds__(256, 8)
 lf_match_matrices_kernel(const double* __restrict__ dets, const int32_t* __restrict__ det_off,
                          const lf_box2d* __restrict__ rects, const int32_t* __restrict__ box_off,
                          const int64_t* __restrict__ out_off, double w_iou, double w_center, double w_size,

@@ -147,6 +147,138 @@ lf_resize_linear_smem_kernel(const uint8_t* __restrict__ src, int64_t m, int h, 
     }
 }
 
+// Separable form of the same arithmetic for enlarging (or equal) widths, the reference's case (a 192x704 or
+// 384x1408 network mask to the 376x1408 camera image).  The plain kernels above recompute the horizontal
+// interpolation for both source rows of EVERY output row (each source row serves ~4 output rows when the
+// image is enlarged 2x) and pay four byte-wide loads per pixel.  Here a CTA takes RL_ROWS output rows of one
+// image: pass 1 interpolates every source row the tile touches once -- a thread does four neighbouring
+// columns from one 8-byte window of the row (two aligned 32-bit loads), each pixel = one PRMT that puts its
+// two source bytes into the low half of a register + one DP2A with the packed coefficients (c0 | c1 << 16),
+// which IS S0*c0 + S1*c1 -- and leaves the 15-bit values (a >> 4) in shared memory; pass 2 combines two of
+// those rows per output pixel, (b*x) >> 16 as the high half of x << 16 times b (IMAD.HI with the running sum
+// as addend).  Same integers in the same order as above: bit-exact with cv2.
+// Needs w % 4 == 0, W % 4 == 0, 4-byte aligned images, scale_x <= 1 (the window of four columns then spans
+// at most 3 + 3 + 2 = 8 bytes) and a vertical scale that keeps the tile's source rows in shared memory.
+constexpr int RL_ROWS = 16;
+
+__global__ void __launch_bounds__(256)
+lf_resize_linear_sep_kernel(const uint8_t* __restrict__ src, int64_t m, int h, int w, uint8_t* __restrict__ dst, int H,
+                            int W, double scale_x, double scale_y, int ns_max) {
+    extern __shared__ __align__(16) uint8_t rl_smem[];
+    const int G = W >> 2;                                     // groups of four output columns
+    uint2* hrow = (uint2*)rl_smem;                            // [ns_max][G] four 16-bit values a >> 4
+    uint4* t_coef = (uint4*)(hrow + (size_t)ns_max * G);      // [G] c0 | c1 << 16 of the four columns
+    int2* t_base = (int2*)(t_coef + G);                       // [G] {word index of the window, word index of its second half}
+    uint32_t* t_sel = (uint32_t*)(t_base + G);                // [G] four PRMT selectors, 8 bits each
+    __shared__ int4 s_row[RL_ROWS];                           // per output row {s0 - r_lo, s1 - r_lo, b0, b1}
+    __shared__ int s_lo, s_ns;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        Tap t[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) t[j] = tap(4 * g + j, scale_x, w, true);
+        const int base = t[0].s0 & ~3;
+        uint32_t sel = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) sel |= (uint32_t)((t[j].s0 - base) | ((t[j].s1 - base) << 4)) << (8 * j);
+        t_sel[g] = sel;
+        t_base[g] = make_int2(base >> 2, (base + 4 < w ? base + 4 : base) >> 2);   // never past the row's end
+        t_coef[g] = make_uint4((uint32_t)t[0].c0 | ((uint32_t)t[0].c1 << 16), (uint32_t)t[1].c0 | ((uint32_t)t[1].c1 << 16),
+                               (uint32_t)t[2].c0 | ((uint32_t)t[2].c1 << 16), (uint32_t)t[3].c0 | ((uint32_t)t[3].c1 << 16));
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    const int tiles_per_img = (H + RL_ROWS - 1) / RL_ROWS;
+    const int64_t items = m * (int64_t)tiles_per_img;
+    for (int64_t it = blockIdx.x; it < items; it += gridDim.x) {
+        const int64_t img = it / tiles_per_img;
+        const int y0 = (int)(it - img * tiles_per_img) * RL_ROWS;
+        const int ny = min(RL_ROWS, H - y0);
+        __syncthreads();                                      // tables ready / previous tile consumed
+        if (threadIdx.x < ny) {
+            const Tap ty = tap(y0 + threadIdx.x, scale_y, h, false);
+            const int lo = tap(y0, scale_y, h, false).s0;     // rows are monotonic: the tile starts at its first row's s0
+            s_row[threadIdx.x] = make_int4(ty.s0 - lo, ty.s1 - lo, ty.c0, ty.c1);
+            if (threadIdx.x == 0) s_lo = lo;
+            if (threadIdx.x == ny - 1) s_ns = ty.s1 - lo + 1;
+        }
+        __syncthreads();
+        const int r_lo = s_lo, ns = s_ns;
+        // ---- pass 1: horizontal interpolation of the tile's source rows.  The (row, group) pairs are one flat range
+        // cut into rounds of 128 (four groups per lane: all eight window loads go out before the first one is
+        // used), dealt to the warps in turn -- a whole row per warp would leave five warps idle for the last rows
+        const int total = ns * G;
+        const uint8_t* tile_src = src + (img * h + r_lo) * (int64_t)w;
+        for (int c0 = warp * 128 + lane; c0 < total; c0 += nwarps * 128) {
+            uint32_t lo[4], hi[4];
+            int gk[4], rk[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int idx = c0 + 32 * k;
+                lo[k] = hi[k] = 0u;
+                rk[k] = idx / G;
+                gk[k] = idx - rk[k] * G;
+                if (idx < total) {
+                    const uint32_t* rp = (const uint32_t*)(tile_src + (int64_t)rk[k] * w);
+                    const int2 tb = t_base[gk[k]];
+                    lo[k] = __ldg(rp + tb.x);
+                    hi[k] = __ldg(rp + tb.y);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (c0 + 32 * k >= total) break;
+                const uint32_t sel = t_sel[gk[k]];
+                const uint4 cf = t_coef[gk[k]];
+                const uint32_t a0 = __dp2a_lo(cf.x, __byte_perm(lo[k], hi[k], sel), 0u);
+                const uint32_t a1 = __dp2a_lo(cf.y, __byte_perm(lo[k], hi[k], sel >> 8), 0u);
+                const uint32_t a2 = __dp2a_lo(cf.z, __byte_perm(lo[k], hi[k], sel >> 16), 0u);
+                const uint32_t a3 = __dp2a_lo(cf.w, __byte_perm(lo[k], hi[k], sel >> 24), 0u);
+                hrow[c0 + 32 * k] = make_uint2(__byte_perm(a0 >> 4, a1 << 12, 0x7610), __byte_perm(a2 >> 4, a3 << 12, 0x7610));
+            }
+        }
+        __syncthreads();
+        // ---- pass 2: vertical combination, four pixels per thread and store
+        for (int y = warp; y < ny; y += nwarps) {
+            const int4 rw = s_row[y];
+            const uint2* h0 = hrow + (size_t)rw.x * G;
+            const uint2* h1 = hrow + (size_t)rw.y * G;
+            const uint32_t b0 = (uint32_t)rw.z, b1 = (uint32_t)rw.w;
+            uint32_t* orow = (uint32_t*)(dst + (img * H + y0 + y) * (int64_t)W);
+#pragma unroll 2
+            for (int g = lane; g < G; g += 32) {
+                const uint2 x0 = h0[g], x1 = h1[g];
+                const uint32_t o0 = __umulhi(x1.x << 16, b1) + (__umulhi(x0.x << 16, b0) + 2u);
+                const uint32_t o1 = __umulhi(x1.x & 0xFFFF0000u, b1) + (__umulhi(x0.x & 0xFFFF0000u, b0) + 2u);
+                const uint32_t o2 = __umulhi(x1.y << 16, b1) + (__umulhi(x0.y << 16, b0) + 2u);
+                const uint32_t o3 = __umulhi(x1.y & 0xFFFF0000u, b1) + (__umulhi(x0.y & 0xFFFF0000u, b0) + 2u);
+                orow[g] = (o0 >> 2) | ((o1 >> 2) << 8) | ((o2 >> 2) << 16) | ((o3 >> 2) << 24);
+            }
+        }
+    }
+}
+
+// exact 2x reduction, eight output pixels per thread: 16 bytes of each of the two source rows, the byte pairs added
+// in 16-bit lanes ((x & 0x00FF00FF) + ((x >> 8) & 0x00FF00FF)), rows added, + 2 >> 2, repacked
+__global__ void __launch_bounds__(256)
+lf_resize_half_vec_kernel(const uint8_t* __restrict__ src, int64_t m, int H, int W, uint8_t* __restrict__ dst) {
+    const int w = 2 * W, qpr = W >> 3;                        // W % 8 == 0
+    const int64_t total = m * (int64_t)H * qpr;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int q = (int)(i % qpr);
+        const int64_t row = i / qpr;                          // img * H + dy
+        const uint4* p = (const uint4*)(src + row * 2 * (int64_t)w) + q;
+        const uint4 a = __ldg(p), b = __ldg(p + (w >> 4));
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t s = (av[k] & 0x00FF00FFu) + ((av[k] >> 8) & 0x00FF00FFu) + (bv[k] & 0x00FF00FFu) +
+                               ((bv[k] >> 8) & 0x00FF00FFu) + 0x00020002u;
+            o[k] = (s >> 2) & 0x00FF00FFu;                    // two results, in bytes 0 and 2
+        }
+        ((uint2*)(dst + row * (int64_t)W))[q] = make_uint2(__byte_perm(o[0], o[1], 0x6420), __byte_perm(o[2], o[3], 0x6420));
+    }
+}
+
 __global__ void __launch_bounds__(256)
 lf_resize_half_kernel(const uint8_t* __restrict__ src, int64_t m, int H, int W, uint8_t* __restrict__ dst) {
     const int w = 2 * W;
@@ -334,12 +466,34 @@ extern "C" int lf_resize_masks(lf_ctx* ctx, const uint8_t* src, int64_t m, int h
     }
     const int64_t cap = (int64_t)ctx->sm_count * 16;
     if (w == 2 * W && h == 2 * H) {
-        int64_t blocks = (m * H * W + 255) / 256;
-        if (blocks > cap) blocks = cap;
-        lf_resize_half_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, m, H, W, dst);
+        if ((W & 7) == 0 && (((uintptr_t)src | (uintptr_t)dst) & 15) == 0) {
+            int64_t blocks = (m * H * (W >> 3) + 255) / 256;
+            if (blocks > cap) blocks = cap;
+            lf_resize_half_vec_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, m, H, W, dst);
+        } else {
+            int64_t blocks = (m * H * W + 255) / 256;
+            if (blocks > cap) blocks = cap;
+            lf_resize_half_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, m, H, W, dst);
+        }
     } else {
         // OpenCV: inv_scale = (double)dsize / ssize; scale = 1. / inv_scale
         const double scale_x = 1.0 / ((double)W / (double)w), scale_y = 1.0 / ((double)H / (double)h);
+        // enlarging widths (the reference's case): the separable kernel, when its rows fit shared memory
+        const int ns_max = (int)((RL_ROWS - 1) * scale_y) + 4;
+        const size_t smem_sep = (size_t)ns_max * (W >> 2) * sizeof(uint2) + (size_t)(W >> 2) * (16 + 8 + 4);
+        if ((w & 3) == 0 && (W & 3) == 0 && w <= W && (((uintptr_t)src | (uintptr_t)dst) & 3) == 0 &&
+            smem_sep <= 100 * 1024) {
+            int64_t b3 = m * ((H + RL_ROWS - 1) / RL_ROWS);
+            LF_CUDA(ctx, cudaFuncSetAttribute(lf_resize_linear_sep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_sep));
+            int per_sm = 0;
+            LF_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lf_resize_linear_sep_kernel, 256, smem_sep));
+            const int64_t c3 = (int64_t)ctx->sm_count * (per_sm > 0 ? per_sm : 1);
+            if (b3 > c3) b3 = c3;
+            lf_resize_linear_sep_kernel<<<(unsigned)b3, 256, smem_sep, st>>>(src, m, h, w, dst, H, W, scale_x, scale_y, ns_max);
+            LF_CUDA(ctx, cudaGetLastError());
+            return LF_OK;
+        }
         if ((size_t)W * sizeof(int2) > 96 * 1024) return LF_E_UNSUPPORTED;      // column taps live in shared memory
         int64_t blocks = m * H;
         const int64_t pcap = (int64_t)ctx->sm_count * 8;

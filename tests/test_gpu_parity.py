@@ -1213,3 +1213,92 @@ def test_peer_store_exchange_equals_the_table_all_reduce(LF, calib):
     finally:
         if own:
             dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------ A6 / A8 stand-alone kernels, every layout
+
+@pytest.mark.parametrize('dtype,stride', [(np.float32, 4), (np.float32, 3), (np.float64, 3), (np.float64, 5)])
+@pytest.mark.parametrize('oriented', [True, False])
+def test_count_and_containment_kernels_every_layout(LF, dtype, stride, oriented):
+    """lf_points_in_box / lf_count_in_boxes straight through the C ABI: float32 records of 4 (one 128-bit load
+    per point), packed rows of 3, float64 rows, 70 boxes (more than one lane block, staged in shared memory),
+    interleaved point sets, NaN / inf / huge coordinates -- against the oracle's per-box test
+    (cvs_erosion.py:114-145, 175-195; V1:118-139)."""
+    import torch
+    from lidar_object_detection_b200 import _abi
+    from lidar_object_detection_b200._abi import check, ptr
+    ctx = LF.get_ctx(None)
+    rng = np.random.default_rng(11 + stride)
+    B, S, n = 70, 5, 20011
+    centres = rng.uniform(-20, 20, (B, 3))
+    corners = np.zeros((B, 8, 3))
+    signs = np.array([[-1, -1, -1], [1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1]], float)
+    for b in range(B):
+        yaw = rng.uniform(0, 2 * np.pi)
+        half = rng.uniform(0.5, 3.0, 3) * signs
+        c, s_ = np.cos(yaw), np.sin(yaw)
+        corners[b] = np.stack([c * half[:, 0] - s_ * half[:, 1], s_ * half[:, 0] + c * half[:, 1], half[:, 2]], 1) + centres[b]
+    # points: sweeps of neighbours around the boxes (so that whole warps see few boxes), some exactly on corners
+    pick = rng.integers(0, B, n)
+    xyz = (centres[pick] + rng.normal(0, 2.0, (n, 3))).astype(dtype)
+    order = np.argsort(pick, kind='stable')
+    xyz = xyz[order]
+    if not oriented:
+        xyz[:8] = corners[3].astype(dtype)                  # on the faces: exact for min / max comparisons (no arithmetic)
+    xyz[100] = (np.nan, 0, 0); xyz[101] = (np.inf, 1, 1); xyz[102] = (1e30, -1e30, 0); xyz[103] = (0, np.nan, np.nan)
+    rows = np.zeros((n, stride), dtype)
+    rows[:, :3] = xyz
+    rows[:, 3:] = 7.0
+    set_id = rng.integers(0, S, n).astype(np.int32)
+    d_rows = torch.from_numpy(rows).to(ctx.device)
+    d_sid = torch.from_numpy(set_id).to(ctx.device)
+    host = _abi.prepare_boxes(corners)
+    d_boxes = torch.from_numpy(host.view(np.uint8).reshape(-1, _abi.BOX_DTYPE.itemsize).copy()).to(ctx.device)
+    test = P.oriented_point_in_bbox if oriented else P.point_in_bbox
+    with np.errstate(all='ignore'):
+        want_in = np.stack([test(xyz.astype(np.float64), corners[b]) for b in range(B)], 1)      # [n, B]
+    if oriented:                                            # counts must not hinge on the last bit of a dot product
+        fin = np.isfinite(xyz).all(1) & (np.abs(xyz) < 1e6).all(1)
+        for b in range(B):
+            rel = xyz[fin].astype(np.float64) - corners[b, 0]
+            for j in (1, 3, 4):
+                e = corners[b, j] - corners[b, 0]
+                t = rel @ e / (e @ e)
+                assert np.min(np.minimum(np.abs(t), np.abs(t - 1))) > 1e-12
+    want = np.zeros((S, B), np.int32)
+    for s_ in range(S):
+        want[s_] = want_in[set_id == s_].sum(0)
+    inside = torch.zeros((S, B), dtype=torch.int32, device=ctx.device)
+    check(ctx.lib.lf_count_in_boxes(ctx.h, ptr(d_rows), int(dtype == np.float64), n, stride, ptr(d_sid), ptr(d_boxes), B,
+                                    int(oriented), ptr(inside), ctx.stream), ctx.h)
+    assert np.array_equal(inside.cpu().numpy(), want)
+    assert want.sum() > 1000
+    for b in (0, 3, 69):
+        flags = torch.empty(n, dtype=torch.uint8, device=ctx.device)
+        check(ctx.lib.lf_points_in_box(ctx.h, ptr(d_rows), int(dtype == np.float64), n, stride, ptr(d_boxes[b]),
+                                       int(oriented), ptr(flags), ctx.stream), ctx.h)
+        assert np.array_equal(flags.cpu().numpy().astype(bool), want_in[:, b])
+
+
+def test_mask_gather_more_than_eight_masks(LF):
+    """lf_mask_gather with 1, 8, 9 and 64 masks (the words are requested eight at a time) against numpy indexing."""
+    import torch
+    from lidar_object_detection_b200 import io as IO
+    from lidar_object_detection_b200._abi import check, ptr
+    ctx = LF.get_ctx(None)
+    rng = np.random.default_rng(3)
+    H, W, n = 37, 100, 5000
+    u = rng.integers(-3, W + 3, n).astype(np.int64)
+    v = rng.integers(-3, H + 3, n).astype(np.int64)
+    ok = (u >= 0) & (u < W) & (v >= 0) & (v < H)
+    d_u, d_v = torch.from_numpy(u).to(ctx.device), torch.from_numpy(v).to(ctx.device)
+    for m in (1, 8, 9, 64):
+        masks = (rng.random((m, H, W)) < 0.4).astype(np.uint8)
+        words = torch.from_numpy(IO.pack_masks(masks).view(np.int32)).to(ctx.device)
+        bits = torch.empty(n, dtype=torch.int64, device=ctx.device)
+        check(ctx.lib.lf_mask_gather(ctx.h, ptr(words), m, H, W, ptr(d_u), ptr(d_v), n, ptr(bits), ctx.stream), ctx.h)
+        got = bits.cpu().numpy().view(np.uint64)
+        want = np.zeros(n, np.uint64)
+        for c in range(m):
+            want[ok] |= masks[c, v[ok], u[ok]].astype(np.uint64) << np.uint64(c)
+        assert np.array_equal(got, want), m

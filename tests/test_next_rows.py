@@ -146,7 +146,7 @@ def test_device_box_projection_edge_cases(cam):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize('src', [(376, 1408), (384, 1408), (160, 608), (104, 384), (188, 704), (752, 2816),
-                                 (100, 333), (3, 5), (1, 1), (20, 5000)])
+                                 (100, 333), (3, 5), (1, 1), (20, 5000), (192, 704), (48, 176), (700, 32), (12, 1408)])
 def test_device_resize_is_bit_exact_with_cv2(src):
     """cv2.resize(u8, (W, H)) (default INTER_LINEAR) against lf_resize_masks: identity,
     the 2x2-average substitution at exactly 2x, fixed-point bilinear up and down;
@@ -349,6 +349,14 @@ def test_device_depth_overlay_matches_numpy(golden_arrays):
     assert C.depth_overlays(stack[:0], image).shape == (0,) + image.shape
     with pytest.raises(ValueError):
         C.depth_overlays(stack, image[:-1])
+    # a pixel count that is not a multiple of four takes the one-pixel-per-thread kernel
+    small = rng.random((3, 5, 7)) * (rng.random((3, 5, 7)) < 0.5)
+    small[2] = 0.0
+    simg = rng.integers(0, 256, (3, 5, 7, 3), dtype=np.uint8)
+    got = C.depth_overlays(small, simg)
+    for i in range(2):
+        assert np.array_equal(got[i], P.depth_overlay_reference(small[i].copy(), simg[i], P.jet_lut_restated())), i
+    assert np.array_equal(got[2], simg[2][:, :, ::-1])
 
 
 # ------------------------------------------------------------------ rank 4 (I/O formats)
