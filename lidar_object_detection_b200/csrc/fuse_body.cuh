@@ -15,14 +15,17 @@
 //                 reference's float64 result        -> "certain" (pixel known) or "uncertain"
 //            Survivors are compacted (ballot + popc prefix) into two per-warp shared-memory
 //            queues: certain points with their pixel, uncertain ones for the exact chain.
-//            Consecutive queue entries are consecutive survivors of the sweep, so a group of 32
+//            Consecutive queue entries are consecutive survivors of the sweep, so a group of 64
 //            covers a short arc of one ring: tight pixel and xyz bounds for the culls below.
 //   exact    whenever 32 uncertain points are queued the warp runs the float64 dgemm-order
 //            chain and the two divisions on all 32 lanes (common.cuh) and moves the points
 //            that pass the gate of cvs_erosion.py:359 to the certain queue.
-//   phase B  full 32-lane groups of certain points: packed-mask gather (L2) behind a mask
+//   phase B  groups of 64 certain points, two per lane: packed-mask gather (L2) behind a mask
 //            bounding-box cull, box cull, float64 containment, ballot/popc counts added to the
-//            global counters with one reduction-atomic per (car, box) and group.
+//            global counters with one reduction-atomic per (car, box) and group.  (Two points per
+//            lane: bounds, culls, candidate loops and atomics are paid once per 64 points and the
+//            two points' loads overlap; against 32-point groups: cfg3 0.650 -> 0.635 ms, cfg5
+//            0.863 -> 0.830, the 20 real frames with up to 314 boxes 0.306 -> 0.262.)
 // Nothing fp32 ever decides a result: a point is "certain" only if the fp32 residual proves
 // the rounded pixel and the gate (error bounds: lf_set_camera); everything else takes the exact path.
 // Measured and dropped: stage 3 as a separate pass over a candidate queue, and a
@@ -142,36 +145,37 @@ __device__ __forceinline__ void cull_bounds(const FuseFrame& Fr, int b, float (&
     }
 }
 
-// counts of one 32-mask block: one reduction-atomic per car present in the group
-__device__ __forceinline__ void add_per_car(unsigned blk, bool pred, int32_t* dst, int stride, int lane) {
-    unsigned un = __reduce_or_sync(0xFFFFFFFFu, pred ? blk : 0u);
+// counts of one 32-mask block for two points per lane: one reduction-atomic per car present in the 64 points
+__device__ __forceinline__ void add_per_car2(unsigned blk0, unsigned blk1, bool p0, bool p1, int32_t* dst, int stride,
+                                             int lane) {
+    unsigned un = __reduce_or_sync(0xFFFFFFFFu, (p0 ? blk0 : 0u) | (p1 ? blk1 : 0u));
     while (un) {
         const int c = __ffs((int)un) - 1;
         un &= un - 1;
-        const unsigned bal = __ballot_sync(0xFFFFFFFFu, pred && ((blk >> c) & 1u));
-        if (lane == 0) atomicAdd(dst + (int64_t)c * stride, __popc(bal));
+        const unsigned b0 = __ballot_sync(0xFFFFFFFFu, p0 && ((blk0 >> c) & 1u));
+        const unsigned b1 = __ballot_sync(0xFFFFFFFFu, p1 && ((blk1 >> c) & 1u));
+        if (lane == 0) atomicAdd(dst + (int64_t)c * stride, __popc(b0) + __popc(b1));
     }
 }
 
-// ---- phase B: 32 work-queue points, one per lane (`have` false only in a claim's last, partial group).
-// e = {x, y, z, bits(u | v << 16)}.  Returns the lane's membership bits.
-__device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const FuseArgs& A, const FuseFrame& Fr,
-                                                      float4 e, bool have, int plane32) {
+// ---- phase B on 64 work-queue points, two per lane (lane l: entries l and l + 32): the pixel / xyz bounds, both
+// culls, the candidate loops and the counter atomics are paid once per 64 points instead of once per 32.
+__device__ __forceinline__ void fuse_group2(const LfCam& cam, const FuseArgs& A, const FuseFrame& Fr, float4 e0, float4 e1,
+                                            bool have0, bool have1, int plane32, unsigned long long& bits0,
+                                            unsigned long long& bits1) {
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
-    const unsigned uv = __float_as_uint(e.w);
-    const int ui = (int)(uv & 0xFFFFu), vi = (int)(uv >> 16);
+    const unsigned uv0 = __float_as_uint(e0.w), uv1 = __float_as_uint(e1.w);
+    const int ui0 = (int)(uv0 & 0xFFFFu), vi0 = (int)(uv0 >> 16), ui1 = (int)(uv1 & 0xFFFFu), vi1 = (int)(uv1 >> 16);
     const int M = Fr.M, B = Fr.B;
-    // ---- K4: point-in-mask gather (cvs_erosion.py:152-160).  Lanes first test the masks' bounding
-    // boxes against the pixel bounds of the group (one mask per lane); only surviving masks are read.
-    unsigned blk[2] = {0u, 0u};                              // membership bits, masks 0..31 and 32..63
+    unsigned blk0[2] = {0u, 0u}, blk1[2] = {0u, 0u};         // membership bits of the two points, masks 0..31 and 32..63
     if (M > 0) {
-        const int off = vi * cam.wpr + (ui >> 5);            // word offset inside one packed mask
-        const int sh = ui & 31;
-        const int u0 = __reduce_min_sync(FULL, have ? ui : 0x7fffffff);
-        const int u1 = __reduce_max_sync(FULL, have ? ui : -1);
-        const int v0 = __reduce_min_sync(FULL, have ? vi : 0x7fffffff);
-        const int v1 = __reduce_max_sync(FULL, have ? vi : -1);
+        const int off0 = vi0 * cam.wpr + (ui0 >> 5), off1 = vi1 * cam.wpr + (ui1 >> 5);
+        const int sh0 = ui0 & 31, sh1 = ui1 & 31;
+        const int u0 = __reduce_min_sync(FULL, min(have0 ? ui0 : 0x7fffffff, have1 ? ui1 : 0x7fffffff));
+        const int u1 = __reduce_max_sync(FULL, max(have0 ? ui0 : -1, have1 ? ui1 : -1));
+        const int v0 = __reduce_min_sync(FULL, min(have0 ? vi0 : 0x7fffffff, have1 ? vi1 : 0x7fffffff));
+        const int v1 = __reduce_max_sync(FULL, max(have0 ? vi0 : -1, have1 ? vi1 : -1));
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int g = 32 * h;
@@ -183,36 +187,42 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
                 cand = u1 >= bb.x && u0 <= bb.z && v1 >= bb.y && v0 <= bb.w;
             }
             unsigned cmask = __ballot_sync(FULL, cand);
-            unsigned acc = 0u;
-            // LF_FUSE_GATHER candidate masks per round: their words are requested together, so a
-            // group pays one L2 round trip for them, not one per mask (after the bounding-box cull a
-            // group of neighbouring points rarely has more than two candidates)
+            unsigned acc0 = 0u, acc1 = 0u;
             while (cmask) {
                 int c[LF_FUSE_GATHER];
-                uint32_t w[LF_FUSE_GATHER];
+                uint32_t w0[LF_FUSE_GATHER], w1[LF_FUSE_GATHER];
 #pragma unroll
                 for (int j = 0; j < LF_FUSE_GATHER; ++j) {
                     c[j] = cmask ? __ffs((int)cmask) - 1 : -1;
                     cmask &= cmask - 1;
                 }
 #pragma unroll
-                for (int j = 0; j < LF_FUSE_GATHER; ++j)
-                    w[j] = (have && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off + (g + c[j]) * plane32)) : 0u;
+                for (int j = 0; j < LF_FUSE_GATHER; ++j) {
+                    w0[j] = (have0 && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off0 + (g + c[j]) * plane32)) : 0u;
+                    w1[j] = (have1 && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off1 + (g + c[j]) * plane32)) : 0u;
+                }
 #pragma unroll
                 for (int j = 0; j < LF_FUSE_GATHER; ++j)
-                    if (c[j] >= 0) acc |= ((w[j] >> sh) & 1u) << c[j];
+                    if (c[j] >= 0) {
+                        acc0 |= ((w0[j] >> sh0) & 1u) << c[j];
+                        acc1 |= ((w1[j] >> sh1) & 1u) << c[j];
+                    }
             }
-            blk[h] = acc;
-            add_per_car(acc, true, Fr.total + g, 1, lane);
+            blk0[h] = acc0;
+            blk1[h] = acc1;
+            add_per_car2(acc0, acc1, true, true, Fr.total + g, 1, lane);
         }
     }
-    const unsigned long long bits = ((unsigned long long)blk[1] << 32) | blk[0];
-    if (B == 0) return bits;
-    // ---- bounding box of the group's points, then lanes test the boxes' cull bounds in parallel
+    bits0 = ((unsigned long long)blk0[1] << 32) | blk0[0];
+    bits1 = ((unsigned long long)blk1[1] << 32) | blk1[0];
+    if (B == 0) return;
     const float INF = __int_as_float(0x7f800000);
-    const float wx0 = warp_min_f32(have ? e.x : INF), wx1 = warp_max_f32(have ? e.x : -INF);
-    const float wy0 = warp_min_f32(have ? e.y : INF), wy1 = warp_max_f32(have ? e.y : -INF);
-    const float wz0 = warp_min_f32(have ? e.z : INF), wz1 = warp_max_f32(have ? e.z : -INF);
+    const float wx0 = warp_min_f32(fminf(have0 ? e0.x : INF, have1 ? e1.x : INF));
+    const float wx1 = warp_max_f32(fmaxf(have0 ? e0.x : -INF, have1 ? e1.x : -INF));
+    const float wy0 = warp_min_f32(fminf(have0 ? e0.y : INF, have1 ? e1.y : INF));
+    const float wy1 = warp_max_f32(fmaxf(have0 ? e0.y : -INF, have1 ? e1.y : -INF));
+    const float wz0 = warp_min_f32(fminf(have0 ? e0.z : INF, have1 ? e1.z : INF));
+    const float wz1 = warp_max_f32(fmaxf(have0 ? e0.z : -INF, have1 ? e1.z : -INF));
     for (int g = 0; g < B; g += 32) {
         const int bl = g + lane;
         bool cand = false;
@@ -222,23 +232,23 @@ __device__ __forceinline__ unsigned long long fuse_group(const LfCam& cam, const
             cand = wx1 >= c[0] && wx0 <= c[3] && wy1 >= c[1] && wy0 <= c[4] && wz1 >= c[2] && wz0 <= c[5];
         }
         unsigned cmask = __ballot_sync(FULL, cand);
-        // ---- K5: containment (cvs_erosion.py:114-145 / V1:118-139) on the candidates
         while (cmask) {
             const int b = g + __ffs((int)cmask) - 1;
             cmask &= cmask - 1;
             float c[6];
             cull_bounds(Fr, b, c);
-            const bool near = have && e.x >= c[0] && e.x <= c[3] && e.y >= c[1] && e.y <= c[4] && e.z >= c[2] && e.z <= c[5];
-            if (!__any_sync(FULL, near)) continue;
-            const bool in = near && point_in_box(Fr.boxes + b, e.x, e.y, e.z, A.use_oriented);
-            const unsigned bal = __ballot_sync(FULL, in);
-            if (!bal) continue;
-            if (lane == 0 && Fr.nin) atomicAdd(Fr.nin + b, __popc(bal));
-            add_per_car(blk[0], in, Fr.inside + b, B, lane);
-            if (M > 32) add_per_car(blk[1], in, Fr.inside + (int64_t)32 * B + b, B, lane);
+            const bool near0 = have0 && e0.x >= c[0] && e0.x <= c[3] && e0.y >= c[1] && e0.y <= c[4] && e0.z >= c[2] && e0.z <= c[5];
+            const bool near1 = have1 && e1.x >= c[0] && e1.x <= c[3] && e1.y >= c[1] && e1.y <= c[4] && e1.z >= c[2] && e1.z <= c[5];
+            if (!__any_sync(FULL, near0 | near1)) continue;
+            const bool in0 = near0 && point_in_box(Fr.boxes + b, e0.x, e0.y, e0.z, A.use_oriented);
+            const bool in1 = near1 && point_in_box(Fr.boxes + b, e1.x, e1.y, e1.z, A.use_oriented);
+            const unsigned bal0 = __ballot_sync(FULL, in0), bal1 = __ballot_sync(FULL, in1);
+            if (!(bal0 | bal1)) continue;
+            if (lane == 0 && Fr.nin) atomicAdd(Fr.nin + b, __popc(bal0) + __popc(bal1));
+            add_per_car2(blk0[0], blk1[0], in0, in1, Fr.inside + b, B, lane);
+            if (M > 32) add_per_car2(blk0[1], blk1[1], in0, in1, Fr.inside + (int64_t)32 * B + b, B, lane);
         }
     }
-    return bits;
 }
 
 // ---- exact path: up to 32 queued uncertain points (one per lane) through the float64 dgemm-order
@@ -276,7 +286,8 @@ template <int WARPS, int PER, bool BITS>
 struct FuseGeom {
     static constexpr int NT = 32 * WARPS;
     static constexpr int SPAN = PER * 32;                  // points per iteration of one warp
-    static constexpr int QCAP = PER * 32 + 64;             // certain queue: < 32 left over + PER*32 new + < 32 resolved
+    static constexpr int GRP = 64;                         // queue entries phase B takes at a time (two per lane)
+    static constexpr int QCAP = PER * 32 + 32 + GRP;       // certain queue: < GRP left over + PER*32 new + < 32 resolved
     static constexpr int UCAP = 64;                        // uncertain queue: < 32 left over + 32 new
     static constexpr size_t queue_bytes = (size_t)(QCAP + UCAP) * 16 + (BITS ? (size_t)QCAP * 4 : 0);
     // + per-warp frame cache: mask bounding boxes (16 B each) and box cull bounds (24 B each)
@@ -356,13 +367,15 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
             }
             int qn = 0, un = 0;                             // queue fill, warp-uniform
             int nval = 0;                                   // certain points consumed in this claim
-            // phase B on the last 32 (or fewer, at the very end) entries of the certain queue
+            // phase B on the last GRP (or fewer, at the very end) entries of the certain queue
             auto consume = [&](int cnt) {
-                const bool have = lane < cnt;
-                const int at = qn - cnt + (have ? lane : 0);
-                const float4 e = q[at];
-                const unsigned long long bits = fuse_group(cam, A, Fr, e, have, plane32);
-                if (BITS && have) A.car_bits[seg0 + qi[at]] = bits;
+                const bool have0 = lane < cnt, have1 = lane + 32 < cnt;
+                const int at0 = qn - cnt + (have0 ? lane : 0), at1 = qn - cnt + (have1 ? lane + 32 : 0);
+                const float4 e0 = q[at0], e1 = q[at1];
+                unsigned long long bits0, bits1;
+                fuse_group2(cam, A, Fr, e0, e1, have0, have1, plane32, bits0, bits1);
+                if (BITS && have0) A.car_bits[seg0 + qi[at0]] = bits0;
+                if (BITS && have1) A.car_bits[seg0 + qi[at1]] = bits1;
                 nval += cnt;
                 qn -= cnt;
             };
@@ -437,7 +450,7 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                     un = 0;
                 }
                 __syncwarp();
-                while (qn >= 32 || (last && qn > 0)) consume(min(qn, 32));
+                while (qn >= G::GRP || (last && qn > 0)) consume(min(qn, G::GRP));
                 if (last) break;
                 __syncwarp();
             }
