@@ -1,8 +1,12 @@
-# point pass, 64-point phase B: bench lines (cfg3 and cfg5) and latency per variant
 mkdir -p gpurun_out
-bash scripts/run_variants.sh base g2 g2s
-BENCH_EXTRA="--workload cfg5 --steps 10" bash scripts/run_variants.sh base g2 g2s
-for v in base g2 g2s; do echo "== $v"; LIDARFUSE_LIB=$PWD/build/variants/liblidarfuse_$v.so timeout 300 python scripts/latency_cfg12.py 2>/dev/null | python -c "
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -x > gpurun_out/pytest_fuse.log 2>&1; echo "pytest rc=$?"; tail -2 gpurun_out/pytest_fuse.log
+timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-e2e --no-parity --no-packed --no-cfg4 --no-cfg5 2>/dev/null | python -c "
+import sys, json
+d = json.loads(sys.stdin.read().strip().splitlines()[-1]); print('cfg3 step %.3f' % d['ms_per_step'], d['kernel_ms'])"
+timeout 300 python bench.py --workload cfg5 --steps 10 --warmup 5 --no-cpu-baseline --no-e2e --no-parity --no-packed 2>/dev/null | python -c "
+import sys, json
+d = json.loads(sys.stdin.read().strip().splitlines()[-1]); print('cfg5 step %.3f' % d['ms_per_step'], d['kernel_ms'])"
+timeout 300 python scripts/latency_cfg12.py 2>/dev/null | python -c "
 import sys, json
 for l in sys.stdin:
-    d = json.loads(l); print(d['config'], 'direct %.4f ms' % d['direct']['device_ms_per_call'], 'graph %.4f ms' % d['graph']['device_ms_per_call'])"; done
+    d = json.loads(l); print(' ', d['config'], 'direct %.4f ms' % d['direct']['device_ms_per_call'], 'graph %.4f ms' % d['graph']['device_ms_per_call'])"
