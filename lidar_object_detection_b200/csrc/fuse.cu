@@ -15,7 +15,10 @@ namespace {
 #define LF_FUSE_WARPS 8
 #endif
 #ifndef LF_FUSE_PER
-#define LF_FUSE_PER 8            /* loads in flight per thread and iteration; the small-queue geometry uses half */
+#define LF_FUSE_PER 5            /* loads in flight per thread and iteration (2..6 are instantiated) */
+#endif
+#ifndef LF_FUSE_PER_DENSE
+#define LF_FUSE_PER_DENSE 3      /* the same for frames of millions of points */
 #endif
 #ifndef LF_FUSE_CTAS
 #define LF_FUSE_CTAS 4           /* launch bound (registers); shared memory decides how many really fit */
@@ -73,19 +76,37 @@ cudaError_t launch_fuse(lf_ctx* ctx, FuseArgs A, int F, int64_t max_points_per_f
 }
 
 template <bool BITS>
+cudaError_t launch_fuse_per(int per, lf_ctx* ctx, const FuseArgs& A, int F, int64_t maxn, cudaStream_t st) {
+    switch (per) {
+        case 2: return launch_fuse<LF_FUSE_WARPS, 2, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+        case 3: return launch_fuse<LF_FUSE_WARPS, 3, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+        case 4: return launch_fuse<LF_FUSE_WARPS, 4, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+        case 5: return launch_fuse<LF_FUSE_WARPS, 5, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+        default: return launch_fuse<LF_FUSE_WARPS, 6, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+    }
+}
+
+// per-warp shared memory of the geometry with `per` loads per iteration (FuseGeom::warp_bytes, PER at run time)
+template <bool BITS>
+size_t fuse_warp_bytes(int per, int cars, int boxes) {
+    const size_t qcap = (size_t)per * 32 + 32 + 64;
+    return ((qcap + 64) * 16 + (BITS ? qcap * 4 : 0) + 16 * (size_t)cars + 24 * (size_t)boxes + 8 + 15) & ~(size_t)15;
+}
+
+template <bool BITS>
 cudaError_t launch_fuse_any(lf_ctx* ctx, const FuseArgs& A, int F, int64_t maxn, cudaStream_t st) {
-    // LF_FUSE_PER loads per iteration when LF_FUSE_CTAS such CTAs fit one SM; half of it when the per-warp
-    // caches of the frame state are large.  Small batches (a frame or two: latency, not throughput) take
-    // shorter iterations still, so that a claim -- one warp's serial work -- is 128 or 64 points and the
-    // frame spreads over every warp of the machine.
-    using Gf = FuseGeom<LF_FUSE_WARPS, LF_FUSE_PER, BITS>;
-    int per = LF_FUSE_PER;
-    if (Gf::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 > (size_t)227 * 1024 / LF_FUSE_CTAS) per /= 2;
+    // loads in flight per thread and iteration (an iteration of a warp covers 32 * per consecutive points):
+    // LF_FUSE_PER for ordinary sweeps, as many as leave LF_FUSE_CTAS CTAs per SM when the per-warp caches of the
+    // frame state are large.  Small batches (a frame or two: latency, not throughput) take shorter iterations
+    // still, so that a claim -- one warp's serial work -- is 128 or 64 points and the frame spreads over every
+    // warp of the machine.
+    int per = maxn >= (1 << 20) ? LF_FUSE_PER_DENSE : LF_FUSE_PER;
+    if (per > 6) per = 6;
+    while (per > 2 && fuse_warp_bytes<BITS>(per, A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 > (size_t)227 * 1024 / LF_FUSE_CTAS)
+        --per;
     const int64_t warps = (int64_t)ctx->sm_count * LF_FUSE_CTAS * LF_FUSE_WARPS;
-    while (per > 2 && (int64_t)F * maxn / (32 * per) < 2 * warps) per /= 2;
-    if (per >= LF_FUSE_PER) return launch_fuse<LF_FUSE_WARPS, LF_FUSE_PER, BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
-    if (per >= LF_FUSE_PER / 2) return launch_fuse<LF_FUSE_WARPS, (LF_FUSE_PER / 2), BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
-    return launch_fuse<LF_FUSE_WARPS, (LF_FUSE_PER / 4), BITS, LF_FUSE_CTAS>(ctx, A, F, maxn, st);
+    while (per > 2 && (int64_t)F * maxn / (32 * per) < 2 * warps) per = per / 2 > 2 ? per / 2 : 2;
+    return launch_fuse_per<BITS>(per, ctx, A, F, maxn, st);
 }
 
 // K6: one warp per frame; lanes stride over the frame's cars, each walks the
@@ -178,8 +199,7 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     A.claim = nullptr; A.F = 0; A.cpf = 0; A.claim_points = 0; A.group = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // the per-warp caches of the largest frame must leave room for the half-size queues
-    if (FuseGeom<LF_FUSE_WARPS, (LF_FUSE_PER / 4), true>::warp_bytes(A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 >
-        (size_t)227 * 1024)
+    if (fuse_warp_bytes<true>(2, A.smem_cars, A.smem_boxes) * LF_FUSE_WARPS + 1024 > (size_t)227 * 1024)
         return LF_E_UNSUPPORTED;
     // the claim space of one launch is 31 bits: very large batches go out in several launches
     // (the CSR arrays are simply entered at frame f0)

@@ -36,7 +36,7 @@
 #include "common.cuh"
 
 #ifndef LF_FUSE_GATHER
-#define LF_FUSE_GATHER 4           /* mask words requested together per round of the gather */
+#define LF_FUSE_GATHER 2           /* mask words requested together per round of the gather */
 #endif
 #ifndef LF_FUSE_PAIR1
 #define LF_FUSE_PAIR1 0            /* 1: stage 1 of two groups interleaved */
