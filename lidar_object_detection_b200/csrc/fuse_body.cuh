@@ -38,9 +38,6 @@
 #ifndef LF_FUSE_GATHER
 #define LF_FUSE_GATHER 2           /* mask words requested together per round of the gather */
 #endif
-#ifndef LF_FUSE_PAIR1
-#define LF_FUSE_PAIR1 0            /* 1: stage 1 of two groups interleaved */
-#endif
 #ifndef LF_FUSE_PFDIST
 #define LF_FUSE_PFDIST 1           /* iterations the L2 prefetch runs ahead of the loads */
 #endif
@@ -282,6 +279,24 @@ __device__ __noinline__ int fuse_resolve(const LfCam& cam, const FuseArgs& A, co
 }
 
 
+// The points of iteration `it` of a claim into registers (dead lanes of the last iteration are masked by `k < npts`
+// in stage 1), and PER * 4 lines (128 B each) of a later iteration, one per lane, towards L2.
+template <int PER>
+__device__ __forceinline__ void fuse_load(float4 (&P)[PER], const float4* src, int it, int npts, int lane) {
+    constexpr int SPAN = PER * 32;
+    const int kbase = it * SPAN + lane;
+    const int kn = (it + LF_FUSE_PFDIST) * SPAN + lane * 8;
+    if (lane < PER * 4 && kn < npts) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + kn));
+    if (it * SPAN + SPAN <= npts) {
+#pragma unroll
+        for (int j = 0; j < PER; ++j) P[j] = ld_stream_f4(src + kbase + 32 * j);
+    } else {
+#pragma unroll
+        for (int j = 0; j < PER; ++j)
+            P[j] = kbase + 32 * j < npts ? ld_stream_f4(src + kbase + 32 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
 // Geometry of one warp's working set.
 //   WARPS  warps per CTA (independent workers; the CTA only shares the shared-memory allocation)
 //   PER    128-bit loads in flight per thread and iteration (an iteration covers PER*32 consecutive points)
@@ -393,21 +408,8 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                 const bool last = it == niter;              // pseudo-iteration: flush both queues
                 if (!last) {
                     const int kbase = it * SPAN + lane;     // group j: kbase + 32 j
-                    {   // PER * 4 lines (128 B each) of the iteration after next, one per lane, towards L2
-                        const int kn = (it + LF_FUSE_PFDIST) * SPAN + lane * 8;
-                        if (lane < PER * 4 && kn < npts) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + kn));
-                    }
                     float4 P[PER];
-                    if (it * SPAN + SPAN <= npts) {
-#pragma unroll
-                        for (int j = 0; j < PER; ++j) P[j] = ld_stream_f4(src + kbase + 32 * j);
-                    } else {                                // dead lanes are masked by `k < npts` in stage 1
-#pragma unroll
-                        for (int j = 0; j < PER; ++j)
-                            P[j] = kbase + 32 * j < npts ? ld_stream_f4(src + kbase + 32 * j)
-                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
-#pragma unroll
+                    fuse_load<PER>(P, src, it, npts, lane);
                     // ---- stage 1: depth row.  tol bounds every fp32 evaluation error of this point
                     // (+inf beyond 2^20 m and for NaN / inf input: such points are never decided here).
                     auto stage1 = [&](const float4& p, int k, float& d, float& tol) -> bool {
@@ -451,20 +453,6 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                             }
                         }
                     };
-#if LF_FUSE_PAIR1
-                    // stage 1 of two groups at a time: two independent dependency chains per thread
-#pragma unroll
-                    for (int j = 0; j < PER; j += 2) {
-                        const int k0 = kbase + 32 * j, k1 = k0 + 32;
-                        float d0, t0, d1, t1;
-                        const bool o0 = stage1(P[j], k0, d0, t0), o1 = stage1(P[j + 1], k1, d1, t1);
-                        const bool a0 = __any_sync(FULL, o0), a1 = __any_sync(FULL, o1);
-                        if (a0) stages23(P[j], k0, d0, t0, o0);
-                        else if (BITS && k0 < npts) A.car_bits[seg0 + k0] = 0ULL;
-                        if (a1) stages23(P[j + 1], k1, d1, t1, o1);
-                        else if (BITS && k1 < npts) A.car_bits[seg0 + k1] = 0ULL;
-                    }
-#else
 #pragma unroll
                     for (int j = 0; j < PER; ++j) {
                         const int k = kbase + 32 * j;
@@ -473,7 +461,6 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                         if (__any_sync(FULL, okd)) stages23(P[j], k, d, tol, okd);
                         else if (BITS && k < npts) A.car_bits[seg0 + k] = 0ULL;
                     }
-#endif
                 } else if (un > 0) {
                     qn = fuse_resolve<BITS>(cam, A, uq, un, q, qi, qn, seg0);
                     un = 0;
