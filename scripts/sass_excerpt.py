@@ -12,14 +12,18 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, 'lidar_object_detection_b200', 'csrc')
-HOT = [('fuse.cu', r'lf_fuse_kernelILi8ELi8ELb0', 'lf_fuse_kernel<8 warps, 8 loads, no car_bits> (point pass)'),
+HOT = [('fuse.cu', r'lf_fuse_kernelILi8ELi5ELb0', 'lf_fuse_kernel<8 warps, 5 loads, no car_bits> (point pass)'),
        ('fuse.cu', r'lf_car_stats_kernel', 'lf_car_stats_kernel (per-car decision)'),
        ('erode.cu', r'lf_erode_fast_kernelINS_6SeSpecILi3ELi0ELi1ELi0ELi0EEELi0EE', 'lf_erode_fast_kernel<SeCross3, uint8> (erode + pack, dominant)'),
        ('erode.cu', r'lf_erode_packed_kernelINS_6SeSpecILi3ELi0ELi1ELi0ELi0EEEEE', 'lf_erode_packed_kernel<SeCross3> (masks arrive bit-packed)'),
        ('compact.cu', r'lf_car_compact_kernelIfE', 'lf_car_compact_kernel<float> (order-preserving per-car compaction)'),
-       ('project.cu', r'lf_zscatter_batch_kernelILi1E', 'lf_zscatter_batch_kernel<last> (depth maps, scatter)')]
+       ('project.cu', r'lf_zscatter_batch_kernelILi1E', 'lf_zscatter_batch_kernel<last> (depth maps, scatter)'),
+       ('resize.cu', r'lf_resize_linear_sep_kernel', 'lf_resize_linear_sep_kernel (separable bilinear resize: PRMT + IDP.2A per pixel)'),
+       ('points.cu', r'lf_count_in_boxes_kernelIfE', 'lf_count_in_boxes_kernel<float> (128 points per warp, box cull by lane)'),
+       ('points.cu', r'lf_mask_gather_lean_kernel', 'lf_mask_gather_lean_kernel (funnel-shift bit collection)')]
 KEYS = ['UBLKCP', 'SYNCS', 'CREDUX', 'LDG.E.NA.128', 'LDG.E.128', 'LDG.E', 'CCTL', 'STG', 'REDG', 'ATOMG', 'ATOM.E', 'ATOMS', 'RED',
-        'DFMA', 'DMUL', 'DADD', 'FFMA', 'MUFU', 'VOTE', 'POPC', 'SHFL', 'LDS', 'STS', 'LDL', 'STL', 'BAR', 'UTMALDG', 'UTCHMMA']
+        'DFMA', 'DMUL', 'DADD', 'FFMA', 'MUFU', 'VOTE', 'POPC', 'SHFL', 'MATCH', 'IDP', 'PRMT', 'IMAD.HI', 'SHF', 'LDS', 'STS', 'LDL', 'STL',
+        'BAR', 'UTMALDG', 'UTCHMMA']
 
 
 def main():
@@ -63,7 +67,7 @@ def main():
         print('   %d SASS instructions; ' % len(ins) + ', '.join('%s %d' % (k, cnt[k]) for k in KEYS if cnt[k]))
         shown = 0
         for m in re.finditer(r'/\*([0-9a-f]{4})\*/\s+(.*?);', body):
-            if re.search(r'UBLKCP|SYNCS|CREDUX|LDG\.E\.NA\.128|CCTL|REDG|ATOM', m.group(2)) and shown < 6:
+            if re.search(r'UBLKCP|SYNCS|CREDUX|LDG\.E\.NA\.128|CCTL|REDG|ATOM|IDP|MATCH', m.group(2)) and shown < 6:
                 print('      /*%s*/ %s' % (m.group(1), m.group(2).strip()[:100]))
                 shown += 1
 
