@@ -1217,19 +1217,20 @@ def test_peer_store_exchange_equals_the_table_all_reduce(LF, calib):
 
 # ------------------------------------------------------------------ A6 / A8 stand-alone kernels, every layout
 
-@pytest.mark.parametrize('dtype,stride', [(np.float32, 4), (np.float32, 3), (np.float64, 3), (np.float64, 5)])
+@pytest.mark.parametrize('dtype,stride,B', [(np.float32, 4, 70), (np.float32, 3, 70), (np.float64, 3, 70), (np.float64, 5, 70),
+                                            (np.float32, 4, 530)])
 @pytest.mark.parametrize('oriented', [True, False])
-def test_count_and_containment_kernels_every_layout(LF, dtype, stride, oriented):
+def test_count_and_containment_kernels_every_layout(LF, dtype, stride, B, oriented):
     """lf_points_in_box / lf_count_in_boxes straight through the C ABI: float32 records of 4 (one 128-bit load
-    per point), packed rows of 3, float64 rows, 70 boxes (more than one lane block, staged in shared memory),
-    interleaved point sets, NaN / inf / huge coordinates -- against the oracle's per-box test
+    per point), packed rows of 3, float64 rows, 70 boxes (more than one lane block, staged in shared memory) and
+    530 (read from global memory), interleaved point sets, NaN / inf / huge coordinates -- against the oracle's per-box test
     (cvs_erosion.py:114-145, 175-195; V1:118-139)."""
     import torch
     from lidar_object_detection_b200 import _abi
     from lidar_object_detection_b200._abi import check, ptr
     ctx = LF.get_ctx(None)
-    rng = np.random.default_rng(11 + stride)
-    B, S, n = 70, 5, 20011
+    rng = np.random.default_rng(11 + stride + B)
+    S, n = 5, 20011
     centres = rng.uniform(-20, 20, (B, 3))
     corners = np.zeros((B, 8, 3))
     signs = np.array([[-1, -1, -1], [1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1]], float)
@@ -1273,7 +1274,7 @@ def test_count_and_containment_kernels_every_layout(LF, dtype, stride, oriented)
                                     int(oriented), ptr(inside), ctx.stream), ctx.h)
     assert np.array_equal(inside.cpu().numpy(), want)
     assert want.sum() > 1000
-    for b in (0, 3, 69):
+    for b in (0, 3, B - 1):
         flags = torch.empty(n, dtype=torch.uint8, device=ctx.device)
         check(ctx.lib.lf_points_in_box(ctx.h, ptr(d_rows), int(dtype == np.float64), n, stride, ptr(d_boxes[b]),
                                        int(oriented), ptr(flags), ctx.stream), ctx.h)
