@@ -51,7 +51,7 @@ lf_mask_gather_kernel(const uint32_t* __restrict__ packed, int m, int H, int W, 
 // The same with 32-bit arithmetic after one unsigned range test per coordinate (negative values wrap to huge ones),
 // the words of eight masks requested together, and each bit moved into place by one funnel shift
 // (acc = acc >> 1 | bit << 31).  Needs m * H * wpr < 2^31 words (the host checks).
-// What bounds it on a sweep (ncu, profiles/r02b_next_ncu_summary.txt): the L1 sector rate -- the 32 pixels of a warp
+// What bounds it on a sweep (ncu, profiles/r02c_next_ncu_summary.txt): the L1 sector rate -- the 32 pixels of a warp
 // lie on several image rows, so one gather instruction touches ~9.5 sectors, sixteen times per point.
 __global__ void __launch_bounds__(256)
 lf_mask_gather_lean_kernel(const uint32_t* __restrict__ packed, int m, int H, int W, int wpr,
