@@ -274,9 +274,10 @@ lf_erode_packed_direct_kernel(const uint4* __restrict__ in, uint4* __restrict__ 
         return o;
     };
     BBoxAcc acc;
-    const int nq = (r1 - r0) * qpr;
+    const int nq = (r1 - r0) * qpr;                          // < 2^16 (the launch checks): q / qpr by one multiplication
+    const unsigned qmagic = (unsigned)((0x100000000ULL + (unsigned)qpr - 1) / (unsigned)qpr);
     for (int q = threadIdx.x; q < nq; q += blockDim.x) {
-        const int lr = q / qpr, qx = q - lr * qpr, y = r0 + lr;
+        const int lr = mdiv(q, qmagic), qx = q - lr * qpr, y = r0 + lr;
         const int at = y * qpr + qx;                        // quad index inside the mask
         const bool up = y > 0, dn = y + 1 < H, lf = qx > 0, rt = qx + 1 < qpr;
         const uint4 c = __ldg(min4 + at);
@@ -318,7 +319,8 @@ cudaError_t launch_fast(const ErodeParams& P, int mode, const uint8_t* masks, ui
                         unsigned grid, size_t smem, cudaStream_t s) {
     if (mode == 0) return launch_fast_mode<SE, 0>(P, masks, packed, bbox, grid, smem, s);
     if (mode == 1) return launch_fast_mode<SE, 1>(P, masks, packed, bbox, grid, smem, s);
-    if (mode == 3 && SE::k == 3 && P.iterations == 1 && (int64_t)P.H * P.wpr < ((int64_t)1 << 29)) {
+    if (mode == 3 && SE::k == 3 && P.iterations == 1 && (int64_t)P.H * P.wpr < ((int64_t)1 << 29) &&
+        (int64_t)((P.H + EPD_STRIPS - 1) / EPD_STRIPS) * (P.wpr >> 2) + 256 < 65536) {
         // 3x3, one pass: straight from global memory through registers (whole quads per row are a condition of spec >= 0)
         lf_erode_packed_direct_kernel<(SE::hw(0) == 1)><<<(unsigned)(grid / P.strips * EPD_STRIPS), 256, 0, s>>>(
             (const uint4*)masks, (uint4*)packed, bbox, P.H, P.wpr >> 2);

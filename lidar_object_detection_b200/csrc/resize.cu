@@ -205,7 +205,8 @@ lf_resize_linear_sep_kernel(const uint8_t* __restrict__ src, int64_t m, int h, i
         // ---- pass 1: horizontal interpolation of the tile's source rows.  The (row, group) pairs are one flat range
         // cut into rounds of 128 (four groups per lane: all eight window loads go out before the first one is
         // used), dealt to the warps in turn -- a whole row per warp would leave five warps idle for the last rows
-        const int total = ns * G;
+        const int total = ns * G;                            // < 2^16 (the host checks): idx / G by one multiplication
+        const unsigned gmagic = (unsigned)((0x100000000ULL + (unsigned)G - 1) / (unsigned)G);
         const uint8_t* tile_src = src + (img * h + r_lo) * (int64_t)w;
         for (int c0 = warp * 128 + lane; c0 < total; c0 += nwarps * 128) {
             uint32_t lo[4], hi[4];
@@ -214,7 +215,7 @@ lf_resize_linear_sep_kernel(const uint8_t* __restrict__ src, int64_t m, int h, i
             for (int k = 0; k < 4; ++k) {
                 const int idx = c0 + 32 * k;
                 lo[k] = hi[k] = 0u;
-                rk[k] = idx / G;
+                rk[k] = mdiv(idx, gmagic);
                 gk[k] = idx - rk[k] * G;
                 if (idx < total) {
                     const uint32_t* rp = (const uint32_t*)(tile_src + (int64_t)rk[k] * w);
@@ -482,7 +483,7 @@ extern "C" int lf_resize_masks(lf_ctx* ctx, const uint8_t* src, int64_t m, int h
         const int ns_max = (int)((RL_ROWS - 1) * scale_y) + 4;
         const size_t smem_sep = (size_t)ns_max * (W >> 2) * sizeof(uint2) + (size_t)(W >> 2) * (16 + 8 + 4);
         if ((w & 3) == 0 && (W & 3) == 0 && w <= W && (((uintptr_t)src | (uintptr_t)dst) & 3) == 0 &&
-            smem_sep <= 100 * 1024) {
+            smem_sep <= 100 * 1024 && (int64_t)ns_max * (W >> 2) + 128 < 65536) {
             int64_t b3 = m * ((H + RL_ROWS - 1) / RL_ROWS);
             LF_CUDA(ctx, cudaFuncSetAttribute(lf_resize_linear_sep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_sep));

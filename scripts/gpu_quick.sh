@@ -1,15 +1,14 @@
-# quick GPU check: parity tests + short bench (no CPU baseline); extra bench args: $@
+# quick GPU check: parity tests + next-row timings (+ short bench); extra bench args: $@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_gpu.log
-for mode in "" "--workload cfg5 --steps 10"; do
-timeout 600 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --e2e-steps 1 $mode "$@" > gpurun_out/bench_quick${mode:0:3}.json 2> gpurun_out/bench_quick${mode:0:3}.err; echo "bench $mode rc=$?"
-python - "$mode" <<'PY'
-import json, sys
-m = sys.argv[1]
-try:
-    d=json.load(open('gpurun_out/bench_quick%s.json' % m[:3]))
-    print(m, 'ms/step', d['ms_per_step'], 'value %.4g'%d['value'], d['kernel_ms'], 'roofline frac', d['roofline']['frac'], 'e2e %.4g' % d['e2e']['value'])
-except Exception as e:
-    print('no bench line', e); print(open('gpurun_out/bench_quick%s.err' % m[:3]).read()[-2000:])
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 900 python bench_next.py > gpurun_out/bench_next.jsonl 2> gpurun_out/bench_next.err; echo "bench_next rc=$?"
+python - <<'PY'
+import json
+for l in open('gpurun_out/bench_next.jsonl'):
+    if l.startswith('{'):
+        d = json.loads(l)
+        print('%-60s %8.4f ms  frac %s' % (d['kernel'][:60], d['ms'], round(d.get('frac', 0), 3)))
 PY
-done
+timeout 600 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-e2e --no-cfg4 "$@" 2>/dev/null | python -c "
+import sys, json
+d = json.loads(sys.stdin.read().strip().splitlines()[-1]); print('cfg3 step %.3f' % d['ms_per_step'], d['kernel_ms'], 'parity', d['parity_checked_frames']); print('cfg5', d['cfg5'] and d['cfg5']['kernel_ms']); print('packed', d['packed_masks_in'] and d['packed_masks_in']['kernel_ms'])"
