@@ -71,6 +71,9 @@ cudaError_t launch_fuse(lf_ctx* ctx, FuseArgs A, int F, int64_t max_points_per_f
     if (e != cudaSuccess) return e;
     int64_t blocks = (cpf * F + WARPS - 1) / WARPS;
     if (blocks > (int64_t)ctx->sm_count * per_sm) blocks = (int64_t)ctx->sm_count * per_sm;
+#ifdef LF_FUSE_GRID_CAP
+    if (blocks > (int64_t)ctx->sm_count * LF_FUSE_GRID_CAP) blocks = (int64_t)ctx->sm_count * LF_FUSE_GRID_CAP;   // experiment
+#endif
     kern<<<(unsigned)blocks, G::NT, smem, stream>>>(ctx->cam, A);
     return cudaGetLastError();
 }
