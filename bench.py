@@ -34,6 +34,7 @@ CALIB_ROOT = os.path.join(ROOT, 'tests', 'golden', 'kitti360_sample')
 METRIC = 'points/sec (project+mask+bbox eval)'
 FRAMES, NCARS, RINGS, AZ = 1024, 16, 64, 2048
 KSIZE = 3
+SPARSE_ROWS = True       # timed steps write only the rows of the packed masks that have a set pixel (--dense-rows: every row)
 # BASELINE.json configs[2] (the metric's configuration) and configs[4] (dense stress)
 WORKLOADS = {'cfg3': dict(frames=1024, ncars=16, rings=64, az=2048, ksize=3),
              'cfg5': dict(frames=64, ncars=64, rings=64, az=32768, ksize=7)}
@@ -149,6 +150,8 @@ def bench_config(workload, frames, n_pts, world, step_bytes=None, exchange=None)
                                                              NCARS, KSIZE, KSIZE),
             'frames_per_gpu': frames, 'points_per_frame': n_pts, 'masks_per_frame': NCARS,
             'l2_policy': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush' % (step_bytes / 1e9),
+            'packed_rows': ('only the rows of the (internal) packed masks that have a set pixel are written and read '
+                            '(lf_erode_pack_rows / lf_fuse_batch_rows)') if SPARSE_ROWS else 'every row written (lf_erode_pack / lf_fuse_batch)',
             'parallelism': 'frames sharded, dp%d' % world,
             'exchange': exchange}
 
@@ -290,7 +293,7 @@ def side_cfg4(torch, dist, D, S, world, rank, local, dev, cam, TVC, TVR, sb0, ex
     def job(check):
         for i in range(nb):
             b = sbs[i % pool].batch
-            b.run(KSIZE, 1, 50, 10, True)
+            b.run(KSIZE, 1, 50, 10, True, sparse_rows=SPARSE_ROWS)
             if exch is not None:
                 t, _ = exch.exchange_batch(b)
                 got, agg = t, exch.agg
@@ -355,7 +358,7 @@ def side_cfg5(torch, dist, D, S, world, rank, local, dev, cam, TVC, TVR, steps):
     stream = torch.cuda.current_stream(dev)
 
     def step(mark=None):
-        b.run(w['ksize'], 1, 50, 10, True, mark=mark)
+        b.run(w['ksize'], 1, 50, 10, True, mark=mark, sparse_rows=SPARSE_ROWS)
         if ex is not None:
             ex.exchange_batch(b)
 
@@ -460,7 +463,7 @@ def run_gpu(args):
                 raise SystemExit('PARITY FAILURE: peer-store exchange differs from the NCCL all-reduce')
 
     def step(mark=None):
-        batch.run(KSIZE, 1, 50, 10, True, mark=mark)
+        batch.run(KSIZE, 1, 50, 10, True, mark=mark, sparse_rows=SPARSE_ROWS)
         if exch is not None:
             exch.exchange_batch(batch)
 
@@ -593,6 +596,7 @@ def run_gpu(args):
     if not args.no_packed:
         for _ in range(3):
             pstep()
+        batch.run(KSIZE, 1, 50, 10, True)                     # every row of the packed masks, for the comparison
         sync_all()
         same = all(torch.equal(a, b) for a, b in ((pb.total, batch.total), (pb.inside, batch.inside),
                                                   (pb.best_idx, batch.best_idx), (pb.packed.words, batch.packed.words)))
@@ -802,9 +806,14 @@ def main():
     ap.add_argument('--no-parity', action='store_true')
     ap.add_argument('--parity-frames', type=int, default=32, help='frames of the batch checked against the oracle')
     ap.add_argument('--no-packed', action='store_true', help='skip the packed-masks-in secondary measurement')
+    ap.add_argument('--dense-rows', action='store_true',
+                    help='write every row of the packed masks (lf_erode_pack / lf_fuse_batch) instead of only the rows '
+                         'with a set pixel (lf_erode_pack_rows / lf_fuse_batch_rows, the default of the timed steps)')
     ap.add_argument('--exchange', default='peer', choices=['peer', 'nccl'],
                     help='N > 1: per-car table exchanged by stores into peer memory (default) or by the NCCL all-reduce')
     args = ap.parse_args()
+    global SPARSE_ROWS
+    SPARSE_ROWS = not args.dense_rows
     set_workload(args.workload, args.frames)
     # stdout carries the ONE JSON line and nothing else: whatever libraries print while the job runs
     # (NCCL's version banner goes to stdout when NCCL_DEBUG is set) is sent to stderr at the fd level.

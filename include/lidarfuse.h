@@ -114,6 +114,20 @@ int lf_erode_pack(lf_ctx* ctx, const void* masks /*DEVICE [m][H][W], mode 3: [m]
                   uint32_t* packed /*DEVICE [m][H][wpr]*/,
                   int32_t* bbox /*DEVICE [m][4], zeroed by the caller, or NULL*/, void* stream);
 
+/* lf_erode_pack with a ROW MAP (same reference lines: cvs_erosion.py:96-106): bit y of
+ * row_map[mask * ceil(H/32) + (y >> 5)] = row y of the eroded mask has a set pixel.  Rows OUTSIDE the row range
+ * of the mask's bounding box (before its first / after its last row with a set pixel) may be left unwritten
+ * in `packed` -- the kernels that hold the eroded strip in shared memory skip every row without a set pixel,
+ * and the skipped rows inside the range are zero-filled afterwards: an instance mask covers a tenth of the
+ * image rows, so nine tenths of the packed words never travel to HBM.  Unwritten words are unspecified.
+ * For consumers that read a packed word only inside the bounding box's rows -- lf_fuse_batch_rows.
+ * row_map: DEVICE uint32 [m][ceil(H/32)], zeroed by the call; bbox must be given for the guarantee about
+ * the rows inside the range.  row_map == NULL is lf_erode_pack. */
+int lf_erode_pack_rows(lf_ctx* ctx, const void* masks /*DEVICE*/, int mode, int64_t m, int H, int W,
+                       const uint8_t* se /*HOST [k][k]*/, int k, int iterations, uint32_t* packed /*DEVICE [m][H][wpr]*/,
+                       int32_t* bbox /*DEVICE [m][4], zeroed by the caller, or NULL*/,
+                       uint32_t* row_map /*DEVICE [m][ceil(H/32)] or NULL*/, void* stream);
+
 /* Host-side transfer encoding of instance masks (plain C++, no device work): binarise
  * with the rule of `mode` (0, 1, 2 as lf_erode_pack) and pack to one bit per pixel,
  * uint32 [m][H][wpr], LSB = lowest x, pad bits zero -- the layout lf_erode_pack (mode 3)
@@ -162,6 +176,20 @@ int lf_fuse_batch(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_of
                   int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,
                   int32_t* total /*DEVICE*/, int32_t* inside /*DEVICE*/, int32_t* n_in_box /*DEVICE*/,
                   int32_t* n_valid /*DEVICE*/, uint64_t* car_bits /*DEVICE or NULL*/, void* stream);
+
+/* lf_fuse_batch for packed masks written by lf_erode_pack_rows (row_map != NULL says so; mask_bbox must be the
+ * one of that call): a packed word is read only inside its mask's bounding-box rows (same reference lines:
+ * cvs_erosion.py:342-372 without the erosion).  row_map == NULL is lf_fuse_batch. */
+int lf_fuse_batch_rows(lf_ctx* ctx, const float* pts /*DEVICE*/, const int64_t* pt_off /*DEVICE [F+1]*/,
+                  const uint32_t* packed /*DEVICE*/,
+                  const int32_t* mask_bbox /*DEVICE [sum M][4] from lf_erode_pack, 16-B aligned, or NULL*/,
+                  const int32_t* mask_off /*DEVICE [F+1]*/,
+                  const lf_box* boxes /*DEVICE*/, const int32_t* box_off /*DEVICE [F+1]*/,
+                  const int64_t* cnt_off /*DEVICE [F+1]*/, int F, int64_t max_points_per_frame,
+                  int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,
+                  int32_t* total /*DEVICE*/, int32_t* inside /*DEVICE*/, int32_t* n_in_box /*DEVICE*/,
+                  int32_t* n_valid /*DEVICE*/, uint64_t* car_bits /*DEVICE or NULL*/,
+                  const uint32_t* row_map /*DEVICE [sum M][ceil(H/32)] from lf_erode_pack_rows, or NULL*/, void* stream);
 
 /* The whole per-batch body of cvs_erosion.process_frames (:342-372) in one call:
  * lf_erode_pack + lf_fuse_batch + lf_car_stats with the same arguments and the same

@@ -40,6 +40,7 @@ SIGNATURES = {
     'lf_set_camera': (C.c_int, [_vp, _vp, _vp, _i32, _i32]),
     'lf_project': (C.c_int, [_vp, _vp, _i64, _f64, _vp, _vp, _vp, _vp, _vp]),
     'lf_erode_pack': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp]),
+    'lf_erode_pack_rows': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     'lf_unpack_masks': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     'lf_pack_masks_host': (C.c_int, [_vp, _i32, _i64, _i32, _i32, _vp, _i32]),
     'lf_host_simd': (C.c_int, [_i32]),
@@ -48,6 +49,8 @@ SIGNATURES = {
     'lf_prepare_boxes': (C.c_int, [_vp, _i64, _vp]),
     'lf_fuse_batch': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
                                 _vp, _vp, _vp, _vp, _vp, _vp]),
+    'lf_fuse_batch_rows': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _f64, _i32,
+                                     _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'lf_process_batch': (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i64, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                    _i32, _i64, _i32, _i32, _f64, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp]),

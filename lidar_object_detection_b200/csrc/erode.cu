@@ -314,13 +314,18 @@ cudaError_t launch_fast_mode(const ErodeParams& P, const uint8_t* masks, uint32_
     return cudaGetLastError();
 }
 
+// the direct kernel's case: packed words in, 3x3 element, one pass, index ranges of its 32-bit arithmetic
+static bool packed_direct_ok(const ErodeParams& P, int mode) {
+    return mode == 3 && P.k == 3 && P.iterations == 1 && (int64_t)P.H * P.wpr < ((int64_t)1 << 29) &&
+           (int64_t)((P.H + EPD_STRIPS - 1) / EPD_STRIPS) * (P.wpr >> 2) + 256 < 65536;
+}
+
 template <class SE>
 cudaError_t launch_fast(const ErodeParams& P, int mode, const uint8_t* masks, uint32_t* packed, int32_t* bbox,
                         unsigned grid, size_t smem, cudaStream_t s) {
     if (mode == 0) return launch_fast_mode<SE, 0>(P, masks, packed, bbox, grid, smem, s);
     if (mode == 1) return launch_fast_mode<SE, 1>(P, masks, packed, bbox, grid, smem, s);
-    if (mode == 3 && SE::k == 3 && P.iterations == 1 && (int64_t)P.H * P.wpr < ((int64_t)1 << 29) &&
-        (int64_t)((P.H + EPD_STRIPS - 1) / EPD_STRIPS) * (P.wpr >> 2) + 256 < 65536) {
+    if (SE::k == 3 && packed_direct_ok(P, mode)) {
         // 3x3, one pass: straight from global memory through registers (whole quads per row are a condition of spec >= 0)
         lf_erode_packed_direct_kernel<(SE::hw(0) == 1)><<<(unsigned)(grid / P.strips * EPD_STRIPS), 256, 0, s>>>(
             (const uint4*)masks, (uint4*)packed, bbox, P.H, P.wpr >> 2);
@@ -394,6 +399,51 @@ lf_erode_generic_kernel(const __grid_constant__ ErodeParams P, const void* __res
     }
     erode_and_store(P, bufA, bufB, ga, gb, r0, r1, packed + mask * (int64_t)P.H * P.wpr,
                     bbox ? bbox + 4 * mask : nullptr);
+}
+
+// Row map of packed masks that were written in full (the paths without the in-kernel map): one warp per
+// (mask, row), bit y of row_map[mask][y >> 5] = some word of row y is non-zero.
+__global__ void __launch_bounds__(256)
+lf_row_map_kernel(const uint32_t* __restrict__ packed, int64_t rows, int H, int wpr, int rm_wpr,
+                  uint32_t* __restrict__ row_map) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows; r += nw) {
+        uint32_t any = 0u;
+        for (int wx = lane; wx < wpr; wx += 32) any |= __ldg(packed + r * wpr + wx);
+        if (__any_sync(0xFFFFFFFFu, any != 0u) && lane == 0) {
+            const int64_t mask = r / H;
+            const int y = (int)(r - mask * H);
+            atomicOr(row_map + mask * rm_wpr + (y >> 5), 1u << (y & 31));
+        }
+    }
+}
+
+// After the kernels that skip rows without a set pixel: rows INSIDE a mask's bounding-box row range that were
+// skipped (a mask of two blobs, one above the other) are written as zeros, so that "every row from the first to
+// the last row with a set pixel is valid" holds -- what lf_fuse_batch_rows relies on.  One warp per mask; for the
+// usual single-blob mask there is nothing to do.
+__global__ void __launch_bounds__(256)
+lf_row_gap_fill_kernel(uint32_t* __restrict__ packed, const int32_t* __restrict__ bbox, const uint32_t* __restrict__ row_map,
+                       int64_t m, int H, int wpr, int rm_wpr) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t mask = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; mask < m; mask += nw) {
+        const int4 r = __ldg((const int4*)bbox + mask);
+        if (r.z <= 0) continue;                               // empty mask
+        const int y0 = (1 << 20) - r.y, y1 = r.w - 1;
+        for (int yw = y0 >> 5; yw <= (y1 >> 5); ++yw) {
+            uint32_t gaps = ~__ldg(row_map + mask * rm_wpr + yw);
+            if (yw == (y0 >> 5)) gaps &= 0xFFFFFFFFu << (y0 & 31);
+            if (yw == (y1 >> 5)) gaps &= 0xFFFFFFFFu >> (31 - (y1 & 31));
+            while (gaps) {
+                const int y = 32 * yw + __ffs((int)gaps) - 1;
+                gaps &= gaps - 1;
+                uint32_t* row = packed + (mask * H + y) * (int64_t)wpr;
+                for (int wx = lane; wx < wpr; wx += 32) row[wx] = 0u;
+            }
+        }
+    }
 }
 
 __global__ void lf_unpack_kernel(const uint32_t* __restrict__ packed, int64_t total_px, int H, int W, int wpr,
@@ -489,6 +539,12 @@ int lf_erode_plan(const lf_ctx* ctx, const void* masks, int mode, int64_t m, int
 extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
                              const uint8_t* se, int k, int iterations, uint32_t* packed, int32_t* bbox,
                              void* stream) {
+    return lf_erode_pack_rows(ctx, masks, mode, m, H, W, se, k, iterations, packed, bbox, nullptr, stream);
+}
+
+extern "C" int lf_erode_pack_rows(lf_ctx* ctx, const void* masks, int mode, int64_t m, int H, int W,
+                                  const uint8_t* se, int k, int iterations, uint32_t* packed, int32_t* bbox,
+                                  uint32_t* row_map, void* stream) {
     if (!ctx || m < 0 || H <= 0 || W <= 0 || iterations < 0 || mode < 0 || mode > 3) return LF_E_ARG;
     if (m > 0 && (!masks || !packed)) return LF_E_ARG;
     if (mode == 3 && (const void*)masks == (const void*)packed) return LF_E_ARG;   // strips read their neighbours' rows
@@ -505,6 +561,33 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
     if (rc != LF_OK) return rc;
     const unsigned grid = (unsigned)(m * P.strips);
     cudaStream_t s = (cudaStream_t)stream;
+    // row map: the kernels that hold the eroded strip in shared memory write it themselves and skip the rows without
+    // a set pixel; the others write every row, and the map is read off the packed words afterwards
+    const int rm_wpr = (H + 31) / 32;
+    bool map_in_kernel = false;
+    if (row_map) {
+        LF_CUDA(ctx, cudaMemsetAsync(row_map, 0, (size_t)m * rm_wpr * sizeof(uint32_t), s));
+        map_in_kernel = spec >= 0 && !packed_direct_ok(P, mode);
+        if (map_in_kernel) { P.row_map = row_map; P.rm_wpr = rm_wpr; }
+    }
+    auto finish = [&]() -> int {
+        if (row_map && map_in_kernel && bbox) {
+            int64_t blocks = (m + 7) / 8;
+            const int64_t cap = (int64_t)ctx->sm_count * 16;
+            if (blocks > cap) blocks = cap;
+            lf_row_gap_fill_kernel<<<(unsigned)blocks, 256, 0, s>>>(packed, bbox, row_map, m, H, P.wpr, rm_wpr);
+            LF_CUDA(ctx, cudaGetLastError());
+        }
+        if (row_map && !map_in_kernel) {
+            const int64_t rows = m * H;
+            int64_t blocks = (rows + 7) / 8;
+            const int64_t cap = (int64_t)ctx->sm_count * 16;
+            if (blocks > cap) blocks = cap;
+            lf_row_map_kernel<<<(unsigned)blocks, 256, 0, s>>>(packed, rows, H, P.wpr, rm_wpr, row_map);
+            LF_CUDA(ctx, cudaGetLastError());
+        }
+        return LF_OK;
+    };
     if (spec >= 0) {
         const uint8_t* mk = (const uint8_t*)masks;
         cudaError_t e;
@@ -520,7 +603,7 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
             default: e = launch_fast<SeCross7>(P, mode, mk, packed, bbox, grid, smem, s); break;
         }
         LF_CUDA(ctx, e);
-        return LF_OK;
+        return finish();
     }
     if (fast && mode == 0) {
         LF_CUDA(ctx, cudaFuncSetAttribute(lf_erode_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -544,7 +627,7 @@ extern "C" int lf_erode_pack(lf_ctx* ctx, const void* masks, int mode, int64_t m
         lf_erode_generic_kernel<2><<<grid, ER_THREADS, smem, s>>>(P, masks, packed, bbox);
     }
     LF_CUDA(ctx, cudaGetLastError());
-    return LF_OK;
+    return finish();
 }
 
 extern "C" int lf_unpack_masks(lf_ctx* ctx, const uint32_t* packed, int64_t m, int H, int W, uint8_t* out,

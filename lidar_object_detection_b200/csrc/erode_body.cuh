@@ -23,6 +23,10 @@ struct ErodeParams {
     unsigned short se_rows[LF_MAX_SE];   // bit j of se_rows[i] = SE[i][j]
     signed char span_a[LF_MAX_SE];       // row i covers dx in [-span_a[i], +span_b[i]]; span_a < 0: empty row
     signed char span_b[LF_MAX_SE];
+    // optional row map (lf_erode_pack_rows): bit y of row_map[mask * rm_wpr + (y >> 5)] = row y of the eroded mask
+    // has a set pixel; when given, rows WITHOUT a set pixel are not written to `packed` at all
+    uint32_t* row_map;
+    int rm_wpr;
 };
 
 // Host-side plan of one lf_erode_pack call (erode.cu): fills P, picks the compile-time
@@ -186,12 +190,21 @@ __device__ __forceinline__ uint32_t erode_pass_fast(const ErodeParams& P, const 
 }
 
 // Rows [r0, r1) of the result from the guarded layout to global memory + the mask's bounding box.
+// With a row map (`rowmap_rec` = the mask's words of it): a first pass over the shared-memory words notes which rows
+// have a set pixel, only those rows are stored, and their bits are OR-ed into the map -- an instance mask covers a
+// tenth of the image rows, so nine tenths of the packed words never travel to HBM.
 template <int PAD>
 __device__ __forceinline__ void store_rows_fast(const ErodeParams& P, const uint32_t* cur, uint32_t* __restrict__ dstw,
-                                                int32_t* __restrict__ bbox_rec, int r0, int r1, int first, int S,
-                                                int tid) {
+                                                int32_t* __restrict__ bbox_rec, uint32_t* __restrict__ rowmap_rec, int r0,
+                                                int r1, int first, int S, int tid) {
     // `first` = word index of (row r0, wx 0) in `cur`
+    __shared__ uint32_t s_rowbits[(ER_MAX_ROWS + 31) / 32 + 1];
     BBoxAcc acc;
+    const bool sparse = rowmap_rec != nullptr;
+    if (sparse) {
+        if (tid < (int)(sizeof(s_rowbits) / 4)) s_rowbits[tid] = 0u;
+        er_sync();
+    }
     if ((P.wpr & 3) == 0) {
         // four words per thread: one 128-bit store, one bounding-box test per 128 pixels
         const int qpr = P.wpr >> 2;                        // quads per row
@@ -202,10 +215,20 @@ __device__ __forceinline__ void store_rows_fast(const ErodeParams& P, const uint
             const int wq = q - lr * qpr;
             const uint32_t* sp = cur + lr * S + 4 * wq + first;
             const uint4 v = PAD == 4 ? *(const uint4*)sp : make_uint4(sp[0], sp[1], sp[2], sp[3]);
-            *(uint4*)(dstw + 4 * q) = v;
+            if (!sparse) *(uint4*)(dstw + 4 * q) = v;
             if (v.x | v.y | v.z | v.w) {
                 acc.add(v.x, r0 + lr, 4 * wq); acc.add(v.y, r0 + lr, 4 * wq + 1);
                 acc.add(v.z, r0 + lr, 4 * wq + 2); acc.add(v.w, r0 + lr, 4 * wq + 3);
+                if (sparse) atomicOr(&s_rowbits[lr >> 5], 1u << (lr & 31));
+            }
+        }
+        if (sparse) {
+            er_sync();
+            for (int q = tid; q < nq; q += ER_THREADS) {
+                const int lr = mdiv(q, qmagic);
+                if (!((s_rowbits[lr >> 5] >> (lr & 31)) & 1u)) continue;
+                const uint32_t* sp = cur + lr * S + 4 * (q - lr * qpr) + first;
+                *(uint4*)(dstw + 4 * q) = PAD == 4 ? *(const uint4*)sp : make_uint4(sp[0], sp[1], sp[2], sp[3]);
             }
         }
     } else {
@@ -213,14 +236,28 @@ __device__ __forceinline__ void store_rows_fast(const ErodeParams& P, const uint
         for (int it = tid; it < out_items; it += ER_THREADS) {
             const int lr = mdiv(it, P.wpr_magic);
             const uint32_t w = cur[it + PAD * lr + first];
-            dstw[it] = w;
+            if (!sparse) dstw[it] = w;
+            else if (w) atomicOr(&s_rowbits[lr >> 5], 1u << (lr & 31));
             acc.add(w, r0 + lr, it - lr * P.wpr);
         }
+        if (sparse) {
+            er_sync();
+            for (int it = tid; it < out_items; it += ER_THREADS) {
+                const int lr = mdiv(it, P.wpr_magic);
+                if ((s_rowbits[lr >> 5] >> (lr & 31)) & 1u) dstw[it] = cur[it + PAD * lr + first];
+            }
+        }
+    }
+    if (sparse) {
+        for (int lr = tid; lr < r1 - r0; lr += ER_THREADS)
+            if ((s_rowbits[lr >> 5] >> (lr & 31)) & 1u) atomicOr(rowmap_rec + ((r0 + lr) >> 5), 1u << ((r0 + lr) & 31));
+        er_sync();                                         // s_rowbits is free for a next item of this CTA
     }
     if (bbox_rec) acc.flush(bbox_rec);
 }
 
 __device__ __forceinline__ void store_zero_rows(const ErodeParams& P, uint32_t* __restrict__ dstw, int out_items, int tid) {
+    if (P.row_map) return;                                 // no row of the strip has a set pixel: nothing to write, no bit to set
     if ((P.wpr & 3) == 0) {
         for (int q = tid; q < (out_items >> 2); q += ER_THREADS) *(uint4*)(dstw + 4 * q) = make_uint4(0u, 0u, 0u, 0u);
     } else {
@@ -343,7 +380,8 @@ __device__ __forceinline__ void erode_fast_item(const ErodeParams& P, const uint
         uint32_t* t = cur; cur = nxt; nxt = t;
     }
     if (P.iterations > 0) er_sync();
-    store_rows_fast<1>(P, cur, dstw, bbox ? bbox + 4 * mask : nullptr, r0, r1, data0 + (r0 - ga) * S, S, tid);
+    store_rows_fast<1>(P, cur, dstw, bbox ? bbox + 4 * mask : nullptr, P.row_map ? P.row_map + mask * P.rm_wpr : nullptr, r0,
+                       r1, data0 + (r0 - ga) * S, S, tid);
 }
 
 // Masks that arrive bit-packed already (mode 3: uint32 [M][H][wpr], LSB = lowest x; whole quads per
@@ -399,7 +437,8 @@ __device__ __forceinline__ void erode_packed_item(const ErodeParams& P, const ui
             return;
         }
     }
-    store_rows_fast<PAD>(P, cur, dstw, bbox ? bbox + 4 * mask : nullptr, r0, r1, data0 + (r0 - ga) * S, S, tid);
+    store_rows_fast<PAD>(P, cur, dstw, bbox ? bbox + 4 * mask : nullptr, P.row_map ? P.row_map + mask * P.rm_wpr : nullptr,
+                         r0, r1, data0 + (r0 - ga) * S, S, tid);
 }
 
 typedef SeSpec<3, 0, 1, 0, 0> SeCross3;     // = MORPH_ELLIPSE 3x3 (cvs_erosion.py:98 default)

@@ -30,11 +30,11 @@ namespace {
 #define LF_FUSE_CLAIM 2048       /* points per claim for batches that fill the machine */
 #endif
 
-template <int WARPS, int PER, bool BITS, int CTAS>
+template <int WARPS, int PER, bool BITS, int CTAS, bool ROWS>
 __global__ void __launch_bounds__(32 * WARPS, CTAS)
 lf_fuse_kernel(const __grid_constant__ LfCam cam, const __grid_constant__ FuseArgs A) {
     extern __shared__ __align__(128) uint8_t smem[];
-    fuse_warp_loop<WARPS, PER, BITS>(cam, A, smem);
+    fuse_warp_loop<WARPS, PER, BITS, ROWS>(cam, A, smem);
 }
 
 // Persistent launch: as many CTAs as fit the machine (or as there are claims), every warp an
@@ -43,7 +43,9 @@ template <int WARPS, int PER, bool BITS, int CTAS>
 cudaError_t launch_fuse(lf_ctx* ctx, FuseArgs A, int F, int64_t max_points_per_frame, cudaStream_t stream) {
     using G = FuseGeom<WARPS, PER, BITS>;
     const size_t smem = G::warp_bytes(A.smem_cars, A.smem_boxes) * WARPS;
-    auto kern = lf_fuse_kernel<WARPS, PER, BITS, CTAS>;
+    // the kernels without per-point membership output come in two builds, without and with the row-map lookup in
+    // the gather (the lookup costs the dense path 2 % just by being there); the others always carry it
+    auto kern = (BITS || A.row_map) ? lf_fuse_kernel<WARPS, PER, BITS, CTAS, true> : lf_fuse_kernel<WARPS, PER, BITS, CTAS, BITS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
@@ -168,6 +170,17 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
                              int max_masks_per_frame, int max_boxes_per_frame, double max_depth,
                              int use_oriented, int32_t* total, int32_t* inside, int32_t* n_in_box,
                              int32_t* n_valid, uint64_t* car_bits, void* stream) {
+    return lf_fuse_batch_rows(ctx, pts, pt_off, packed, mask_bbox, mask_off, boxes, box_off, cnt_off, F, max_points_per_frame,
+                              max_masks_per_frame, max_boxes_per_frame, max_depth, use_oriented, total, inside, n_in_box,
+                              n_valid, car_bits, nullptr, stream);
+}
+
+extern "C" int lf_fuse_batch_rows(lf_ctx* ctx, const float* pts, const int64_t* pt_off, const uint32_t* packed,
+                                  const int32_t* mask_bbox, const int32_t* mask_off, const lf_box* boxes,
+                                  const int32_t* box_off, const int64_t* cnt_off, int F, int64_t max_points_per_frame,
+                                  int max_masks_per_frame, int max_boxes_per_frame, double max_depth, int use_oriented,
+                                  int32_t* total, int32_t* inside, int32_t* n_in_box, int32_t* n_valid,
+                                  uint64_t* car_bits, const uint32_t* row_map, void* stream) {
     if (!ctx || F < 0 || max_points_per_frame < 0 || max_masks_per_frame < 0 || max_boxes_per_frame < 0)
         return LF_E_ARG;
     if (!ctx->has_camera) return LF_E_NOCAMERA;
@@ -177,6 +190,7 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     if (max_boxes_per_frame > 0 && (!boxes || !n_in_box)) return LF_E_ARG;
     if (max_masks_per_frame > 0 && max_boxes_per_frame > 0 && !inside) return LF_E_ARG;
     if (((uintptr_t)pts & 15) != 0 || ((uintptr_t)mask_bbox & 15) != 0) return LF_E_ARG;
+    if (row_map && !mask_bbox) return LF_E_ARG;             // the rows that are valid are the bounding box's
     if ((int64_t)ctx->cam.H * ctx->cam.wpr * LF_MAX_CARS >= ((int64_t)1 << 31)) return LF_E_UNSUPPORTED;
     if (ctx->cam.W > 65535 || ctx->cam.H > 65535) return LF_E_UNSUPPORTED;   // queued pixels are 16 + 16 bits
     if (max_masks_per_frame > LF_MAX_CARS && car_bits) return LF_E_UNSUPPORTED;   // one 64-bit membership word per point
@@ -185,6 +199,7 @@ extern "C" int lf_fuse_batch(lf_ctx* ctx, const float* pts, const int64_t* pt_of
     FuseArgs A;
     A.pts = (const float4*)pts; A.pt_off = pt_off; A.packed = packed; A.mask_bbox = mask_bbox; A.mask_off = mask_off;
     A.boxes = boxes; A.box_off = box_off; A.cnt_off = cnt_off;
+    A.row_map = row_map; A.rm_wpr = (ctx->cam.H + 31) / 32;
     A.total = total; A.inside = inside; A.n_in_box = n_in_box; A.n_valid = n_valid;
     A.car_bits = (unsigned long long*)car_bits;
     A.max_depth = max_depth;

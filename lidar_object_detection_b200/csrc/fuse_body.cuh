@@ -49,6 +49,8 @@ struct FuseArgs {
     const int64_t* pt_off;
     const uint32_t* packed;
     const int32_t* mask_bbox;   // optional [sum M][4] from lf_erode_pack, NULL = test every mask
+    const uint32_t* row_map;    // non-NULL: the packed masks come from lf_erode_pack_rows -- only the rows inside a mask's bounding box are valid
+    int rm_wpr;
     const int32_t* mask_off;
     const lf_box* boxes;
     const int32_t* box_off;
@@ -161,6 +163,7 @@ __device__ __forceinline__ void add_per_car2(unsigned blk0, unsigned blk1, bool 
 
 // ---- phase B on 64 work-queue points, two per lane (lane l: entries l and l + 32): the pixel / xyz bounds, both
 // culls, the candidate loops and the counter atomics are paid once per 64 points instead of once per 32.
+template <bool ROWS>
 __device__ __forceinline__ void fuse_group2(const LfCam& cam, const FuseArgs& A, const FuseFrame& Fr, float4 e0, float4 e1,
                                             bool have0, bool have1, int plane32, unsigned long long& bits0,
                                             unsigned long long& bits1) {
@@ -199,8 +202,16 @@ __device__ __forceinline__ void fuse_group2(const LfCam& cam, const FuseArgs& A,
                 }
 #pragma unroll
                 for (int j = 0; j < LF_FUSE_GATHER; ++j) {
-                    w0[j] = (have0 && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off0 + (g + c[j]) * plane32)) : 0u;
-                    w1[j] = (have1 && c[j] >= 0) ? __ldg(Fr.mask_base + (unsigned)(off1 + (g + c[j]) * plane32)) : 0u;
+                    bool g0 = have0 && c[j] >= 0, g1 = have1 && c[j] >= 0;
+                    if (ROWS && A.row_map && c[j] >= 0) {
+                        // packed masks of lf_erode_pack_rows: only the rows from the mask's first to its last row with
+                        // a set pixel hold valid words (the bounding box says which), the others were never written
+                        const int4 bb = Fr.mbb[g + c[j]];
+                        g0 &= vi0 >= bb.y && vi0 <= bb.w;
+                        g1 &= vi1 >= bb.y && vi1 <= bb.w;
+                    }
+                    w0[j] = g0 ? __ldg(Fr.mask_base + (unsigned)(off0 + (g + c[j]) * plane32)) : 0u;
+                    w1[j] = g1 ? __ldg(Fr.mask_base + (unsigned)(off1 + (g + c[j]) * plane32)) : 0u;
                 }
 #pragma unroll
                 for (int j = 0; j < LF_FUSE_GATHER; ++j)
@@ -315,7 +326,8 @@ struct FuseGeom {
     }
 };
 
-template <int WARPS, int PER, bool BITS>
+//   ROWS   the packed masks may come with a row map (lf_erode_pack_rows): the gather consults it
+template <int WARPS, int PER, bool BITS, bool ROWS>
 __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs& A, uint8_t* smem) {
     using G = FuseGeom<WARPS, PER, BITS>;
     constexpr int SPAN = G::SPAN, QCAP = G::QCAP, UCAP = G::UCAP;
@@ -397,7 +409,7 @@ __device__ __forceinline__ void fuse_warp_loop(const LfCam& cam, const FuseArgs&
                 const int at0 = qn - cnt + (have0 ? lane : 0), at1 = qn - cnt + (have1 ? lane + 32 : 0);
                 const float4 e0 = q[at0], e1 = q[at1];
                 unsigned long long bits0, bits1;
-                fuse_group2(cam, A, Fr, e0, e1, have0, have1, plane32, bits0, bits1);
+                fuse_group2<ROWS>(cam, A, Fr, e0, e1, have0, have1, plane32, bits0, bits1);
                 if (BITS && have0) A.car_bits[seg0 + qi[at0]] = bits0;
                 if (BITS && have1) A.car_bits[seg0 + qi[at1]] = bits1;
                 nval += cnt;

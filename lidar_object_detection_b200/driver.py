@@ -162,7 +162,7 @@ def process_sweeps_streamed(paths, frame_inputs, camera, TrVeloToRect, frames_pe
                                                         device=ctx.device)
         batch = LF.FrameBatch(points, counts, mt, nm, np.concatenate(corners) if corners else np.zeros((0, 8, 3)), nb,
                               camera, TrVeloToRect, device=ctx.device.index)
-        batch.run(erosion_kernel_size, erosion_iterations, max_depth, min_points, use_oriented)
+        batch.run(erosion_kernel_size, erosion_iterations, max_depth, min_points, use_oriented, sparse_rows=True)
         if pending is not None:
             drain(pending)                                 # read batch i-1 back while batch i runs
         pending = (batch, frame_ids[i0:i0 + n])

@@ -712,9 +712,15 @@ class FrameBatch:
         self.launches_per_run = 0
 
     def run(self, erosion_kernel_size=3, erosion_iterations=1, max_depth=50, min_points=10, use_oriented=True,
-            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, one_call=False, exact=False):
+            shape=MORPH_ELLIPSE, float_threshold='ge_one', mark=None, one_call=False, exact=False, sparse_rows=False):
         """memset + erode/pack + fused point pass + per-car decision, all async
         on the current stream.  Returns nothing; read ``results()`` / ``table()``.
+
+        ``sparse_rows=True`` (uint8 / float32 / raw packed masks eroded by this call): the erode kernel writes only
+        the rows of the packed masks that have a set pixel plus a row map, and the point pass consults the map
+        (``lf_erode_pack_rows`` / ``lf_fuse_batch_rows``) -- same counters, nine tenths of the packed words never
+        travel to HBM; ``self.packed.words`` is then NOT a complete mask (rows without a set pixel keep whatever
+        they held), so leave it off when something else reads the packed masks afterwards.
 
         ``one_call=True`` issues erode + point pass + decision through the single ABI entry
         ``lf_process_batch`` instead of the three calls (``mark(name)`` between them);
@@ -766,18 +772,24 @@ class FrameBatch:
             mark('car_stats')
             self.launches_per_run = 1 + (1 if raw else 0) + (2 if (self.F and self.max_n) else 0)
             return
+        row_map = None
+        if raw and sparse_rows and not pre:                # (packed words in: the direct kernel writes every row anyway)
+            if getattr(self, '_row_map', None) is None:
+                self._row_map = torch.empty((max(len(mt), 1), (self.camera.height + 31) // 32), dtype=torch.int32,
+                                            device=ctx.device)
+            row_map = self._row_map
         if raw:
-            check(lib.lf_erode_pack(ctx.h, ptr(mt), mode, len(mt), self.camera.height, self.camera.width,
-                                    se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
-                                    ptr(self.packed.words), ptr(self.mask_bbox), st), ctx.h)
-            launches += 1
+            check(lib.lf_erode_pack_rows(ctx.h, ptr(mt), mode, len(mt), self.camera.height, self.camera.width,
+                                         se.ctypes.data if iters else None, se.shape[0] if iters else 1, iters,
+                                         ptr(self.packed.words), ptr(self.mask_bbox), ptr(row_map), st), ctx.h)
+            launches += 2 if row_map is not None else 1    # + the gap-fill kernel behind the row map
         mark('erode_pack')
         if self.F and self.max_n:
-            check(lib.lf_fuse_batch(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
-                                    ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
-                                    self.F, self.max_n, self.max_m, self.max_b, float(max_depth),
-                                    flags, ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
-                                    ptr(self.n_valid), ptr(self.car_bits), st), ctx.h)
+            check(lib.lf_fuse_batch_rows(ctx.h, ptr(self.points), ptr(self.pt_off), ptr(self.packed.words), ptr(bbox),
+                                         ptr(self.mask_off), ptr(self.boxes), ptr(self.box_off), ptr(self.cnt_off),
+                                         self.F, self.max_n, self.max_m, self.max_b, float(max_depth),
+                                         flags, ptr(self.total), ptr(self.inside), ptr(self.n_in_box),
+                                         ptr(self.n_valid), ptr(self.car_bits), ptr(row_map), st), ctx.h)
             mark('fuse')
             check(lib.lf_car_stats(ctx.h, ptr(self.total), ptr(self.inside), ptr(self.mask_off),
                                    ptr(self.box_off), ptr(self.cnt_off), self.F, int(min_points),
@@ -958,7 +970,8 @@ def process_frames_batched(points, n_points, masks, n_masks, bboxes_per_frame, c
     allc = np.concatenate(corners) if corners else np.zeros((0, 8, 3))
     batch = FrameBatch(points, n_points, masks, n_masks, allc, n_boxes, camera, TrVeloToRect, device,
                        want_car_bits=return_points)
-    batch.run(erosion_kernel_size, erosion_iterations, max_depth, min_points, use_oriented)
+    batch.run(erosion_kernel_size, erosion_iterations, max_depth, min_points, use_oriented,
+              sparse_rows=True)                        # the packed masks are this call's own intermediate
     res = batch.results()
     out = []
     for f in range(batch.F):

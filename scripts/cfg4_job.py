@@ -65,7 +65,7 @@ def main():
     def job(check):
         for i in range(nb):
             sb = sbs[i % pool]
-            sb.batch.run(3, 1, 50, 10, True)
+            sb.batch.run(3, 1, 50, 10, True, sparse_rows=True)
             table, _ = exch.exchange_batch(sb.batch)
             if check:
                 ok.mul_((table.to(torch.int32) == want[i % pool]).all().to(torch.int32))

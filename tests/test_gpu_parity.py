@@ -1303,3 +1303,89 @@ def test_mask_gather_more_than_eight_masks(LF):
         for c in range(m):
             want[ok] |= masks[c, v[ok], u[ok]].astype(np.uint64) << np.uint64(c)
         assert np.array_equal(got, want), m
+
+
+# ------------------------------------------------------------------ row map: only the rows with a set pixel are written
+
+@pytest.mark.parametrize('W,H', [(1408, 376), (128, 40), (1000, 123), (64, 8)])
+def test_erode_pack_rows_writes_the_map_and_only_needs_the_mapped_rows(LF, W, H):
+    """lf_erode_pack_rows against lf_erode_pack for every mask format and kernel family (compile-time elements
+    with the in-kernel map, the direct packed kernel and the generic paths with the map read off afterwards):
+    the map is exactly "row has a set pixel", the mapped rows hold the dense result, the bounding boxes agree;
+    the packed buffer is poisoned first, so a row that is skipped shows."""
+    import torch
+    from lidar_object_detection_b200 import _abi, io as IO
+    from lidar_object_detection_b200._abi import check, ptr
+    ctx = LF.get_ctx(None)
+    rng = np.random.default_rng(W + 3 * H)
+    masks = MP.random_blob_masks(rng, 6, H, W, n_blobs=2, max_r=max(3, min(H, W) // 5))
+    masks[3] = 1
+    masks[4] = 0
+    masks[5, :, :] = 0
+    masks[5, H // 2, W // 3] = 1                             # a single pixel: gone after any erosion
+    wpr, rmw = (W + 31) // 32, (H + 31) // 32
+    inputs = [('u8', torch.from_numpy(masks * 255).to(ctx.device), _abi.MODE_U8 if hasattr(_abi, 'MODE_U8') else 0),
+              ('f32', torch.from_numpy(masks.astype(np.float32)).to(ctx.device), 1),
+              ('packed', torch.from_numpy(IO.pack_masks_host(masks).view(np.int32)).to(ctx.device), 3)]
+    for name, t, mode in inputs:
+        for shape in (LF.MORPH_ELLIPSE, LF.MORPH_RECT):
+            for k, it in ((3, 1), (5, 2), (1, 0)):
+                se = LF.structuring_element(shape, k) if it else None
+                dense = torch.zeros((6, H, wpr), dtype=torch.int32, device=ctx.device)
+                bb_d = torch.zeros((6, 4), dtype=torch.int32, device=ctx.device)
+                check(ctx.lib.lf_erode_pack(ctx.h, ptr(t), mode, 6, H, W, se.ctypes.data if it else None, k, it,
+                                            ptr(dense), ptr(bb_d), ctx.stream), ctx.h)
+                sparse = torch.full((6, H, wpr), 0x5A5A5A5A, dtype=torch.int32, device=ctx.device)
+                bb_s = torch.zeros((6, 4), dtype=torch.int32, device=ctx.device)
+                rm = torch.full((6, rmw), -1, dtype=torch.int32, device=ctx.device)    # the call zeroes it
+                check(ctx.lib.lf_erode_pack_rows(ctx.h, ptr(t), mode, 6, H, W, se.ctypes.data if it else None, k, it,
+                                                 ptr(sparse), ptr(bb_s), ptr(rm), ctx.stream), ctx.h)
+                d, s_, m = dense.cpu().numpy(), sparse.cpu().numpy(), rm.cpu().numpy().view(np.uint32)
+                rows = (d != 0).any(axis=2)                                           # [6, H]
+                got_rows = ((m[:, np.arange(H) >> 5] >> (np.arange(H) & 31).astype(np.uint32)) & 1).astype(bool)
+                key = (name, W, H, shape, k, it)
+                assert np.array_equal(got_rows, rows), key
+                assert np.array_equal(s_[rows], d[rows]), key
+                assert torch.equal(bb_s, bb_d), key
+                assert np.all((s_[~rows] == 0) | (s_[~rows] == 0x5A5A5A5A)), key      # skipped, or written as zeros
+                # every row from the first to the last row with a set pixel is valid (skipped rows in between are
+                # zero-filled); outside that range the kernels with the in-kernel map really skip
+                ys = np.arange(H)
+                for i in range(6):
+                    if not rows[i].any():
+                        continue
+                    y0, y1 = ys[rows[i]].min(), ys[rows[i]].max()
+                    assert np.array_equal(s_[i, y0:y1 + 1], d[i, y0:y1 + 1]), key
+                    if name != 'packed' and W % 32 == 0 and k in (3, 5):
+                        outside = np.ones(H, bool)
+                        outside[y0:y1 + 1] = False
+                        assert np.all(s_[i, outside] == 0x5A5A5A5A), key
+
+
+def test_sparse_rows_batch_equals_the_dense_batch(LF, calib, golden):
+    """FrameBatch.run(sparse_rows=True): same counters and decisions as the dense step, with the packed buffer
+    poisoned beforehand (a word of an unmapped row that reached a counter would show) -- the real sample frames
+    (up to 314 boxes), a synthetic batch, and frames with 130 masks (two passes of 64)."""
+    import torch
+    from lidar_object_detection_b200 import synthetic as S
+    cam, TVC, TVR = calib
+    frames = golden['_meta']['frames'][:6]
+    pts, masks, boxes, raws = _batch_inputs(frames, cam, TVC, LF)
+    corners = [np.array([b['corners_velo'] for b in bs], dtype=np.float64).reshape(-1, 8, 3) for bs in boxes]
+    batches = [LF.FrameBatch(np.concatenate(pts), [len(p) for p in pts], np.concatenate(masks), [len(m) for m in masks],
+                             np.concatenate(corners), [len(b) for b in boxes], cam, TVR)]
+    batches.append(S.SyntheticBatch(12, cam, TVC, TVR, ncars=16, device=0).batch)
+    rng = np.random.default_rng(8)
+    many = MP.random_blob_masks(rng, 130, cam.height, cam.width, n_blobs=1, max_r=40)
+    batches.append(LF.FrameBatch(pts[0], [len(pts[0])], many, [130], corners[0], [len(boxes[0])], cam, TVR))
+    for b in batches:
+        for args in ((3, 1, 50, 10, True), (5, 2, 30, 5, False), (0, 0, 50, 10, True)):
+            b.run(*args)
+            want = {k: v.copy() for k, v in b.results().items()}
+            b.packed.words.fill_(-1)
+            b.run(*args, sparse_rows=True)
+            got = b.results()
+            assert set(got) == set(want)
+            for k in want:
+                assert np.array_equal(got[k], want[k]), (k, args)
+            assert sum(int(v.sum()) for k, v in want.items() if k == 'total') > 0
