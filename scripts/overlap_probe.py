@@ -15,6 +15,7 @@ torch.cuda.synchronize()
 ref = [sb.batch.counters.clone() for sb in sbs]
 streams = [torch.cuda.Stream(), torch.cuda.Stream()]
 K_STEPS = 40
+SPARSE = os.environ.get("LF_PROBE_DENSE") is None
 for mode in ('one stream', 'two streams'):
     for rep in range(2):
         torch.cuda.synchronize()
@@ -25,7 +26,7 @@ for mode in ('one stream', 'two streams'):
         for i in range(K_STEPS):
             st = streams[i % 2] if mode == 'two streams' else streams[0]
             with torch.cuda.stream(st):
-                sbs[i % 2].batch.run(3, 1, 50, 10, True)
+                sbs[i % 2].batch.run(3, 1, 50, 10, True, sparse_rows=SPARSE)
         e1.record(streams[0]); e2.record(streams[1])
         torch.cuda.synchronize()
         ms = max(e0.elapsed_time(e1), e0.elapsed_time(e2)) / K_STEPS
