@@ -12,7 +12,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, 'lidar_object_detection_b200', 'csrc')
-HOT = [('fuse.cu', r'lf_fuse_kernelILi8ELi5ELb0', 'lf_fuse_kernel<8 warps, 5 loads, no car_bits> (point pass)'),
+HOT = [('fuse.cu', r'lf_fuse_kernelILi8ELi5ELb0ELi4ELb1', 'lf_fuse_kernel<8 warps, 5 loads, no car_bits, row-map build> (point pass)'),
        ('fuse.cu', r'lf_car_stats_kernel', 'lf_car_stats_kernel (per-car decision)'),
        ('erode.cu', r'lf_erode_fast_kernelINS_6SeSpecILi3ELi0ELi1ELi0ELi0EEELi0EE', 'lf_erode_fast_kernel<SeCross3, uint8> (erode + pack, dominant)'),
        ('erode.cu', r'lf_erode_packed_kernelINS_6SeSpecILi3ELi0ELi1ELi0ELi0EEEEE', 'lf_erode_packed_kernel<SeCross3> (masks arrive bit-packed)'),
