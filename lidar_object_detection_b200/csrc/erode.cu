@@ -555,8 +555,13 @@ extern "C" int lf_erode_pack_rows(lf_ctx* ctx, const void* masks, int mode, int6
     ErodeParams P;
     int spec, fast;
     size_t smem;
-    const int rc = lf_erode_plan(ctx, masks, mode, m, H, W, se, k, iterations,
-                                 mode == 3 ? ER_MAX_ROWS_PACKED : ER_MAX_ROWS, ER_STAGES, &P,
+    // strip height: with a halo of one row (3x3, one pass -- the reference's default) strips of <= 64 rows, i.e. six
+    // strips of a 376-row image and four CTAs per SM instead of three (measured on cfg3: 48 / 56-72 / 80 / 96 / 128
+    // rows -> 1.301 / 1.274 / 1.343 / 1.360 / 1.533 ms with the row map, 1.374 against 1.448 ms without); larger
+    // elements re-read more halo rows per strip and keep the 96-row strips (cfg5, 7x7: 0.368 against 0.374 ms)
+    const int halo_rows = iterations > 0 ? (k / 2) * iterations : 0;
+    const int strip_rows = mode == 3 ? ER_MAX_ROWS_PACKED : (halo_rows <= 1 ? ER_ROWS_SMALL_HALO : ER_MAX_ROWS);
+    const int rc = lf_erode_plan(ctx, masks, mode, m, H, W, se, k, iterations, strip_rows, ER_STAGES, &P,
                                  &spec, &fast, &smem);
     if (rc != LF_OK) return rc;
     const unsigned grid = (unsigned)(m * P.strips);
