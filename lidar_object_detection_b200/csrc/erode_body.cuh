@@ -1,20 +1,17 @@
-// Fast path of K3 (mask binarisation + binary erosion + bit-packing) as a per-item
-// device function, shared by the stand-alone erode kernel (erode.cu) and the
-// persistent batch kernel (batch.cu).  See erode.cu for the algorithm.
+// Fast path of K3 (mask binarisation + binary erosion + bit-packing) as per-item device
+// functions of the erode kernels (erode.cu has the algorithm and the host side).
 #pragma once
 #include "common.cuh"
 #include "bulk.cuh"
 
 constexpr int ER_THREADS = 256;
 constexpr int ER_STAGES = 4;          // stand-alone kernel
-constexpr int ER_STAGES_BATCH = 4;    // persistent batch kernel: more bytes in flight per CTA, shorter strips
 constexpr int ER_CHUNK = 8192;          // bytes per stage: 256 threads x 32 px
 #ifndef LF_ER_MAX_ROWS
 #define LF_ER_MAX_ROWS 96
 #endif
 constexpr int ER_MAX_ROWS = LF_ER_MAX_ROWS;   // strip height bound (smem: 2 x (96+2*halo) x wpr x 4)
 constexpr int ER_ROWS_SMALL_HALO = 64;         // strip height for a halo of at most one row
-constexpr int ER_MAX_ROWS_BATCH = 96;
 constexpr int ER_MAX_ROWS_PACKED = 64;  // masks that arrive bit-packed (mode 3): 26 KB per CTA, 8 CTAs per SM
 
 struct ErodeParams {
